@@ -1,0 +1,112 @@
+"""Pins the CPU oracle (oracle/photometric_oracle.py) to the reference: every fixture under
+tests/golden/ was produced by the reference's own classes (oracle/gen_golden.py, run in the
+build container where /root/reference exists).  CPU only."""
+import numpy as np
+import pytest
+import torch
+
+import photometric_oracle as O
+from golden_cases import CASES, load_golden, make_inputs
+
+TINY = [n for n in CASES if n.startswith('tiny')]
+MID = [n for n in CASES if n.startswith('B2_')]
+BIG = [n for n in CASES if n.startswith('B1_')]
+
+
+def run_oracle(name, dtype=torch.float64):
+    inp = make_inputs(name, dtype)
+    invd = [d.requires_grad_() for d in inp['inv_depths']]
+    vecs = [v.requires_grad_() for v in inp['vecs']]
+    mats = [O.pose_vec_to_mat(v) for v in vecs]
+    for m in mats:
+        m.retain_grad()
+    out = O.multiview_photometric_loss(inp['image'], inp['context'], invd, inp['K'], inp['K'], mats,
+                                       mask=inp['mask'], fork_premap=inp['fork'], return_parts=True, **inp['hp'])
+    out['loss'].backward()
+    return out, invd, vecs, mats
+
+
+def check_case(name, rtol=1e-11):
+    gold = load_golden(name)
+    out, invd, vecs, mats = run_oracle(name)
+    n = len(gold['d_invd_norm'])
+    np.testing.assert_allclose(out['loss'].detach().numpy(), gold['loss'], rtol=rtol)
+    np.testing.assert_allclose(out['photometric_loss'].numpy(), gold['photometric_loss'], rtol=rtol)
+    np.testing.assert_allclose(out['smoothness_loss'].numpy(), gold['smoothness_loss'], rtol=rtol, atol=1e-300)
+    np.testing.assert_allclose(torch.stack([v.grad for v in vecs]).numpy(), gold['d_vec'], rtol=1e-8, atol=1e-13)
+    np.testing.assert_allclose(torch.stack([m.grad for m in mats]).numpy(), gold['d_posemat'], rtol=1e-8, atol=1e-13)
+    np.testing.assert_allclose([invd[i].grad.norm().item() for i in range(n)], gold['d_invd_norm'], rtol=1e-9)
+    for i in range(n):
+        if 'd_invd_s%d' % i in gold:
+            np.testing.assert_allclose(invd[i].grad.numpy(), gold['d_invd_s%d' % i], rtol=1e-8, atol=1e-14)
+        if 'cands_s%d' % i in gold:
+            np.testing.assert_allclose(torch.cat(out['candidates'][i], 1).detach().numpy(), gold['cands_s%d' % i],
+                                       rtol=1e-10, atol=1e-13)
+            for j in range(len(out['warped'])):
+                np.testing.assert_allclose(out['warped'][j][i].detach().numpy(), gold['warp%d_s%d' % (j, i)],
+                                           rtol=1e-10, atol=1e-13)
+        w0 = out['warped'][0][i].detach()
+        np.testing.assert_allclose([w0.mean().item(), w0.abs().sum().item(), (w0 == 0).double().mean().item()],
+                                   gold['warp0_s%d_stats' % i], rtol=1e-10)
+
+
+@pytest.mark.parametrize('name', TINY + MID)
+def test_oracle_matches_reference_small(name):
+    check_case(name)
+
+
+@pytest.mark.parametrize('name', BIG[:2])
+def test_oracle_matches_reference_kitti(name):
+    check_case(name)
+
+
+def test_survey_appendix_b_values():
+    """SURVEY.md Appendix B row 5 (B2 64x160 C2 U zeros), as printed there."""
+    g = load_golden('B2_64x160_C2_U_zeros')
+    assert abs(float(g['loss'][0]) - 0.331711678682) < 1e-11
+    assert abs(float(g['photometric_loss']) - 0.331645006933) < 1e-11
+    np.testing.assert_allclose(g['d_vec'][0, 0], [-1.76486478e-03, 4.82144930e-03, 5.76757203e-05,
+                                                  -9.86472822e-02, -4.32803122e-02, 5.18670414e-02], rtol=1e-7)
+
+
+def test_units_against_reference():
+    u = load_golden('units')
+    t = lambda k: torch.from_numpy(u[k])
+    K, vec, depth, img, img2 = t('K'), t('vec'), t('depth'), t('img'), t('img2')
+    T = O.pose_vec_to_mat(vec)
+    eq = lambda a, b: np.testing.assert_allclose(a.numpy() if hasattr(a, 'numpy') else a, u[b], rtol=1e-12, atol=1e-14)
+    eq(O.euler_to_rotation(vec[:, 3:]), 'euler2mat')
+    eq(T, 'pose_mat')
+    eq(O.invert_rigid(T), 'pose_inv')
+    eq(O.invert_rigid(T), 'invert_pose')
+    eq(T @ O.invert_rigid(T), 'pose_compose')
+    eq(O.lifting_matrix(K), 'Kinv')
+    eq(O.scale_K(K, 0.5), 'K_scaled_half')
+    eq(O.scale_K(K, 0.25, 0.5), 'K_scaled_xy')
+    eq(O.scale_K(K, 0.5, 0.25), 'scale_intrinsics')
+    eq(O.reconstruct(depth, K), 'reconstruct_c')
+    eq(O.reconstruct(depth, K, O.invert_rigid(T)), 'reconstruct_w')
+    X = O.reconstruct(depth, K)
+    eq(O.project(X, K, T), 'project_w')
+    eq(O.project(X, K), 'project_c')
+    eq(O.transform_points(T, X), 'transform_points')
+    for pm in ('zeros', 'border'):
+        eq(O.view_synthesis(img, depth, K, T, K, pm), 'view_synthesis_' + pm)
+    eq(O.ssim_index(img, img2), 'ssim')
+    eq(O.ssim_distance(img, img2), 'ssim_loss')
+    invd = [t('invd0'), t('invd1')]
+    imgs = O.match_scales(img, invd, 2)
+    eq(imgs[1], 'match_scale1')
+    sx, sy = O.smoothness_maps(invd, imgs, 2)
+    eq(sx[0], 'smooth_x0'); eq(sy[0], 'smooth_y0'); eq(sx[1], 'smooth_x1'); eq(sy[1], 'smooth_y1')
+    eq(O.inv2depth(invd[0]), 'inv2depth')
+
+
+def test_grid_sample_probe_values():
+    """SURVEY Appendix A.6 probe, produced by torch in the build container."""
+    u = load_golden('units')
+    np.testing.assert_allclose(u['gs_out_zeros'].ravel(), [1.75, 3.64, 3.0025, 11.0], atol=1e-12)
+    np.testing.assert_allclose(u['gs_out_border'].ravel(), [7.0, 5.2, 3.0025, 11.0], atol=1e-12)
+    np.testing.assert_allclose(u['gs_dgrid_zeros'].reshape(4, 2), [[-10.5, 1.0], [7.8, 2.8], [1.5, 4.0], [-16.5, -11.0]],
+                               atol=1e-12)
+    np.testing.assert_allclose(u['gs_dgrid_border'].reshape(4, 2), [[0, 4], [0, 4], [1.5, 4], [0, 0]], atol=1e-12)
