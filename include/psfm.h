@@ -1,0 +1,144 @@
+/*
+ * psfm.h -- C ABI of libpsfm_b200.so: the multi-view photometric loss with differentiable
+ * view synthesis (forward + backward) as hand-written CUDA kernels for sm_100a.
+ *
+ * The reference (YoungseokOh/packnet-sfm-resnet-san) is 100 % Python/PyTorch and has no
+ * FFI of its own; each entry point below therefore cites the reference *Python* interface
+ * it replaces (file:line relative to the reference root).  INTEGRATION.md shows the ctypes
+ * binding a reference maintainer would add.
+ *
+ * Conventions
+ *   - every data pointer is a DEVICE pointer to a caller-owned, contiguous NCHW buffer;
+ *   - nothing is allocated or freed by the library; scratch lives in a caller-provided
+ *     workspace of psfm_loss_workspace_bytes() bytes;
+ *   - all work is enqueued asynchronously on `stream` (a cudaStream_t passed as void*);
+ *     the library never synchronises;
+ *   - every function returns 0 on success and a negative psfm_status on failure;
+ *     psfm_last_error() returns a thread-local human-readable message;
+ *   - `real` below is the arithmetic type selected by cfg->real_dtype (fp32 in production,
+ *     fp64 for the math-parity tests).  Inverse depths, K, poses, losses and gradients are
+ *     `real`; images are stored as cfg->img_dtype (fp32, bf16 or fp64) and converted on load.
+ *   - reductions are deterministic: per-block partials in fixed slots + fixed-order finish.
+ */
+#ifndef PSFM_H_
+#define PSFM_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PSFM_ABI_VERSION 1
+#define PSFM_MAX_SCALES 4
+#define PSFM_MAX_CTX 8
+
+typedef enum psfm_status {
+  PSFM_OK = 0,
+  PSFM_ERR_INVALID = -1,      /* bad argument / unsupported configuration */
+  PSFM_ERR_CUDA = -2,         /* a CUDA runtime call failed (see psfm_last_error) */
+  PSFM_ERR_WORKSPACE = -3     /* workspace too small */
+} psfm_status;
+
+typedef enum psfm_dtype { PSFM_F32 = 0, PSFM_BF16 = 1, PSFM_F64 = 2 } psfm_dtype;
+typedef enum psfm_padding { PSFM_PAD_ZEROS = 0, PSFM_PAD_BORDER = 1 } psfm_padding;
+typedef enum psfm_reduce { PSFM_REDUCE_MIN = 0, PSFM_REDUCE_MEAN = 1 } psfm_reduce;
+
+/* Hyper-parameters and shapes of one loss evaluation.
+ * Mirrors MultiViewPhotometricLoss.__init__ (losses/multiview_photometric_loss.py:92-118)
+ * and the shapes of MultiViewPhotometricLoss.forward (:331-360). */
+typedef struct psfm_loss_cfg {
+  int32_t B;                      /* batch                                                    */
+  int32_t C;                      /* number of context frames (1..PSFM_MAX_CTX)               */
+  int32_t n;                      /* number of scales in use (1..PSFM_MAX_SCALES)             */
+  int32_t H, W;                   /* size of the full-resolution image (K/ref_K refer to it)  */
+  int32_t Hs[PSFM_MAX_SCALES];    /* inv_depths[i].shape[2]                                   */
+  int32_t Ws[PSFM_MAX_SCALES];    /* inv_depths[i].shape[3]                                   */
+  int32_t img_dtype;              /* psfm_dtype of images / mask                              */
+  int32_t real_dtype;             /* PSFM_F32 or PSFM_F64                                     */
+  int32_t padding;                /* psfm_padding  (padding_mode)                             */
+  int32_t reduce_op;              /* psfm_reduce   (photometric_reduce_op)                    */
+  int32_t automask;               /* automask_loss                                            */
+  int32_t premap;                 /* 0: inv_depths are inverse depths (upstream / north star) */
+                                  /* 1: fork's sigmoid pre-map (:362-369)                     */
+  double ssim_w;                  /* ssim_loss_weight                                         */
+  double smooth_w;                /* smooth_loss_weight                                       */
+  double C1, C2;                  /* SSIM constants                                           */
+  double clip_loss;               /* clip_loss (0 disables)                                   */
+  double min_depth, max_depth;    /* only used when premap == 1                               */
+} psfm_loss_cfg;
+
+/* Device pointers of one loss evaluation.  Per-scale entries beyond cfg->n and per-context
+ * entries beyond cfg->C are ignored.  In "U mode" (all scales full resolution) image[i] and
+ * ctx[i][j] are simply the same pointers for every i. */
+typedef struct psfm_loss_io {
+  const void* image[PSFM_MAX_SCALES];               /* [B,3,Hs,Ws] img_dtype: target at scale i     */
+  const void* ctx[PSFM_MAX_SCALES][PSFM_MAX_CTX];   /* [B,3,Hs,Ws] img_dtype: context j at scale i  */
+  const void* inv_depth[PSFM_MAX_SCALES];           /* [B,1,Hs,Ws] real                              */
+  const void* mask[PSFM_MAX_SCALES];                /* [B,1,Hs,Ws] img_dtype or NULL                 */
+  const void* K;                                    /* [B,3,3] real, full-resolution intrinsics      */
+  const void* ref_K;                                /* [B,3,3] real                                  */
+  const void* pose[PSFM_MAX_CTX];                   /* [B,4,4] real, Pose.mat of context j           */
+  uint8_t* sel[PSFM_MAX_SCALES];                    /* [B,Hs,Ws] u8: arg-min candidate (fwd out, bwd in) */
+  void* d_inv_depth[PSFM_MAX_SCALES];               /* [B,1,Hs,Ws] real (bwd out, overwritten)       */
+  void* d_pose[PSFM_MAX_CTX];                       /* [B,4,4] real (bwd out, overwritten; row 3 = 0) */
+} psfm_loss_io;
+
+int psfm_abi_version(void);
+const char* psfm_last_error(void);
+
+/* Scratch bytes psfm_loss_forward/backward need for this configuration. */
+size_t psfm_loss_workspace_bytes(const psfm_loss_cfg* cfg);
+
+/* MultiViewPhotometricLoss.forward (losses/multiview_photometric_loss.py:331-410) with the
+ * pinhole warp_ref_image (:131-195 upstream form): view synthesis for every (scale, context)
+ * (geometry/camera_utils.py:27-59, geometry/camera.py:111-190, geometry/pose.py:80-86),
+ * calc_photometric_loss (:218-267), automask identity terms (:394-399),
+ * reduce_photometric_loss (:269-297) and calc_smoothness_loss (:301-327).
+ * loss_out: device real[3] = {loss, photometric_loss, smoothness_loss}.
+ * Also fills io->sel (arg-min maps) and workspace state that psfm_loss_backward consumes. */
+int psfm_loss_forward(const psfm_loss_cfg* cfg, const psfm_loss_io* io, void* workspace,
+                      size_t workspace_bytes, void* loss_out, void* stream);
+
+/* Backward of the above (replaces the autograd replay of SURVEY.md §3.3): recomputes the
+ * warp, writes d loss / d inv_depths[i] and d loss / d pose[j].mat, both scaled by the
+ * upstream gradient *grad_loss (device real[1]).  Must follow psfm_loss_forward with the
+ * same cfg/io/workspace. */
+int psfm_loss_backward(const psfm_loss_cfg* cfg, const psfm_loss_io* io, void* workspace,
+                       size_t workspace_bytes, const void* grad_loss, void* stream);
+
+/* Single-pass variant: loss and the gradients for upstream gradient 1 in one sweep over the
+ * inputs (no arg-min maps, no recompute).  Outputs as forward + backward(grad_loss = 1). */
+int psfm_loss_forward_backward(const psfm_loss_cfg* cfg, const psfm_loss_io* io, void* workspace,
+                               size_t workspace_bytes, void* loss_out, void* stream);
+
+/* y[i] = x[i] * (*scale) for i < count; used to apply the upstream gradient to the outputs
+ * of psfm_loss_forward_backward. */
+int psfm_scale_inplace(void* x, const void* scale, size_t count, int real_dtype, void* stream);
+
+/* view_synthesis (geometry/camera_utils.py:27-59): out[B,3,H,W] = grid_sample(ref_image,
+ * project(reconstruct(depth))) with align_corners=True.  K / ref_K are the intrinsics of THIS
+ * resolution (already scaled); pose = ref_cam.Tcw.mat [B,4,4].  depth is a depth map. */
+int psfm_warp_forward(int B, int H, int W, int img_dtype, int real_dtype, int padding,
+                      const void* ref_image, const void* depth, const void* K, const void* ref_K,
+                      const void* pose, void* out, void* stream);
+
+/* Backward of psfm_warp_forward w.r.t. depth [B,1,H,W] and pose [B,4,4] (and, when
+ * d_ref_image != NULL, w.r.t. the reference image, accumulated with atomics into a
+ * pre-zeroed buffer).  grad_out: [B,3,H,W] real.  workspace: psfm_warp_workspace_bytes(). */
+size_t psfm_warp_workspace_bytes(int B, int H, int W, int real_dtype);
+int psfm_warp_backward(int B, int H, int W, int img_dtype, int real_dtype, int padding,
+                       const void* ref_image, const void* depth, const void* K, const void* ref_K,
+                       const void* pose, const void* grad_out, void* d_depth, void* d_pose,
+                       void* d_ref_image, void* workspace, size_t workspace_bytes, void* stream);
+
+/* interpolate_image / match_scales (utils/image.py:117-214): bilinear, align_corners=True
+ * (mode 0) or nearest (mode 1) resize of [N,Hi,Wi] planes to [N,Ho,Wo]. */
+int psfm_resize(int N, int Hi, int Wi, int Ho, int Wo, int dtype, int mode, const void* in, void* out,
+                void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif  /* PSFM_H_ */

@@ -1,0 +1,243 @@
+"""torch.autograd.Function wrappers over the C ABI (include/psfm.h).
+
+`photometric_loss` is the fused hot path behind `MultiViewPhotometricLoss.forward`
+(reference: losses/multiview_photometric_loss.py:331-410); `view_synthesis_op` backs
+`geometry.camera_utils.view_synthesis` (reference: geometry/camera_utils.py:27-59);
+`resize_op` backs `utils.image.interpolate_image` (reference: utils/image.py:117-146).
+PyTorch is used for device memory, streams and autograd plumbing only.
+"""
+import ctypes as C
+import os
+
+import torch
+
+from . import _C
+
+# 'fused': loss and unit-upstream gradients in one sweep (psfm_loss_forward_backward), the
+#          backward only applies the upstream scalar.
+# 'split': psfm_loss_forward, then psfm_loss_backward recomputes the warp (north-star layout).
+DEFAULT_MODE = os.environ.get('PSFM_LOSS_MODE', 'fused')
+
+
+def _as_batched_K(K, B, dtype):
+    if K.dim() == 2:
+        K = K.unsqueeze(0).expand(B, 3, 3)
+    if tuple(K.shape) != (B, 3, 3):
+        raise ValueError('intrinsics must be [B,3,3], got %s' % (tuple(K.shape),))
+    return K.to(dtype).contiguous()
+
+
+def resize_op(x, size, mode='bilinear'):
+    """[..,Hi,Wi] -> [..,Ho,Wo]; bilinear means align_corners=True.  No autograd."""
+    _C.require_cuda(x)
+    if x.requires_grad:
+        raise NotImplementedError('resize of a tensor that requires grad is outside the accelerated path')
+    Ho, Wo = int(size[0]), int(size[1])
+    x = x.contiguous()
+    Hi, Wi = x.shape[-2:]
+    out = torch.empty(x.shape[:-2] + (Ho, Wo), dtype=x.dtype, device=x.device)
+    N = x.numel() // (Hi * Wi)
+    with torch.cuda.device(x.device):
+        _C.check(_C.lib.psfm_resize(N, Hi, Wi, Ho, Wo, _C.dtype_code(x), 0 if mode == 'bilinear' else 1,
+                                    _C.ptr(x), _C.ptr(out), _C.stream_ptr(x.device)))
+    return out
+
+
+class _LossPlan:
+    """cfg / io structs and buffers for one call."""
+
+    def __init__(self, hp, image, context, inv_depths, K, ref_K, pose_mats, mask):
+        n, Cn = len(inv_depths), len(context)
+        B, ch, H, W = image.shape
+        if ch != 3:
+            raise ValueError('image must be [B,3,H,W]')
+        if n < 1 or n > _C.MAX_SCALES:
+            raise ValueError('between 1 and %d scales are supported, got %d' % (_C.MAX_SCALES, n))
+        if Cn < 1 or Cn > _C.MAX_CTX:
+            raise ValueError('between 1 and %d context frames are supported, got %d' % (_C.MAX_CTX, Cn))
+        if len(pose_mats) != Cn:
+            raise ValueError('need one pose per context frame')
+        _C.require_cuda(image, K, ref_K, mask, *context, *inv_depths, *pose_mats)
+        real = inv_depths[0].dtype
+        if real not in (torch.float32, torch.float64):
+            raise ValueError('inverse depths must be float32 (or float64 for the math-parity build)')
+        img_dtype = image.dtype
+        dev = image.device
+        self.real, self.dev, self.n, self.C, self.B = real, dev, n, Cn, B
+        cfg = _C.LossCfg()
+        cfg.B, cfg.C, cfg.n, cfg.H, cfg.W = B, Cn, n, H, W
+        cfg.img_dtype = _C.dtype_code(image)
+        cfg.real_dtype = _C.F64 if real == torch.float64 else _C.F32
+        cfg.padding = _C.PAD[hp['padding_mode']] if hp['padding_mode'] in _C.PAD else -1
+        if hp['photometric_reduce_op'] not in _C.REDUCE:
+            raise NotImplementedError('Unknown photometric_reduce_op: {}'.format(hp['photometric_reduce_op']))
+        cfg.reduce_op = _C.REDUCE[hp['photometric_reduce_op']]
+        cfg.automask = int(bool(hp['automask_loss']))
+        cfg.premap = int(hp.get('premap', 0))
+        cfg.ssim_w, cfg.smooth_w = float(hp['ssim_loss_weight']), float(hp['smooth_loss_weight'])
+        cfg.C1, cfg.C2, cfg.clip_loss = float(hp['C1']), float(hp['C2']), float(hp['clip_loss'])
+        cfg.min_depth, cfg.max_depth = float(hp.get('min_depth', 0.05)), float(hp.get('max_depth', 80.0))
+        io = _C.LossIO()
+        keep = []
+        image = image.contiguous()
+        context = [c.to(img_dtype).contiguous() for c in context]
+        for c in context:
+            if tuple(c.shape) != (B, 3, H, W):
+                raise ValueError('context frames must match the image shape')
+        if mask is not None:
+            mask = mask.to(img_dtype).contiguous()
+        self.inv_depths = [d.contiguous() for d in inv_depths]
+        for s, d in enumerate(self.inv_depths):
+            if d.dim() != 4 or d.shape[0] != B or d.shape[1] != 1 or d.dtype != real:
+                raise ValueError('inv_depths[%d] must be [B,1,Hs,Ws] %s' % (s, real))
+            Hs, Ws = int(d.shape[2]), int(d.shape[3])
+            cfg.Hs[s], cfg.Ws[s] = Hs, Ws
+            if (Hs, Ws) == (H, W):          # interpolate_image returns the image itself (utils/image.py:138-142)
+                img_s, ctx_s, mask_s = image, context, mask
+            else:                           # match_scales: bilinear align_corners=True; nearest for the mask
+                img_s = resize_op(image, (Hs, Ws))
+                ctx_s = [resize_op(c, (Hs, Ws)) for c in context]
+                mask_s = None if mask is None else resize_op(mask, (Hs, Ws), mode='nearest')
+            keep += [img_s, mask_s] + list(ctx_s)
+            io.image[s] = img_s.data_ptr()
+            io.inv_depth[s] = d.data_ptr()
+            io.mask[s] = 0 if mask_s is None else mask_s.data_ptr()
+            for j in range(Cn):
+                io.ctx[s][j] = ctx_s[j].data_ptr()
+        self.K = _as_batched_K(K, B, real)
+        self.ref_K = _as_batched_K(ref_K, B, real)
+        io.K, io.ref_K = self.K.data_ptr(), self.ref_K.data_ptr()
+        self.pose = []
+        for j, m in enumerate(pose_mats):
+            if tuple(m.shape) != (B, 4, 4):
+                raise ValueError('pose matrices must be [B,4,4]')
+            m = m.to(real).contiguous()
+            self.pose.append(m)
+            io.pose[j] = m.data_ptr()
+        self.keep = keep
+        self.cfg, self.io = cfg, io
+        self.ws_bytes = int(_C.lib.psfm_loss_workspace_bytes(C.byref(cfg)))
+        if self.ws_bytes == 0:
+            _C.check(-1)
+        self.ws = torch.empty(self.ws_bytes, dtype=torch.uint8, device=dev)
+        self.sel = [torch.empty((B,) + tuple(d.shape[2:]), dtype=torch.uint8, device=dev) for d in self.inv_depths]
+        for s in range(n):
+            io.sel[s] = self.sel[s].data_ptr()
+        self.out = torch.empty(3, dtype=real, device=dev)
+        self.grads = None
+
+    def alloc_grads(self):
+        sizes = [d.numel() for d in self.inv_depths] + [self.B * 16] * self.C
+        flat = torch.empty(sum(sizes), dtype=self.real, device=self.dev)
+        views, off = [], 0
+        for sz in sizes:
+            views.append(flat[off:off + sz])
+            off += sz
+        self.grads = flat
+        self.d_invd = [v.view_as(d) for v, d in zip(views[:self.n], self.inv_depths)]
+        self.d_pose = [v.view(self.B, 4, 4) for v in views[self.n:]]
+        for s in range(self.n):
+            self.io.d_inv_depth[s] = self.d_invd[s].data_ptr()
+        for j in range(self.C):
+            self.io.d_pose[j] = self.d_pose[j].data_ptr()
+
+    def args(self):
+        return C.byref(self.cfg), C.byref(self.io), _C.ptr(self.ws), self.ws_bytes
+
+
+class _PhotometricLossFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, hp, mode, image, K, ref_K, mask, n, Cn, *tensors):
+        context, inv_depths, pose_mats = tensors[:Cn], tensors[Cn:Cn + n], tensors[Cn + n:]
+        plan = _LossPlan(hp, image, context, inv_depths, K, ref_K, pose_mats, mask)
+        need_grad = any(t.requires_grad for t in tensors[Cn:])
+        st = _C.stream_ptr(plan.dev)
+        with torch.cuda.device(plan.dev):
+            if need_grad and mode == 'fused':
+                plan.alloc_grads()
+                _C.check(_C.lib.psfm_loss_forward_backward(*plan.args(), _C.ptr(plan.out), st))
+            else:
+                _C.check(_C.lib.psfm_loss_forward(*plan.args(), _C.ptr(plan.out), st))
+        ctx.plan, ctx.mode, ctx.consumed = plan, mode, False
+        ctx.counts = (n, Cn)
+        return plan.out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        plan, (n, Cn) = ctx.plan, ctx.counts
+        g = grad_out.to(plan.real).contiguous()
+        st = _C.stream_ptr(plan.dev)
+        with torch.cuda.device(plan.dev):
+            if ctx.mode == 'fused':
+                if ctx.consumed:
+                    raise RuntimeError('the fused photometric loss keeps its gradients in place and can be '
+                                       'back-propagated once; use mode="split" to retain the graph')
+                ctx.consumed = True
+                _C.check(_C.lib.psfm_scale_inplace(_C.ptr(plan.grads), _C.ptr(g), plan.grads.numel(),
+                                                   plan.cfg.real_dtype, st))
+            else:
+                plan.alloc_grads()
+                _C.check(_C.lib.psfm_loss_backward(*plan.args(), _C.ptr(g), st))
+        return (None,) * 8 + (None,) * Cn + tuple(plan.d_invd) + tuple(plan.d_pose)
+
+
+def photometric_loss(hp, image, context, inv_depths, K, ref_K, pose_mats, mask=None, mode=None):
+    """Returns a [3] tensor {loss, photometric_loss, smoothness_loss}; element 0 carries the
+    gradient w.r.t. `inv_depths` and `pose_mats`."""
+    mode = DEFAULT_MODE if mode is None else mode
+    if mode not in ('fused', 'split'):
+        raise ValueError('mode must be "fused" or "split"')
+    n, Cn = len(inv_depths), len(context)
+    return _PhotometricLossFn.apply(hp, mode, image, K, ref_K, mask, n, Cn, *context, *inv_depths, *pose_mats)
+
+
+class _ViewSynthesisFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, ref_image, depth, K, ref_K, pose, padding):
+        _C.require_cuda(ref_image, depth, K, ref_K, pose)
+        B, ch, H, W = ref_image.shape
+        if ch != 3:
+            raise ValueError('ref_image must be [B,3,H,W]')
+        real = depth.dtype
+        ref_image = ref_image.contiguous()
+        depth = depth.contiguous()
+        K, ref_K = _as_batched_K(K, B, real), _as_batched_K(ref_K, B, real)
+        pose = pose.to(real).contiguous()
+        out = torch.empty((B, 3, H, W), dtype=real, device=depth.device)
+        rd = _C.F64 if real == torch.float64 else _C.F32
+        with torch.cuda.device(depth.device):
+            _C.check(_C.lib.psfm_warp_forward(B, H, W, _C.dtype_code(ref_image), rd, padding, _C.ptr(ref_image),
+                                              _C.ptr(depth), _C.ptr(K), _C.ptr(ref_K), _C.ptr(pose), _C.ptr(out),
+                                              _C.stream_ptr(depth.device)))
+        ctx.save_for_backward(ref_image, depth, K, ref_K, pose)
+        ctx.padding = padding
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        ref_image, depth, K, ref_K, pose = ctx.saved_tensors
+        B, _, H, W = ref_image.shape
+        real = depth.dtype
+        rd = _C.F64 if real == torch.float64 else _C.F32
+        grad_out = grad_out.to(real).contiguous()
+        d_depth = torch.empty_like(depth)
+        d_pose = torch.empty((B, 4, 4), dtype=real, device=depth.device)
+        d_ref = torch.zeros(ref_image.shape, dtype=real, device=depth.device) if ctx.needs_input_grad[0] else None
+        nbytes = int(_C.lib.psfm_warp_workspace_bytes(B, H, W, rd))
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=depth.device)
+        with torch.cuda.device(depth.device):
+            _C.check(_C.lib.psfm_warp_backward(B, H, W, _C.dtype_code(ref_image), rd, ctx.padding, _C.ptr(ref_image),
+                                               _C.ptr(depth), _C.ptr(K), _C.ptr(ref_K), _C.ptr(pose),
+                                               _C.ptr(grad_out), _C.ptr(d_depth), _C.ptr(d_pose), _C.ptr(d_ref),
+                                               _C.ptr(ws), nbytes, _C.stream_ptr(depth.device)))
+        if d_ref is not None:
+            d_ref = d_ref.to(ref_image.dtype)
+        return d_ref, d_depth, None, None, d_pose, None
+
+
+def view_synthesis_op(ref_image, depth, K, ref_K, pose_mat, padding_mode='zeros'):
+    if padding_mode not in _C.PAD:
+        raise ValueError('padding_mode must be zeros or border (got %s)' % padding_mode)
+    if depth.dtype not in (torch.float32, torch.float64):
+        raise ValueError('depth must be float32 or float64')
+    return _ViewSynthesisFn.apply(ref_image, depth, K, ref_K, pose_mat, _C.PAD[padding_mode])
