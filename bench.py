@@ -1,0 +1,442 @@
+#!/usr/bin/env python
+"""bench.py -- photometric-loss fwd+bwd frames/s (BASELINE.json metric) on N B200s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--config 2]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" is one forward + backward of MultiViewPhotometricLoss over one batch of synthetic
+frames (BASELINE.json configs[1] by default: B=8 per GPU, 192x640, 2 contexts, 4 full-resolution
+scales, fp32, zeros padding, automask).  Prints ONE JSON line on rank 0.
+
+value      frames/s with the inputs resident in HBM; K steps between two CUDA events, max over ranks.
+           Steps rotate over several resident input sets whose total footprint exceeds 3x the L2, so
+           every step reads its inputs from HBM (no flush launches inside the timed region).
+e2e        the same metric through the public API with HOST (pinned) inputs: H2D copy of the
+           step's inputs + fwd+bwd + D2H read of the loss inside the timed region.
+roofline   algorithmic bytes of the dominant kernel / its live CUDA-event time
+           (psfm_profile_* hooks), against MEASURED_PEAKS.json.
+cpu_baseline / --impl reference: the CPU oracle (oracle/photometric_oracle.py, a port of the
+           reference's PyTorch implementation -- the reference is pure Python and cannot compile
+           to oracle/_ref) timed on this box's host cores.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, 'packnet-sfm-resnet-san_b200'))
+
+import torch  # noqa: E402
+
+CONFIGS = {
+    # name: B per GPU, H, W, C, n, img dtype, padding          (BASELINE.json configs[k])
+    1: dict(B=1, H=192, W=640, C=2, n=4, img='fp32', padding='zeros'),
+    2: dict(B=8, H=192, W=640, C=2, n=4, img='fp32', padding='zeros'),
+    3: dict(B=8, H=384, W=640, C=2, n=4, img='bf16', padding='zeros'),
+    4: dict(B=4, H=1216, W=1936, C=2, n=4, img='fp32', padding='border'),
+    5: dict(B=32, H=384, W=640, C=4, n=4, img='fp32', padding='zeros'),
+}
+LOSS_HP = dict(num_scales=4, ssim_loss_weight=0.85, smooth_loss_weight=0.001, photometric_reduce_op='min',
+               clip_loss=0.0, automask_loss=True)
+METRIC = 'photometric-loss fwd+bwd frames/s'
+
+
+def workload_name(k, cfg):
+    return 'configs[%d]: B=%d/GPU %dx%d C=%d n=%d U-mode %s %s automask' % (
+        k - 1, cfg['B'], cfg['W'], cfg['H'], cfg['C'], cfg['n'], cfg['img'], cfg['padding'])
+
+
+def bytes_per_frame(cfg, part='all'):
+    """sum_s P_s * (12 + 6 e (1 + C)); fwd share = 4 + 3e(1+C), bwd share = that + 4."""
+    e = 2 if cfg['img'] == 'bf16' else 4
+    P = cfg['H'] * cfg['W']
+    fwd = 4 + 3 * e * (1 + cfg['C'])
+    per_px = {'all': 2 * fwd + 4, 'fwd': fwd, 'bwd': fwd + 4}[part]
+    return cfg['n'] * P * per_px
+
+
+def synth_batch(cfg, device, seed=1234):
+    """Synthetic frames of the workload's shape: box-filtered uniform noise images, inverse depths of
+    a 2..40 m scene, small ego-motion (the shapes/statistics of SURVEY.md recipe S3)."""
+    import torch.nn.functional as F
+    g = torch.Generator('cpu').manual_seed(seed)
+    B, H, W, C, n = cfg['B'], cfg['H'], cfg['W'], cfg['C'], cfg['n']
+
+    def tex(ch, k):
+        x = torch.rand(B, ch, H, W, generator=g)
+        x = F.avg_pool2d(F.pad(x, (k // 2,) * 4, mode='reflect'), k, 1)
+        lo, hi = x.amin((2, 3), True), x.amax((2, 3), True)
+        return (x - lo) / (hi - lo)
+
+    idt = torch.bfloat16 if cfg['img'] == 'bf16' else torch.float32
+    image = tex(3, 3).to(idt)
+    context = [tex(3, 3).to(idt) for _ in range(C)]
+    inv_depths = [1.0 / (2.0 + 38.0 * tex(1, 15)) for _ in range(n)]
+    base = torch.tensor([0.02, -0.01, 0.8, 0.003, -0.01, 0.002])
+    vecs = []
+    for j in range(C):
+        v = base.clone()
+        v[2] *= (-1.0 if j % 2 == 0 else 1.0)
+        vecs.append(v.repeat(B, 1) + 0.01 * torch.randn(B, 6, generator=g))
+    K = torch.tensor([[0.58 * W, 0, 0.5 * W], [0, 1.92 * H, 0.5 * H], [0, 0, 1.]]).repeat(B, 1, 1)
+    host = dict(image=image, context=context, inv_depths=inv_depths, vecs=vecs, K=K)
+    if device is None:
+        return host
+    mv = lambda t: t.to(device)
+    return dict(image=mv(image), context=[mv(c) for c in context], inv_depths=[mv(d) for d in inv_depths],
+                vecs=[mv(v) for v in vecs], K=mv(K))
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons while the timed region runs."""
+    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q,
+                                      '--format=csv,noheader,nounits'], capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in out.strip().split(',')]
+                if len(f) >= 6:
+                    self.rows.append(f)
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def summary(self):
+        self.stop_flag = True
+        self.join(timeout=6)
+        if not self.rows:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['unavailable']}
+        sm = sorted(float(r[0]) for r in self.rows)
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        reasons = [n for k, n in enumerate(names) if any(r[2 + k].lower().startswith('active') for r in self.rows)]
+        return {'sm_mhz': sm[len(sm) // 2], 'sm_max_mhz': float(self.rows[0][1]), 'reasons': reasons,
+                'samples': len(self.rows)}
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, 'MEASURED_PEAKS.json')) as f:
+            return float(json.load(f)['hbm_gbs']), 'measured (MEASURED_PEAKS.json hbm_gbs)'
+    except Exception:
+        return 6650.0, 'fallback (B200_PROFILING.md)'
+
+
+def cpu_oracle_rate(cfg, frames_per_step, min_seconds=10.0, max_iters=10, warmup=1, threads=None):
+    """frames/s of the CPU oracle (port of the reference's PyTorch implementation), fwd+bwd."""
+    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+    import photometric_oracle as O
+    if threads:
+        torch.set_num_threads(threads)
+    c = dict(cfg, B=frames_per_step)
+    h = synth_batch(c, None)
+    hp = dict(LOSS_HP, padding_mode=cfg['padding'])
+    f32 = lambda t: t.float()
+
+    def one():
+        invd = [d.clone().requires_grad_() for d in h['inv_depths']]
+        vecs = [v.clone().requires_grad_() for v in h['vecs']]
+        out = O.multiview_photometric_loss(f32(h['image']), [f32(x) for x in h['context']], invd, h['K'], h['K'],
+                                           [O.pose_vec_to_mat(v) for v in vecs], **hp)
+        out['loss'].backward()
+        return float(out['loss'])
+
+    for _ in range(warmup):
+        one()
+    times = []
+    t_all = time.perf_counter()
+    while len(times) < max_iters and (time.perf_counter() - t_all < min_seconds or len(times) < 3):
+        t0 = time.perf_counter()
+        one()
+        times.append(time.perf_counter() - t0)
+    times.sort()
+    med = times[len(times) // 2]
+    return frames_per_step / med, len(times), torch.get_num_threads()
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path (oracle port; the reference
+    is pure Python, no oracle/_ref binary) on the host cores; rank 0 only."""
+    if int(os.environ.get('RANK', 0)) != 0:
+        return
+    cfg = CONFIGS[args.config]
+    sample = 1                     # frames per CPU step: a bounded sample of the B-frame batch
+    cores = os.cpu_count()
+    torch.set_num_threads(cores)
+    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+    import photometric_oracle as O
+    c = dict(cfg, B=sample)
+    h = synth_batch(c, None)
+    hp = dict(LOSS_HP, padding_mode=cfg['padding'])
+
+    def one():
+        invd = [d.clone().requires_grad_() for d in h['inv_depths']]
+        vecs = [v.clone().requires_grad_() for v in h['vecs']]
+        out = O.multiview_photometric_loss(h['image'].float(), [x.float() for x in h['context']], invd, h['K'],
+                                           h['K'], [O.pose_vec_to_mat(v) for v in vecs], **hp)
+        out['loss'].backward()
+
+    steps = min(args.steps, 40)    # bounded: each CPU step costs ~0.1-0.5 s per frame
+    for _ in range(min(args.warmup, 3)):
+        one()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        one()
+    dt = time.perf_counter() - t0
+    val = sample * steps / dt
+    line = {'impl': 'reference', 'metric': METRIC, 'value': val, 'unit': 'frames/s', 'n_gpus': args.gpus,
+            'steps': steps, 'warmup': min(args.warmup, 3), 'ms_per_step': 1e3 * dt / steps,
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': {'workload': workload_name(args.config, cfg)},
+            'cpu_baseline': {'value': val, 'unit': 'frames/s', 'cores': torch.get_num_threads(), 'kind': 'port',
+                             'sample': '%d frame(s) of the %d-frame batch per step, %d steps, fp32, PyTorch CPU' % (
+                                 sample, cfg['B'], steps)},
+            'e2e': {'value': val, 'unit': 'frames/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import torch.distributed as dist
+    world, rank = int(os.environ.get('WORLD_SIZE', 1)), int(os.environ.get('RANK', 0))
+    local = int(os.environ.get('LOCAL_RANK', 0))
+    dev = torch.device('cuda', local)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    from packnet_sfm import _C
+    from packnet_sfm.losses.multiview_photometric_loss import MultiViewPhotometricLoss
+    from packnet_sfm.geometry.pose import Pose
+    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+
+    cfg = CONFIGS[args.config]
+    B = cfg['B']
+    loss_fn = MultiViewPhotometricLoss(padding_mode=cfg['padding'], kernel_mode=args.mode, **LOSS_HP)
+    real_b = 4
+    e = 2 if cfg['img'] == 'bf16' else 4
+    P = cfg['H'] * cfg['W']
+    in_bytes = B * P * (3 * e * (1 + cfg['C']) + real_b * cfg['n'])          # inputs of one step
+    foot = in_bytes + B * P * (real_b + 1) * cfg['n']                        # + grads + arg-min maps
+    L2 = 126 * 2 ** 20
+    R = max(2, -(-3 * L2 // foot)) if not args.no_rotate else 1              # rotating input sets > 3x L2
+
+    class Slot:
+        """One resident input set (device) with its pinned host copy and, optionally, a CUDA graph."""
+        def __init__(self, seed):
+            self.host = synth_batch(cfg, None, seed)
+            self.pin = {k: ([t.pin_memory() for t in v] if isinstance(v, list) else v.pin_memory())
+                        for k, v in self.host.items()}
+            d = {k: ([t.to(dev) for t in v] if isinstance(v, list) else v.to(dev)) for k, v in self.host.items()}
+            self.image, self.context, self.K = d['image'], d['context'], d['K']
+            self.invd = [x.requires_grad_() for x in d['inv_depths']]
+            with torch.no_grad():
+                self.mats = [Pose.from_vec(v, 'euler').mat for v in d['vecs']]
+            self.mats = [m.requires_grad_() for m in self.mats]
+            self.mats_pin = [m.detach().cpu().pin_memory() for m in self.mats]
+            self.graph, self.loss = None, None
+
+        def step(self):
+            for t in self.invd + self.mats:
+                t.grad = None
+            out = loss_fn(self.image, self.context, self.invd, self.K, self.K, [Pose(m) for m in self.mats])
+            out['loss'].backward()
+            self.loss = out['loss']
+            return self.loss
+
+        def capture(self):
+            s = torch.cuda.Stream()
+            s.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s):
+                for _ in range(2):
+                    self.step()
+            torch.cuda.current_stream().wait_stream(s)
+            self.graph = torch.cuda.CUDAGraph()
+            for t in self.invd + self.mats:
+                t.grad = None
+            with torch.cuda.graph(self.graph):
+                self.step()
+
+        def run(self):
+            if self.graph is not None:
+                self.graph.replay()
+            else:
+                self.step()
+            return self.loss
+
+        def upload(self):
+            """H2D of this step's inputs from pinned host memory."""
+            n = 0
+            self.image.copy_(self.pin['image'], non_blocking=True); n += self.image.numel() * self.image.element_size()
+            for a, b in zip(self.context, self.pin['context']):
+                a.copy_(b, non_blocking=True); n += a.numel() * a.element_size()
+            with torch.no_grad():
+                for a, b in zip(self.invd, self.pin['inv_depths']):
+                    a.copy_(b, non_blocking=True); n += a.numel() * a.element_size()
+                for a, b in zip(self.mats, self.mats_pin):
+                    a.copy_(b, non_blocking=True); n += a.numel() * a.element_size()
+            self.K.copy_(self.pin['K'], non_blocking=True); n += self.K.numel() * self.K.element_size()
+            return n
+
+    slots = [Slot(1234 + 100 * rank + r) for r in range(R)]
+    # launches of one eager step (my kernels only; counted by the library)
+    torch.cuda.synchronize()
+    c0 = _C.lib.psfm_launch_count()
+    slots[0].step()
+    torch.cuda.synchronize()
+    launches_per_step = int(_C.lib.psfm_launch_count() - c0)
+
+    use_graph = not args.no_graph
+    if use_graph:
+        try:
+            for s in slots:
+                s.capture()
+        except Exception as ex:      # keep measuring eagerly, but say so
+            print('[bench] CUDA graph capture failed (%s); timing eager launches' % ex, file=sys.stderr)
+            use_graph = False
+            for s in slots:
+                s.graph = None
+
+    red = torch.zeros(3, device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def run_steps(k, e2e=False):
+        """k steps; multi-GPU: one all-reduce of the loss triple per step, waited on one step later
+        so that it overlaps the next step's kernels (all are complete before the region ends)."""
+        pending, h2d, d2h = None, 0, 0
+        host_loss = torch.empty(1, dtype=torch.float32).pin_memory()
+        for i in range(k):
+            s = slots[i % R]
+            if e2e:
+                h2d = s.upload()
+            loss = s.run()
+            if world > 1:
+                if pending is not None:
+                    pending.wait()
+                red[0:1].copy_(loss.detach())
+                pending = dist.all_reduce(red, async_op=True)
+            if e2e:
+                host_loss.copy_(loss.detach(), non_blocking=True)
+                torch.cuda.current_stream().synchronize()
+                d2h = host_loss.numel() * 4
+        if pending is not None:
+            pending.wait()
+        return h2d, d2h
+
+    # ---- value: inputs resident, K steps, CUDA events, max over ranks -------------------------------
+    run_steps(max(args.warmup, 3))
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    run_steps(args.steps)
+    ev1.record()
+    barrier()
+    t_ms = ev0.elapsed_time(ev1)
+    clocks = sampler.summary() if sampler else None
+    # ---- e2e: host inputs, H2D + step + D2H of the loss ----------------------------------------------
+    run_steps(3, e2e=True)
+    barrier()
+    ev2, ev3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev2.record()
+    h2d, d2h = run_steps(args.steps, e2e=True)
+    ev3.record()
+    barrier()
+    t_e2e_ms = ev2.elapsed_time(ev3)
+    tt = torch.tensor([t_ms, t_e2e_ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    t_ms, t_e2e_ms = tt.tolist()
+
+    # ---- dominant kernel, live CUDA-event timing through the library's profile hooks (eager) --------
+    roof = None
+    if rank == 0:
+        _C.lib.psfm_profile_enable(1)
+        PS = 12
+        for i in range(PS):
+            slots[i % R].step()
+        torch.cuda.synchronize()
+        recs = _C.profile_read()
+        _C.lib.psfm_profile_enable(0)
+        by = {}
+        for tag, ms in recs:
+            by.setdefault(tag, []).append(ms)
+        per_step = {t: sum(v) / PS for t, v in by.items()}
+        dom = max(per_step, key=per_step.get)
+        part = {'loss_fwd': 'fwd', 'loss_bwd': 'bwd', 'loss_fused': 'all'}.get(dom, 'all')
+        alg = bytes_per_frame(cfg, part) * B
+        peak, how = measured_peak()
+        ach = alg / (per_step[dom] * 1e-3) / 1e9
+        traffic = None
+        try:
+            with open(os.path.join(ROOT, 'profiles', 'traffic.json')) as f:
+                traffic = json.load(f).get(dom)
+        except Exception:
+            pass
+        roof = {'bound': 'hbm', 'kernel': dom, 'achieved': ach, 'peak': peak, 'unit': 'GB/s', 'frac': ach / peak,
+                'traffic': traffic, 'peak_source': how, 'algorithmic_bytes_per_step': alg,
+                'kernel_ms_per_step': per_step[dom], 'all_kernels_ms_per_step': per_step,
+                'frac_of_nominal_8TBs': ach / 8000.0}
+
+    if rank == 0:
+        frames = world * B * args.steps
+        cpu_val, cpu_iters, cpu_threads = (None, 0, 0)
+        if not args.no_cpu:
+            cpu_val, cpu_iters, cpu_threads = cpu_oracle_rate(CONFIGS[1], 1)
+        line = {'metric': METRIC, 'value': frames / (t_ms * 1e-3), 'unit': 'frames/s', 'n_gpus': world,
+                'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': t_ms / args.steps,
+                'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+                'config': {'workload': workload_name(args.config, cfg), 'global_batch': world * B,
+                           'l2': 'rotating %d resident input sets (%.0f MB total footprint > 3x 126 MB L2)' % (
+                               R, R * foot / 2 ** 20),
+                           'cuda_graph': use_graph, 'kernel_mode': args.mode or 'fused',
+                           'loss': dict(LOSS_HP, padding_mode=cfg['padding']),
+                           'parallelism': 'dp%d (batch-sharded, one NCCL all-reduce of the loss per step)' % world},
+                'e2e': {'value': frames / (t_e2e_ms * 1e-3), 'unit': 'frames/s', 'h2d_bytes_per_step': h2d,
+                        'd2h_bytes_per_step': d2h, 'ms_per_step': t_e2e_ms / args.steps},
+                'gpu_launches': launches_per_step * args.steps, 'gpu_launches_per_step': launches_per_step,
+                'clocks': clocks, 'roofline': roof,
+                'cpu_baseline': None if cpu_val is None else {
+                    'value': cpu_val, 'unit': 'frames/s', 'cores': cpu_threads, 'kind': 'port',
+                    'sample': 'configs[0] (B=1 192x640 C=2 n=4 fp32), median of %d fwd+bwd iterations of the '
+                              'PyTorch-CPU oracle' % cpu_iters}}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=200)
+    ap.add_argument('--warmup', type=int, default=20)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--config', type=int, default=2, choices=sorted(CONFIGS))
+    ap.add_argument('--mode', default=None, choices=['fused', 'split'])
+    ap.add_argument('--no-graph', action='store_true')
+    ap.add_argument('--no-rotate', action='store_true')
+    ap.add_argument('--no-cpu', action='store_true')
+    args = ap.parse_args()
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == '__main__':
+    main()

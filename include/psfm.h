@@ -88,6 +88,15 @@ typedef struct psfm_loss_io {
 int psfm_abi_version(void);
 const char* psfm_last_error(void);
 
+/* Measurement hooks (no reference counterpart; used by bench.py).  psfm_launch_count: kernels
+ * this library has launched since load.  psfm_profile_enable(1) makes the loss entry points
+ * bracket their kernels with CUDA events on the caller's stream; psfm_profile_read waits for
+ * them, returns up to max_records (elapsed ms, tag) pairs and clears the list.
+ * tags: 0 mean, 1 loss forward, 2 loss backward, 3 finish passes, 4 fused forward+backward. */
+unsigned long long psfm_launch_count(void);
+int psfm_profile_enable(int on);
+int psfm_profile_read(float* ms, int* tags, int max_records);
+
 /* Scratch bytes psfm_loss_forward/backward need for this configuration. */
 size_t psfm_loss_workspace_bytes(const psfm_loss_cfg* cfg);
 

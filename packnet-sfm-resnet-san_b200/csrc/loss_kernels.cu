@@ -13,6 +13,7 @@
 #include <math_constants.h>
 #include "psfm_device.cuh"
 #include "loss_params.h"
+#include "profile.h"
 
 namespace psfm {
 
@@ -581,15 +582,25 @@ static cudaError_t run_forward(const psfm_loss_cfg* cfg, const psfm_loss_io* io,
   LossParams P;
   build_params(cfg, io, ws, P);
   P.loss_out = loss_out;
-  if (cfg->smooth_w > 0.0) mean_kernel<real><<<dim3(cfg->B, cfg->n), 1024, 0, st>>>(P);
+  if (cfg->smooth_w > 0.0) {
+    ProfScope ps(st, kTagMean, 1);
+    mean_kernel<real><<<dim3(cfg->B, cfg->n), 1024, 0, st>>>(P);
+  }
   if (cfg->clip_loss > 0.0) {
+    ProfScope ps(st, kTagOther, cfg->n + 1);
     for (int s = 0; s < cfg->n; ++s)
       loss_fwd_kernel<real, img_t><<<dim3(P.sc[s].tiles_x, P.sc[s].tiles_y, cfg->B), kThreads, 0, st>>>(P, s, 1);
     clip_finish_kernel<real><<<1, 256, 0, st>>>(P);
   }
-  for (int s = 0; s < cfg->n; ++s)
-    loss_fwd_kernel<real, img_t><<<dim3(P.sc[s].tiles_x, P.sc[s].tiles_y, cfg->B), kThreads, 0, st>>>(P, s, 0);
-  loss_finish_kernel<real><<<1, 256, 0, st>>>(P);
+  {
+    ProfScope ps(st, kTagFwd, cfg->n);
+    for (int s = 0; s < cfg->n; ++s)
+      loss_fwd_kernel<real, img_t><<<dim3(P.sc[s].tiles_x, P.sc[s].tiles_y, cfg->B), kThreads, 0, st>>>(P, s, 0);
+  }
+  {
+    ProfScope ps(st, kTagFinish, 1);
+    loss_finish_kernel<real><<<1, 256, 0, st>>>(P);
+  }
   return cudaGetLastError();
 }
 
@@ -599,9 +610,15 @@ static cudaError_t run_backward(const psfm_loss_cfg* cfg, const psfm_loss_io* io
   LossParams P;
   build_params(cfg, io, ws, P);
   P.grad_loss = grad_loss;
-  for (int s = 0; s < cfg->n; ++s)
-    loss_bwd_kernel<real, img_t><<<dim3(P.sc[s].tiles_x, P.sc[s].tiles_y, cfg->B), kThreads, 0, st>>>(P, s);
-  pose_finish_kernel<real><<<dim3(cfg->B, cfg->C), 32, 0, st>>>(P, 0);
+  {
+    ProfScope ps(st, kTagBwd, cfg->n);
+    for (int s = 0; s < cfg->n; ++s)
+      loss_bwd_kernel<real, img_t><<<dim3(P.sc[s].tiles_x, P.sc[s].tiles_y, cfg->B), kThreads, 0, st>>>(P, s);
+  }
+  {
+    ProfScope ps(st, kTagFinish, 1);
+    pose_finish_kernel<real><<<dim3(cfg->B, cfg->C), 32, 0, st>>>(P, 0);
+  }
   return cudaGetLastError();
 }
 

@@ -4,6 +4,7 @@
 //   scale_inplace         x *= *scale
 #include <cuda_runtime.h>
 #include "psfm_device.cuh"
+#include "profile.h"
 
 namespace psfm {
 
@@ -161,6 +162,7 @@ static cudaError_t warp_forward_t(int B, int H, int W, int padding, const void* 
                                   const void* refK, const void* pose, void* out, cudaStream_t st) {
   const size_t plane = (size_t)H * W;
   dim3 grid((unsigned)((plane + kOpThreads - 1) / kOpThreads), B);
+  count_launches(1);
   warp_fwd_kernel<real, img_t><<<grid, kOpThreads, 0, st>>>(H, W, padding, (const img_t*)ref, (const real*)depth,
                                                             (const real*)K, (const real*)refK, (const real*)pose,
                                                             (real*)out);
@@ -188,6 +190,7 @@ static cudaError_t warp_backward_t(int B, int H, int W, int padding, const void*
                                    void* d_ref, void* ws, cudaStream_t st) {
   const size_t plane = (size_t)H * W;
   const unsigned nblk = (unsigned)((plane + kOpThreads - 1) / kOpThreads);
+  count_launches(2);
   warp_bwd_kernel<real, img_t><<<dim3(nblk, B), kOpThreads, 0, st>>>(
       H, W, padding, (const img_t*)ref, (const real*)depth, (const real*)K, (const real*)refK, (const real*)pose,
       (const real*)gout, (real*)d_depth, (real*)ws, (real*)d_ref);
@@ -210,6 +213,7 @@ cudaError_t warp_backward_dispatch(int B, int H, int W, int img_dtype, int real_
 cudaError_t resize_dispatch(int N, int Hi, int Wi, int Ho, int Wo, int dtype, int mode, const void* in, void* out,
                             cudaStream_t st) {
   dim3 grid((unsigned)(((size_t)Ho * Wo + kOpThreads - 1) / kOpThreads), N);
+  count_launches(1);
   if (dtype == PSFM_F64)
     resize_kernel<double, double><<<grid, kOpThreads, 0, st>>>(Hi, Wi, Ho, Wo, mode, (const double*)in, (double*)out);
   else if (dtype == PSFM_BF16)
@@ -224,6 +228,7 @@ cudaError_t scale_dispatch(void* x, const void* scale, size_t count, int real_dt
   if (count == 0) return cudaSuccess;
   size_t nb = (count + kOpThreads - 1) / kOpThreads;
   if (nb > 148 * 8) nb = 148 * 8;
+  count_launches(1);
   if (real_dtype == PSFM_F64)
     scale_kernel<double><<<(unsigned)nb, kOpThreads, 0, st>>>((double*)x, (const double*)scale, count);
   else

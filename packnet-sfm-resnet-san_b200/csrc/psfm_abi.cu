@@ -7,6 +7,10 @@
 #include <cstdio>
 #include <cstring>
 #include "../../include/psfm.h"
+#include "profile.h"
+#include <atomic>
+#include <mutex>
+#include <vector>
 
 namespace psfm {
 size_t loss_workspace_bytes(const psfm_loss_cfg* cfg);
@@ -23,6 +27,35 @@ cudaError_t scale_dispatch(void*, const void*, size_t, int, cudaStream_t);
 }  // namespace psfm
 
 static thread_local char g_err[512] = "";
+
+// ---- launch accounting / optional event timing ---------------------------------------------
+namespace psfm {
+static std::atomic<unsigned long long> g_launches{0};
+static std::atomic<int> g_prof_on{0};
+static std::mutex g_prof_mu;
+struct ProfRec { cudaEvent_t a, b; int tag; };
+static std::vector<ProfRec> g_prof;
+
+void count_launches(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
+
+ProfScope::ProfScope(cudaStream_t st, int tag, int launches) : st_(st), slot_(-1) {
+  count_launches(launches);
+  if (!g_prof_on.load(std::memory_order_relaxed)) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  if (g_prof.size() >= 65536) return;
+  ProfRec r;
+  r.tag = tag;
+  if (cudaEventCreate(&r.a) != cudaSuccess || cudaEventCreate(&r.b) != cudaSuccess) return;
+  cudaEventRecord(r.a, st);
+  slot_ = (int)g_prof.size();
+  g_prof.push_back(r);
+}
+ProfScope::~ProfScope() {
+  if (slot_ < 0) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  cudaEventRecord(g_prof[slot_].b, st_);
+}
+}  // namespace psfm
 
 static int fail(int code, const char* fmt, ...) {
   va_list ap;
@@ -82,6 +115,28 @@ static int check_io(const psfm_loss_cfg* c, const psfm_loss_io* io, bool need_gr
 extern "C" {
 
 int psfm_abi_version(void) { return PSFM_ABI_VERSION; }
+
+unsigned long long psfm_launch_count(void) { return psfm::g_launches.load(); }
+
+int psfm_profile_enable(int on) {
+  psfm::g_prof_on.store(on ? 1 : 0);
+  return PSFM_OK;
+}
+
+int psfm_profile_read(float* ms, int* tags, int max_records) {
+  std::lock_guard<std::mutex> lk(psfm::g_prof_mu);
+  int n = 0;
+  for (auto& r : psfm::g_prof) {
+    cudaEventSynchronize(r.b);
+    float t = 0.f;
+    cudaEventElapsedTime(&t, r.a, r.b);
+    if (n < max_records && ms && tags) { ms[n] = t; tags[n] = r.tag; ++n; }
+    cudaEventDestroy(r.a);
+    cudaEventDestroy(r.b);
+  }
+  psfm::g_prof.clear();
+  return n;
+}
 
 const char* psfm_last_error(void) { return g_err; }
 

@@ -17,7 +17,8 @@ F32, BF16, F64 = 0, 1, 2
 PAD = {'zeros': 0, 'border': 1}
 REDUCE = {'min': 0, 'mean': 1}
 
-EXPORTS = ('psfm_abi_version', 'psfm_last_error', 'psfm_loss_workspace_bytes', 'psfm_loss_forward',
+EXPORTS = ('psfm_abi_version', 'psfm_last_error', 'psfm_launch_count', 'psfm_profile_enable', 'psfm_profile_read',
+           'psfm_loss_workspace_bytes', 'psfm_loss_forward',
            'psfm_loss_backward', 'psfm_loss_forward_backward', 'psfm_scale_inplace', 'psfm_warp_forward',
            'psfm_warp_workspace_bytes', 'psfm_warp_backward', 'psfm_resize')
 
@@ -52,6 +53,11 @@ def _load():
     vp, sz, i = C.c_void_p, C.c_size_t, C.c_int
     lib.psfm_abi_version.restype = i
     lib.psfm_last_error.restype = C.c_char_p
+    lib.psfm_launch_count.restype = C.c_ulonglong
+    lib.psfm_profile_enable.restype = i
+    lib.psfm_profile_enable.argtypes = [i]
+    lib.psfm_profile_read.restype = i
+    lib.psfm_profile_read.argtypes = [C.POINTER(C.c_float), C.POINTER(C.c_int), i]
     lib.psfm_loss_workspace_bytes.restype = sz
     lib.psfm_loss_workspace_bytes.argtypes = [C.POINTER(LossCfg)]
     lib.psfm_loss_forward.restype = i
@@ -116,3 +122,14 @@ def stream_ptr(device):
 
 def ptr(t):
     return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+PROFILE_TAGS = {0: 'mean', 1: 'loss_fwd', 2: 'loss_bwd', 3: 'finish', 4: 'loss_fused', 5: 'other'}
+
+
+def profile_read(max_records=65536):
+    """[(tag_name, ms), ...] of the kernels bracketed since profiling was enabled (synchronises)."""
+    ms = (C.c_float * max_records)()
+    tags = (C.c_int * max_records)()
+    n = lib.psfm_profile_read(ms, tags, max_records)
+    return [(PROFILE_TAGS.get(tags[k], str(tags[k])), ms[k]) for k in range(n)]
