@@ -245,6 +245,7 @@ def run_ours(args):
             self.graph, self.loss = None, None
 
         def step(self):
+            self.loss = None            # drop the previous autograd graph (and its AccumulateGrad nodes)
             for t in self.invd + self.mats:
                 t.grad = None
             out = loss_fn(self.image, self.context, self.invd, self.K, self.K, [Pose(m) for m in self.mats])
