@@ -1,0 +1,810 @@
+// loss_sweep.cu -- single-pass photometric loss: loss AND gradients in one sweep over the inputs.
+//
+//   prep_kernel    once per resolution (shared by all full-resolution scales): window statistics of
+//                  the target image (mean, variance + C2), edge weights of the smoothness term, the
+//                  automask candidate (min / arg-min of the identity photometric terms) and the raw
+//                  per-image sums the smoothness normalisation needs.
+//   stats_kernel   per (scale, image): clamped mean, smoothness sums, gradient coupling constant.
+//   sweep_kernel   the hot kernel.  One warp = 32 adjacent columns of one (image, scale, context);
+//                  it marches down the rows with the 3-row SSIM window and its adjoint in register
+//                  rings and exchanges horizontal neighbours by shuffles, so every warped value is
+//                  gathered once and feeds the loss, d/d inv_depth and d/d pose.  The C warps of a
+//                  CTA (one per context) meet once per row to take the per-pixel min.
+//   final_kernel   fixed-order reduction of the CTA partials -> loss triple and d pose.mat.
+//
+// Semantics: SURVEY.md Appendix A (reference losses/multiview_photometric_loss.py:199-410).
+// Restrictions (other settings run on the tile kernels of loss_kernels.cu): photometric_reduce_op
+// = 'min', ssim_loss_weight > 0, clip_loss = 0.
+#include <cuda_runtime.h>
+#include <cstdlib>
+#include "sweep_device.cuh"
+#include "loss_params.h"
+#include "loss_tile.cuh"
+#include "profile.h"
+
+namespace psfm {
+
+constexpr int kPrepVals = 3;         // sum d, sum |dx d| wx, sum |dy d| wy
+constexpr int kPrepInner = 30;       // columns a prep warp produces (32 lanes - 1 halo each side)
+constexpr int kPrepWarps = 4;        // independent warps per prep CTA
+constexpr int kInner = 28;           // columns a sweep warp produces (32 lanes - 2 halo each side)
+constexpr int kRing = 10;            // per-row values parked in shared memory between forward and adjoint
+
+struct SweepSet {                    // scales of equal resolution sharing the same images
+  int ns;
+  int scale[PSFM_MAX_SCALES];
+  int H, W;
+  int nstrips, nchunks, chunk_h;     // sweep kernel decomposition
+  int pstrips, pchunks, pchunk_h;    // prep kernel decomposition
+  void* ymom;                        // real [B][6][H][W]: mean(y) x3, E[y^2]-mean(y)^2+C2 x3
+  void* wxy;                         // real [B][2][H][W]: exp(-mean|dx I|), exp(-mean|dy I|)
+  void* idval;                       // real [B][H][W] min identity photometric value (automask)
+  uint8_t* idsel;                    // u8   [B][H][W] its candidate index (2j+1)
+};
+
+struct SweepParams {
+  LossParams P;
+  SweepSet set;
+  // per scale (indexed by the scale id)
+  double* prep_part[PSFM_MAX_SCALES];   // [B][punits][kPrepVals]
+  void* stats[PSFM_MAX_SCALES];         // real [B][4]: clamped mean, coupling constant, SX, SY
+  double* loss_part[PSFM_MAX_SCALES];   // [B][nunits] photometric sums
+  void* pose_part[PSFM_MAX_SCALES];     // real [B][nunits][C][12]
+};
+
+// ------------------------------------------------------------------------------------------
+// prep kernel: grid (ceil(punits / kPrepWarps), B), 32 * kPrepWarps threads; every warp is an
+// independent (strip, chunk) unit.  Lane l is column c0 - 1 + l; step t loads row t and finishes
+// row p = t - 1.  Pass j handles context j (pass 0 also the image-only outputs).
+// ------------------------------------------------------------------------------------------
+template <typename real, typename img_t>
+__global__ void __launch_bounds__(32 * kPrepWarps) prep_kernel(const SweepParams SP) {
+  const LossParams& P = SP.P;
+  const SweepSet& S = SP.set;
+  const int lane = threadIdx.x & 31;
+  const int unit = blockIdx.x * kPrepWarps + (threadIdx.x >> 5);
+  const int punits = S.pstrips * S.pchunks;
+  if (unit >= punits) return;
+  const int strip = unit % S.pstrips, chunk = unit / S.pstrips;
+  const int H = S.H, W = S.W, b = blockIdx.y;
+  const int plane = H * W;
+  const int u = strip * kPrepInner - 1 + lane, su = reflect1(u, W);
+  const int r0 = chunk * S.pchunk_h, r1 = min(r0 + S.pchunk_h, H);
+  const bool inner = (lane >= 1) && (lane <= kPrepInner) && (u < W);
+  const ScaleDesc& S0 = P.sc[S.scale[0]];
+  const img_t* image = (const img_t*)S0.image + (size_t)b * 3 * plane;
+  real* ymom = (real*)S.ymom + (size_t)b * 6 * plane;
+  real* wxy = (real*)S.wxy + (size_t)b * 2 * plane;
+  real* idval = (real*)S.idval + (size_t)b * plane;
+  uint8_t* idsel = S.idsel + (size_t)b * plane;
+  const real ssim_w = (real)P.ssim_w, C1 = (real)P.C1, C2 = (real)P.C2;
+  const real r3 = real(1) / real(3), r9 = real(1) / real(9);
+  const bool smooth = P.smooth_w > 0.0;
+  const int npass = P.automask ? P.C : 1;
+
+  real sums[PSFM_MAX_SCALES][kPrepVals];
+#pragma unroll
+  for (int k = 0; k < PSFM_MAX_SCALES; ++k)
+#pragma unroll
+    for (int i = 0; i < kPrepVals; ++i) sums[k][i] = real(0);
+
+  for (int j = 0; j < npass; ++j) {
+    const img_t* ctx = (const img_t*)S0.ctx[j] + (size_t)b * 3 * plane;
+    real hy[2][6], hx[2][9];            // horizontal sums of the two previous rows
+    real yp[3], ycp[3], xp[3];          // previous row: y, right neighbour of y, x
+    real dp[PSFM_MAX_SCALES];           // previous row of the raw inverse depths
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+#pragma unroll
+      for (int k = 0; k < 6; ++k) hy[a][k] = real(0);
+#pragma unroll
+      for (int k = 0; k < 9; ++k) hx[a][k] = real(0);
+    }
+#pragma unroll
+    for (int c = 0; c < 3; ++c) { yp[c] = real(0); ycp[c] = real(0); xp[c] = real(0); }
+#pragma unroll
+    for (int k = 0; k < PSFM_MAX_SCALES; ++k) dp[k] = real(0);
+
+    for (int t = r0 - 1; t <= r1; ++t) {
+      const int p = t - 1;
+      const int o = reflect1(t, H) * W + su;
+      real y[3], ya[3], yc[3], hyn[6];
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        y[c] = ldimg<real>(image + (size_t)c * plane, o);
+        ya[c] = shfl_up1(y[c]);
+        yc[c] = shfl_dn1(y[c]);
+        hyn[c] = ya[c] + y[c] + yc[c];
+        hyn[3 + c] = ya[c] * ya[c] + y[c] * y[c] + yc[c] * yc[c];
+      }
+      real x[3] = {real(0), real(0), real(0)}, hxn[9];
+      if (P.automask) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          x[c] = ldimg<real>(ctx + (size_t)c * plane, o);
+          const real z = x[c] * y[c];
+          const real xa = shfl_up1(x[c]), xc = shfl_dn1(x[c]);
+          const real za = shfl_up1(z), zc = shfl_dn1(z);
+          hxn[c * 3 + 0] = xa + x[c] + xc;
+          hxn[c * 3 + 1] = xa * xa + x[c] * x[c] + xc * xc;
+          hxn[c * 3 + 2] = za + z + zc;
+        }
+      }
+      const bool emit = inner && p >= r0 && p < r1;
+      const int op = p * W + u;
+      real wx = real(0), wy = real(0);
+      if (emit) {
+        real my[3], qy[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          my[c] = (hy[0][c] + hy[1][c] + hyn[c]) * r9;
+          qy[c] = ((hy[0][3 + c] + hy[1][3 + c] + hyn[3 + c]) * r9 - my[c] * my[c]) + C2;
+        }
+        if (j == 0) {
+#pragma unroll
+          for (int c = 0; c < 3; ++c) {
+            ymom[(size_t)c * plane + op] = my[c];
+            ymom[(size_t)(3 + c) * plane + op] = qy[c];
+          }
+        }
+        if (P.automask) {
+          real ds = real(0), ls = real(0);
+#pragma unroll
+          for (int c = 0; c < 3; ++c) {
+            ds += ssim_dist_sums<real, false>(hx[0][c * 3] + hx[1][c * 3] + hxn[c * 3],
+                                              hx[0][c * 3 + 1] + hx[1][c * 3 + 1] + hxn[c * 3 + 1],
+                                              hx[0][c * 3 + 2] + hx[1][c * 3 + 2] + hxn[c * 3 + 2], my[c], qy[c], C1,
+                                              C2, nullptr);
+            ls += rabs(xp[c] - yp[c]);
+          }
+          const real val = ssim_w * (ds * r3) + (real(1) - ssim_w) * (ls * r3);
+          if (j == 0 || val < idval[op]) { idval[op] = val; idsel[op] = (uint8_t)(2 * j + 1); }
+        }
+        if (j == 0 && smooth) {
+          if (u + 1 < W) wx = rexp(-((rabs(yp[0] - ycp[0]) + rabs(yp[1] - ycp[1]) + rabs(yp[2] - ycp[2])) * r3));
+          if (p + 1 < H) wy = rexp(-((rabs(yp[0] - y[0]) + rabs(yp[1] - y[1]) + rabs(yp[2] - y[2])) * r3));
+          wxy[op] = wx;
+          wxy[(size_t)plane + op] = wy;
+        }
+      }
+      if (j == 0 && smooth) {
+        // raw smoothness sums of row p for every scale of the set (all lanes take part in the
+        // right-neighbour shuffle)
+#pragma unroll
+        for (int k = 0; k < PSFM_MAX_SCALES; ++k) {
+          if (k < S.ns) {
+            const real* invd = (const real*)P.sc[S.scale[k]].invd + (size_t)b * plane;
+            const real dt = invd[o];
+            const real dr = shfl_dn1(dp[k]);
+            if (emit) {
+              sums[k][0] += dp[k];
+              if (u + 1 < W) sums[k][1] += rabs(dp[k] - dr) * wx;
+              if (p + 1 < H) sums[k][2] += rabs(dp[k] - dt) * wy;
+            }
+            dp[k] = dt;
+          }
+        }
+      }
+      // rotate the rings
+#pragma unroll
+      for (int k = 0; k < 6; ++k) { hy[0][k] = hy[1][k]; hy[1][k] = hyn[k]; }
+      if (P.automask) {
+#pragma unroll
+        for (int k = 0; k < 9; ++k) { hx[0][k] = hx[1][k]; hx[1][k] = hxn[k]; }
+      }
+#pragma unroll
+      for (int c = 0; c < 3; ++c) { yp[c] = y[c]; ycp[c] = yc[c]; xp[c] = x[c]; }
+    }
+  }
+  if (smooth) {
+#pragma unroll
+    for (int k = 0; k < PSFM_MAX_SCALES; ++k) {
+      if (k < S.ns) {
+#pragma unroll
+        for (int i = 0; i < kPrepVals; ++i) {
+          const real v = warp_allsum<real>(sums[k][i]);
+          if (lane == 0) SP.prep_part[S.scale[k]][((size_t)b * punits + unit) * kPrepVals + i] = (double)v;
+        }
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// stats kernel: grid (B, ns), 128 threads.  stats[s][b] = {m', c, SX, SY}:
+//   m' = max(mean d, 1e-6);  SX = sum|gx wx| = raw_x / m', SY likewise (utils/depth.py:146-198);
+//   c  = (coef_x SX + coef_y SY) / (N m') when mean >= 1e-6 (gradient through the mean), else 0.
+// ------------------------------------------------------------------------------------------
+template <typename real>
+__global__ void __launch_bounds__(128) stats_kernel(const SweepParams SP) {
+  const LossParams& P = SP.P;
+  const SweepSet& S = SP.set;
+  const int b = blockIdx.x, s = S.scale[blockIdx.y];
+  const int punits = S.pstrips * S.pchunks;
+  __shared__ double sh[3][128];
+  double a[3] = {0.0, 0.0, 0.0};
+  const double* base = SP.prep_part[s] + (size_t)b * punits * kPrepVals;
+  for (int i = threadIdx.x; i < punits; i += blockDim.x)
+    for (int k = 0; k < 3; ++k) a[k] += base[(size_t)i * kPrepVals + k];
+  for (int k = 0; k < 3; ++k) sh[k][threadIdx.x] = a[k];
+  __syncthreads();
+  for (int o = 64; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o)
+      for (int k = 0; k < 3; ++k) sh[k][threadIdx.x] += sh[k][threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const double N = (double)S.H * S.W;
+    const real mean = (real)(sh[0][0] / N);
+    const real m = rmax(mean, real(1e-6));
+    const real sx = (real)sh[1][0] / m, sy = (real)sh[2][0] / m;
+    real* o = (real*)SP.stats[s] + (size_t)b * 4;
+    o[0] = m;
+    o[1] = (mean >= real(1e-6)) ? ((real)P.sc[s].coef_x * sx + (real)P.sc[s].coef_y * sy) / ((real)N * m) : real(0);
+    o[2] = sx;
+    o[3] = sy;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// sweep kernel: grid (nstrips * nchunks, ns, B), 32 * C threads (warp j = context j).
+// Lane l is column c0 - 2 + l (2 halo columns per side: SSIM needs +-1, its adjoint +-1 more).
+// Step t gathers row t, evaluates SSIM / the candidate min at row p = t - 1 and the adjoint
+// (d/d inv_depth, d/d pose) at row q = t - 2.
+// ------------------------------------------------------------------------------------------
+template <typename real> struct SweepCam {
+  real ki[9];   // reference `Kinv` (camera.py:73-81)
+  real rk[9];   // scaled ref_K
+  real T[12];   // rows of the 3x4 [R|t] (pose.py:80-86)
+};
+
+template <typename real>
+__device__ __forceinline__ void sweep_cam(SweepCam<real>& c, const LossParams& P, int b, int j, real sf) {
+  CamPair<real> cp;
+  setup_cam<real>(cp, (const real*)P.K, (const real*)P.refK, b, sf);
+#pragma unroll
+  for (int i = 0; i < 9; ++i) { c.ki[i] = cp.ki[i]; c.rk[i] = cp.rk[i]; }
+  const real* T = (const real*)P.pose[j] + (size_t)b * 16;
+#pragma unroll
+  for (int i = 0; i < 12; ++i) c.T[i] = T[i];
+}
+
+template <int V> struct IntC { static constexpr int value = V; };
+
+template <typename real, typename img_t, int PAD, bool RARE>
+__global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const LossParams& P = SP.P;
+  const SweepSet& S = SP.set;
+  const int C = P.C;
+  const int lane = threadIdx.x & 31, j = threadIdx.x >> 5;
+  const int unit = blockIdx.x, nunits = gridDim.x;
+  const int strip = unit % S.nstrips, chunk = unit / S.nstrips;
+  const int si = blockIdx.y, s = S.scale[si], b = blockIdx.z;
+  const int H = S.H, W = S.W, plane = H * W;
+  const int u = strip * kInner - 2 + lane, su = reflect1(u, W);
+  const bool col_real = (u >= 0) && (u < W);
+  const bool col_inner = (lane >= 2) && (lane < 30) && col_real;
+  const int r0 = chunk * S.chunk_h, r1 = min(r0 + S.chunk_h, H);
+
+  real* ring = (real*)smem_raw + (size_t)j * 3 * kRing * 32 + lane;        // [slot][kRing][32]
+  real* photo_s = (real*)smem_raw + (size_t)C * 3 * kRing * 32;            // [2][C][32]
+  real* dpart_s = photo_s + 2 * C * 32;                                    // [2][C][32]
+
+  const ScaleDesc& SD = P.sc[s];
+  const img_t* image = (const img_t*)SD.image + (size_t)b * 3 * plane;
+  const img_t* ctx = (const img_t*)SD.ctx[j] + (size_t)b * 3 * plane;
+  const real* invd = (const real*)SD.invd + (size_t)b * plane;
+  const real* ymom = (const real*)S.ymom + (size_t)b * 6 * plane;
+  const real* wxy = (const real*)S.wxy + (size_t)b * 2 * plane;
+  const real* idval = (const real*)S.idval + (size_t)b * plane;
+  const uint8_t* idsel = S.idsel + (size_t)b * plane;
+  const img_t* maskp = (RARE && SD.mask) ? (const img_t*)SD.mask + (size_t)b * plane : nullptr;
+  const bool premap = RARE && P.premap;
+  const bool smooth = P.smooth_w > 0.0;
+
+  // ---- per-thread geometry constants: p = (A0 + A1 v) D + m with A = ref_K R Kinv (u, v, 1) ---------
+  real A0[3], A1[3], mt[3];
+  {
+    SweepCam<real> cam;
+    sweep_cam<real>(cam, P, b, j, (real)SD.sf);
+    real M[9];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+        M[i * 3 + c] = cam.rk[i * 3] * cam.T[c] + cam.rk[i * 3 + 1] * cam.T[4 + c] + cam.rk[i * 3 + 2] * cam.T[8 + c];
+      mt[i] = cam.rk[i * 3] * cam.T[3] + cam.rk[i * 3 + 1] * cam.T[7] + cam.rk[i * 3 + 2] * cam.T[11];
+    }
+    const real fu = (real)su;
+    const real b0 = cam.ki[0] * fu + cam.ki[2], b1 = cam.ki[3] * fu + cam.ki[5], b2 = cam.ki[6] * fu + cam.ki[8];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      A0[i] = M[i * 3] * b0 + M[i * 3 + 1] * b1 + M[i * 3 + 2] * b2;
+      A1[i] = M[i * 3] * cam.ki[1] + M[i * 3 + 1] * cam.ki[4] + M[i * 3 + 2] * cam.ki[7];
+    }
+  }
+  const real ssim_w = (real)P.ssim_w, C1 = (real)P.C1, C2 = (real)P.C2;
+  const real r3 = real(1) / real(3);
+  const real k1 = (real(1) - ssim_w) * r3;
+  const real inv_count = (real)SD.inv_count;
+  const real mu0 = (u == 1) ? real(2) : real(1), mu2 = (u == W - 2) ? real(2) : real(1);
+  const int mycand = P.automask ? 2 * j : j;
+  real inv_m = real(1), cb = real(0);
+  if (smooth) {
+    const real* st = (const real*)SP.stats[s] + (size_t)b * 4;
+    inv_m = real(1) / st[0];
+    cb = st[1];
+  }
+  const real coef_x = (real)SD.coef_x, coef_y = (real)SD.coef_y;
+
+  real h[3][9], hF[3][9], xr[3][3], yr[3][3];
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+#pragma unroll
+    for (int k = 0; k < 9; ++k) { h[a][k] = real(0); hF[a][k] = real(0); }
+#pragma unroll
+    for (int c = 0; c < 3; ++c) { xr[a][c] = real(0); yr[a][c] = real(0); }
+  }
+#pragma unroll
+  for (int k = 0; k < 3 * kRing; ++k) ring[k * 32] = real(0);
+  real S0a[3] = {real(0), real(0), real(0)}, Sva[3] = {real(0), real(0), real(0)}, S1a[3] = {real(0), real(0), real(0)};
+  real loss_acc = real(0), w_cur = real(0), w_old = real(0);
+  real d0 = real(0), d1 = real(0), d2 = real(0), d3 = real(0);   // raw inverse depths of rows t, t-1, t-2, t-3
+  real dsum_prev = real(0);
+  int prev_q = -1;
+  real* d_out = (real*)SD.d_invd + (size_t)b * plane;
+
+  auto finalize_row = [&](int par) {      // context 0 adds the other contexts' parts and stores the row
+    if (j == 0 && prev_q >= 0) {
+      real tot = dsum_prev;
+      for (int jj = 1; jj < C; ++jj) tot += dpart_s[(par * C + jj) * 32 + lane];
+      d_out[prev_q * W + u] = tot;
+    }
+    prev_q = -1;
+  };
+
+  auto step = [&](const int t, auto phc) {
+    constexpr int PH = decltype(phc)::value, Q = (PH + 1) % 3, P1 = (PH + 2) % 3;
+    const int p = t - 1, q = t - 2;
+    const int par = t & 1;
+    // ---------------- gather row t -----------------------------------------------------------------
+    {
+      const int sv = reflect1(t, H);
+      const int o = sv * W + su;
+      d3 = d2; d2 = d1; d1 = d0;
+      d0 = invd[o];
+      real dd = d0;
+      if (premap) { real ch; dd = premap_fork<real>(d0, (real)P.premap_lo, (real)P.premap_hi, ch); }
+      const real D = rrcp(rmax(dd, real(1e-6)));                    // utils/depth.py:120
+      const real fv = (real)sv;
+      const real p0 = (A0[0] + A1[0] * fv) * D + mt[0];
+      const real p1 = (A0[1] + A1[1] * fv) * D + mt[1];
+      const real p2 = (A0[2] + A1[2] * fv) * D + mt[2];
+      const real iz = rrcp(rmax(p2, real(1e-5)));                   // camera.py:179
+      const real ix = p0 * iz, iy = p1 * iz;
+      real x[3], gx[3], gy[3];
+      sample3<real, img_t, PAD>(ctx, plane, H, W, ix, iy, x, gx, gy);
+      real* rs = ring + PH * kRing * 32;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) { rs[c * 32] = gx[c]; rs[(3 + c) * 32] = gy[c]; }
+      rs[6 * 32] = D;
+      rs[7 * 32] = (p2 >= real(1e-5)) ? iz : -iz;                   // sign flags the clamp
+      rs[8 * 32] = ix;
+      rs[9 * 32] = iy;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const real y = ldimg<real>(image + (size_t)c * plane, o);
+        const real z = x[c] * y;
+        xr[PH][c] = x[c];
+        yr[PH][c] = y;
+        const real xa = shfl_up1(x[c]), xc = shfl_dn1(x[c]);
+        const real za = shfl_up1(z), zc = shfl_dn1(z);
+        h[PH][c * 3 + 0] = xa + x[c] + xc;
+        h[PH][c * 3 + 1] = xa * xa + x[c] * x[c] + xc * xc;
+        h[PH][c * 3 + 2] = za + z + zc;
+      }
+    }
+    // ---------------- SSIM + L1 at row p, candidate min across the contexts --------------------------
+    const bool p_real = (p >= 0) && (p < H) && col_real;
+    real coef[9];
+    real F[9];
+    {
+      const int op = min(max(p, 0), H - 1) * W + su;
+      real ds = real(0), ls = real(0);
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const real my = ymom[(size_t)c * plane + op], qy = ymom[(size_t)(3 + c) * plane + op];
+        ds += ssim_dist_sums<real, true>(h[0][c * 3] + h[1][c * 3] + h[2][c * 3],
+                                         h[0][c * 3 + 1] + h[1][c * 3 + 1] + h[2][c * 3 + 1],
+                                         h[0][c * 3 + 2] + h[1][c * 3 + 2] + h[2][c * 3 + 2], my, qy, C1, C2,
+                                         &coef[c * 3]);
+        ls += rabs(xr[P1][c] - yr[P1][c]);
+      }
+      const real photo = ssim_w * (ds * r3) + k1 * ls;
+      real m = real(1);
+      if (RARE && maskp) m = p_real ? ldimg<real>(maskp, (size_t)p * W + u) : real(0);
+      real best = photo * m;
+      int sel = mycand;
+      if (C > 1) {
+        photo_s[(par * C + j) * 32 + lane] = photo;
+        __syncthreads();
+        best = real_inf<real>();
+        sel = 0;
+        for (int jj = 0; jj < C; ++jj) {
+          const real v = photo_s[(par * C + jj) * 32 + lane] * m;
+          if (v < best) { best = v; sel = P.automask ? 2 * jj : jj; }
+        }
+      }
+      if (P.automask && p_real) {
+        const real vi = idval[p * W + u] * m;
+        const int ki = (int)idsel[p * W + u];
+        if (vi < best || (vi == best && ki < sel)) { best = vi; sel = ki; }
+      }
+      w_old = w_cur;
+      w_cur = (p_real && sel == mycand) ? inv_count * m : real(0);
+      if (j == 0 && p_real && col_inner && p >= r0 && p < r1) loss_acc += best;
+      const real wf = w_cur * ssim_w * r3;
+#pragma unroll
+      for (int k = 0; k < 9; ++k) F[k] = (w_cur != real(0)) ? wf * coef[k] : real(0);
+    }
+    finalize_row(par ^ 1);
+    // ---------------- adjoint at row q ----------------------------------------------------------------
+    {
+#pragma unroll
+      for (int k = 0; k < 9; ++k) {
+        const real Fa = shfl_up1(F[k]), Fc = shfl_dn1(F[k]);
+        hF[P1][k] = mu0 * Fa + F[k] + mu2 * Fc;
+      }
+      const bool q_ok = (q >= r0) && (q < r1) && col_inner;
+      const real mv0 = (q == 1) ? real(2) : real(1), mv2 = (q == H - 2) ? real(2) : real(1);
+      const real* rq = ring + Q * kRing * 32;
+      real gix = real(0), giy = real(0);
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const real sa = mv0 * hF[PH][c * 3 + 0] + hF[Q][c * 3 + 0] + mv2 * hF[P1][c * 3 + 0];
+        const real sb = mv0 * hF[PH][c * 3 + 1] + hF[Q][c * 3 + 1] + mv2 * hF[P1][c * 3 + 1];
+        const real sc = mv0 * hF[PH][c * 3 + 2] + hF[Q][c * 3 + 2] + mv2 * hF[P1][c * 3 + 2];
+        const real xq = xr[Q][c], yq = yr[Q][c];
+        const real dl = sa + xq * sb + yq * sc + (w_old * k1) * rsign(xq - yq);
+        gix += dl * rq[c * 32];
+        giy += dl * rq[(3 + c) * 32];
+      }
+      gix = q_ok ? gix : real(0);
+      giy = q_ok ? giy : real(0);
+      const real D = rq[6 * 32], izs = rq[7 * 32], ixq = rq[8 * 32], iyq = rq[9 * 32];
+      const real iz = rabs(izs);
+      const real dp0 = gix * iz, dp1 = giy * iz;
+      const real dp2 = (izs > real(0)) ? -(dp0 * ixq + dp1 * iyq) : real(0);
+      const real fq = (real)q;
+      const real dD = (A0[0] + A1[0] * fq) * dp0 + (A0[1] + A1[1] * fq) * dp1 + (A0[2] + A1[2] * fq) * dp2;
+      real chain = real(1), dd = d2;
+      if (premap) dd = premap_fork<real>(d2, (real)P.premap_lo, (real)P.premap_hi, chain);
+      const real dphoto = (q_ok && dd >= real(1e-6)) ? -(D * D) * dD * chain : real(0);
+      {
+        const real e0 = dp0 * D, e1 = dp1 * D, e2 = dp2 * D;
+        S0a[0] += e0; S0a[1] += e1; S0a[2] += e2;
+        Sva[0] += e0 * fq; Sva[1] += e1 * fq; Sva[2] += e2 * fq;
+        S1a[0] += dp0; S1a[1] += dp1; S1a[2] += dp2;
+      }
+      if (j == 0) {
+        real gs = real(0);
+        if (smooth) {
+          const real dl = shfl_up1(d2), dr = shfl_dn1(d2);
+          const int qc = min(max(q, 0), H - 1);
+          const real wxq = wxy[qc * W + su];
+          const real wyq = wxy[(size_t)plane + qc * W + su];
+          const real wym = wxy[(size_t)plane + max(qc - 1, 0) * W + su];
+          const real wxl = shfl_up1(wxq);
+          real qq = real(0);
+          if (u + 1 < W) qq += coef_x * rsign(d2 - dr) * wxq;
+          if (u >= 1) qq -= coef_x * rsign(dl - d2) * wxl;
+          if (q + 1 < H) qq += coef_y * rsign(d2 - d1) * wyq;
+          if (q >= 1) qq -= coef_y * rsign(d3 - d2) * wym;
+          gs = qq * inv_m - cb;
+        }
+        if (q_ok) {
+          if (C > 1) { dsum_prev = dphoto + gs; prev_q = q; }
+          else d_out[q * W + u] = dphoto + gs;
+        }
+      } else {
+        dpart_s[(par * C + j) * 32 + lane] = dphoto;
+      }
+    }
+  };
+
+  const int t0 = r0 - 2;
+  for (int tb = t0; tb <= r1 + 1; tb += 3) {
+    step(tb, IntC<0>());
+    step(tb + 1, IntC<1>());
+    step(tb + 2, IntC<2>());
+  }
+  if (C > 1) {
+    __syncthreads();
+    // the loop ran ceil((chunk_h + 4) / 3) * 3 steps; the last one had parity of (last t)
+    const int last_t = t0 + ((r1 + 1 - t0) / 3) * 3 + 2;
+    finalize_row(last_t & 1);
+  }
+
+  // ---- epilogue: pose partials (converted from the (u, v, 1) basis) and the loss partial -----------
+  {
+    SweepCam<real> cam;
+    sweep_cam<real>(cam, P, b, j, (real)SD.sf);
+    const real fu = (real)su;
+    real G[12];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const real eu = fu * S0a[i], ev = Sva[i], e1 = S0a[i];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) G[i * 4 + k] = cam.ki[k * 3] * eu + cam.ki[k * 3 + 1] * ev + cam.ki[k * 3 + 2] * e1;
+      G[i * 4 + 3] = S1a[i];
+    }
+#pragma unroll
+    for (int e = 0; e < 12; ++e) G[e] = warp_allsum<real>(G[e]);
+    // d loss / d [R|t] = ref_K^T G
+    real out = real(0);
+#pragma unroll
+    for (int e = 0; e < 12; ++e) {
+      const int i = e / 4, k = e % 4;
+      const real v = cam.rk[i] * G[k] + cam.rk[3 + i] * G[4 + k] + cam.rk[6 + i] * G[8 + k];
+      if (lane == e) out = v;
+    }
+    if (lane < 12) ((real*)SP.pose_part[s])[(((size_t)b * nunits + unit) * C + j) * 12 + lane] = out;
+    const real lsum = warp_allsum<real>(loss_acc);
+    if (j == 0 && lane == 0) SP.loss_part[s][(size_t)b * nunits + unit] = (double)lsum;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// final kernel: block 0 -> loss triple; block 1 + b * C + j -> d pose[j].mat[b].
+// Works over all sets (called once, after every set's sweep kernel).
+// ------------------------------------------------------------------------------------------
+struct FinalParams {
+  int B, C, n;
+  int nunits[PSFM_MAX_SCALES];
+  double inv_count[PSFM_MAX_SCALES], coef_x[PSFM_MAX_SCALES], coef_y[PSFM_MAX_SCALES];
+  const double* loss_part[PSFM_MAX_SCALES];
+  const void* pose_part[PSFM_MAX_SCALES];
+  const void* stats[PSFM_MAX_SCALES];
+  void* d_pose[PSFM_MAX_CTX];
+  void* loss_out;
+  void* one;
+  int smooth;
+};
+
+template <typename real>
+__global__ void __launch_bounds__(256) final_kernel(const FinalParams F) {
+  __shared__ double sh[256];
+  const int tid = threadIdx.x;
+  if (blockIdx.x == 0) {
+    double photo = 0.0, smooth = 0.0;
+    for (int s = 0; s < F.n; ++s) {
+      double a = 0.0;
+      const size_t cnt = (size_t)F.B * F.nunits[s];
+      for (size_t i = tid; i < cnt; i += blockDim.x) a += F.loss_part[s][i];
+      sh[tid] = a;
+      __syncthreads();
+      for (int o = 128; o > 0; o >>= 1) {
+        if (tid < o) sh[tid] += sh[tid + o];
+        __syncthreads();
+      }
+      photo += sh[0] * F.inv_count[s];
+      __syncthreads();
+      if (F.smooth && tid == 0)
+        for (int b = 0; b < F.B; ++b) {
+          const real* st = (const real*)F.stats[s] + (size_t)b * 4;
+          smooth += (double)st[2] * F.coef_x[s] + (double)st[3] * F.coef_y[s];
+        }
+    }
+    if (tid == 0) {
+      real* out = (real*)F.loss_out;
+      out[0] = (real)((real)photo + (real)smooth);
+      out[1] = (real)photo;
+      out[2] = (real)smooth;
+      *(real*)F.one = real(1);
+    }
+    return;
+  }
+  const int bj = blockIdx.x - 1, b = bj / F.C, j = bj - b * F.C;
+  // 12 entries x 21 partial lanes, fixed order: lane k of entry e sums units k, k+21, ...
+  const int e = tid % 12, k = tid / 12;      // 252 active threads
+  double a = 0.0;
+  if (tid < 252) {
+    for (int s = 0; s < F.n; ++s) {
+      const real* base = (const real*)F.pose_part[s] + (((size_t)b * F.nunits[s]) * F.C + j) * 12 + e;
+      for (int i = k; i < F.nunits[s]; i += 21) a += (double)base[(size_t)i * F.C * 12];
+    }
+  }
+  sh[tid] = a;
+  __syncthreads();
+  if (tid < 12) {
+    double v = 0.0;
+    for (int kk = 0; kk < 21; ++kk) v += sh[kk * 12 + tid];
+    ((real*)F.d_pose[j])[(size_t)b * 16 + (tid / 4) * 4 + (tid % 4)] = (real)v;
+  } else if (tid < 16) {
+    ((real*)F.d_pose[j])[(size_t)b * 16 + tid] = real(0);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+static inline size_t al(size_t x) { return (x + 255) / 256 * 256; }
+static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+constexpr int kMinChunk = 16;        // smallest row chunk of either kernel (bounds the partial buffers)
+
+bool stream_eligible(const psfm_loss_cfg* cfg) {
+  if (cfg->reduce_op != PSFM_REDUCE_MIN || !(cfg->ssim_w > 0.0) || cfg->clip_loss > 0.0) return false;
+  if (cfg->C > 8) return false;
+  for (int s = 0; s < cfg->n; ++s)
+    if (cfg->Hs[s] < 4 || cfg->Ws[s] < 4) return false;
+  return true;
+}
+
+struct SweepPlan {
+  int nsets;
+  SweepSet sets[PSFM_MAX_SCALES];
+  size_t off_ymom[PSFM_MAX_SCALES], off_wxy[PSFM_MAX_SCALES], off_idval[PSFM_MAX_SCALES],
+      off_idsel[PSFM_MAX_SCALES];                                         // per scale (a set uses its first scale's)
+  size_t off_prep[PSFM_MAX_SCALES], off_stats[PSFM_MAX_SCALES], off_loss[PSFM_MAX_SCALES],
+      off_pose[PSFM_MAX_SCALES];                                          // per scale
+  int nunits[PSFM_MAX_SCALES];
+  size_t off_one, total;
+};
+
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+
+// rows per unit: the largest chunk that still yields `want` warps (each chunk pays `extra` warm-up rows)
+static int pick_chunk(int H, long warps_per_chunk_row, long want) {
+  static const int cand[] = {1 << 30, 256, 192, 128, 96, 64, 48, 32, 24, kMinChunk};
+  int best = kMinChunk;
+  for (int c : cand) {
+    const int ch = c < H ? c : H;
+    best = ch;
+    if ((long)cdiv(H, ch) * warps_per_chunk_row >= want) break;
+  }
+  return best < kMinChunk ? (H < kMinChunk ? H : kMinChunk) : best;
+}
+
+static void make_plan(const psfm_loss_cfg* cfg, const psfm_loss_io* io, SweepPlan& pl) {
+  const size_t rs = cfg->real_dtype == PSFM_F64 ? 8 : 4;
+  pl.nsets = 0;
+  bool used[PSFM_MAX_SCALES] = {false, false, false, false};
+  for (int s = 0; s < cfg->n; ++s) {
+    if (used[s]) continue;
+    SweepSet& S = pl.sets[pl.nsets++];
+    S.ns = 0; S.H = cfg->Hs[s]; S.W = cfg->Ws[s];
+    for (int k = s; k < cfg->n; ++k) {
+      if (used[k] || cfg->Hs[k] != S.H || cfg->Ws[k] != S.W) continue;
+      if (io && (io->image[k] != io->image[s] || io->mask[k] != io->mask[s])) continue;
+      bool same = true;
+      if (io) for (int j = 0; j < cfg->C; ++j) same = same && io->ctx[k][j] == io->ctx[s][j];
+      if (!same) continue;
+      S.scale[S.ns++] = k;
+      used[k] = true;
+    }
+    S.nstrips = cdiv(S.W, kInner);
+    const int forced = env_int("PSFM_SWEEP_CHUNK", 0);
+    S.chunk_h = forced > 0 ? (forced < S.H ? forced : S.H)
+                           : pick_chunk(S.H, (long)S.nstrips * S.ns * cfg->B * cfg->C, 148L * 16 * 5 / 2);
+    if (S.chunk_h < kMinChunk) S.chunk_h = S.H < kMinChunk ? S.H : kMinChunk;
+    S.nchunks = cdiv(S.H, S.chunk_h);
+    S.pstrips = cdiv(S.W, kPrepInner);
+    S.pchunk_h = pick_chunk(S.H, (long)S.pstrips * cfg->B, 148L * 16);
+    S.pchunks = cdiv(S.H, S.pchunk_h);
+  }
+  // workspace layout does not depend on the grouping: every scale owns worst-case sized regions
+  size_t off = 0;
+  pl.off_one = off; off = al(off + rs);
+  for (int s = 0; s < cfg->n; ++s) {
+    const int Hs = cfg->Hs[s], Ws = cfg->Ws[s];
+    const size_t px = (size_t)cfg->B * Hs * Ws;
+    const int minc = Hs < kMinChunk ? Hs : kMinChunk;
+    const size_t worst = (size_t)cdiv(Ws, kInner) * cdiv(Hs, minc);
+    const size_t pworst = (size_t)cdiv(Ws, kPrepInner) * cdiv(Hs, minc);
+    pl.off_ymom[s] = off;  off = al(off + px * 6 * rs);
+    pl.off_wxy[s] = off;   off = al(off + px * 2 * rs);
+    pl.off_idval[s] = off; off = al(off + px * rs);
+    pl.off_idsel[s] = off; off = al(off + px);
+    pl.off_prep[s] = off;  off = al(off + (size_t)cfg->B * pworst * kPrepVals * sizeof(double));
+    pl.off_stats[s] = off; off = al(off + (size_t)cfg->B * 4 * rs);
+    pl.off_loss[s] = off;  off = al(off + (size_t)cfg->B * worst * sizeof(double));
+    pl.off_pose[s] = off;  off = al(off + (size_t)cfg->B * worst * cfg->C * 12 * rs);
+  }
+  for (int i = 0; i < pl.nsets; ++i) {
+    const SweepSet& S = pl.sets[i];
+    for (int k = 0; k < S.ns; ++k) pl.nunits[S.scale[k]] = S.nstrips * S.nchunks;
+  }
+  pl.total = off;
+}
+
+size_t stream_workspace_bytes(const psfm_loss_cfg* cfg) {
+  SweepPlan pl;
+  make_plan(cfg, nullptr, pl);
+  return pl.total;
+}
+
+void build_params(const psfm_loss_cfg* cfg, const psfm_loss_io* io, void* ws, LossParams& P);   // loss_kernels.cu
+
+template <typename real, typename img_t, int PAD, bool RARE>
+static cudaError_t launch_sweep(const SweepParams& SP, dim3 grid, int threads, size_t smem, cudaStream_t st) {
+  auto kern = sweep_kernel<real, img_t, PAD, RARE>;
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  kern<<<grid, threads, smem, st>>>(SP);
+  return cudaSuccess;
+}
+
+template <typename real, typename img_t>
+static cudaError_t run_sweep(const psfm_loss_cfg* cfg, const psfm_loss_io* io, void* ws_split, void* ws_stream,
+                             void* loss_out, cudaStream_t st) {
+  SweepPlan pl;
+  make_plan(cfg, io, pl);
+  SweepParams SP;
+  build_params(cfg, io, ws_split, SP.P);
+  char* w = (char*)ws_stream;
+  for (int s = 0; s < cfg->n; ++s) {
+    SP.prep_part[s] = (double*)(w + pl.off_prep[s]);
+    SP.stats[s] = w + pl.off_stats[s];
+    SP.loss_part[s] = (double*)(w + pl.off_loss[s]);
+    SP.pose_part[s] = w + pl.off_pose[s];
+  }
+  bool rare = cfg->premap != 0;
+  for (int s = 0; s < cfg->n; ++s) rare = rare || io->mask[s] != nullptr;
+  for (int i = 0; i < pl.nsets; ++i) {
+    SP.set = pl.sets[i];
+    const int s0 = SP.set.scale[0];
+    SP.set.ymom = w + pl.off_ymom[s0];
+    SP.set.wxy = w + pl.off_wxy[s0];
+    SP.set.idval = w + pl.off_idval[s0];
+    SP.set.idsel = (uint8_t*)(w + pl.off_idsel[s0]);
+    const SweepSet& S = SP.set;
+    {
+      ProfScope ps(st, kTagFwd, cfg->smooth_w > 0.0 ? 2 : 1);
+      prep_kernel<real, img_t><<<dim3(cdiv(S.pstrips * S.pchunks, kPrepWarps), cfg->B), 32 * kPrepWarps, 0, st>>>(SP);
+      if (cfg->smooth_w > 0.0) stats_kernel<real><<<dim3(cfg->B, S.ns), 128, 0, st>>>(SP);
+    }
+    const size_t smem = ((size_t)cfg->C * 3 * kRing * 32 + (size_t)4 * cfg->C * 32) * sizeof(real);
+    const dim3 grid(S.nstrips * S.nchunks, S.ns, cfg->B);
+    const int threads = 32 * cfg->C;
+    ProfScope ps(st, kTagFused, 1);
+    cudaError_t e;
+    if (cfg->padding == PSFM_PAD_BORDER)
+      e = rare ? launch_sweep<real, img_t, PSFM_PAD_BORDER, true>(SP, grid, threads, smem, st)
+               : launch_sweep<real, img_t, PSFM_PAD_BORDER, false>(SP, grid, threads, smem, st);
+    else
+      e = rare ? launch_sweep<real, img_t, PSFM_PAD_ZEROS, true>(SP, grid, threads, smem, st)
+               : launch_sweep<real, img_t, PSFM_PAD_ZEROS, false>(SP, grid, threads, smem, st);
+    if (e != cudaSuccess) return e;
+  }
+  FinalParams F;
+  F.B = cfg->B; F.C = cfg->C; F.n = cfg->n; F.smooth = cfg->smooth_w > 0.0;
+  for (int s = 0; s < cfg->n; ++s) {
+    F.nunits[s] = pl.nunits[s];
+    F.inv_count[s] = SP.P.sc[s].inv_count; F.coef_x[s] = SP.P.sc[s].coef_x; F.coef_y[s] = SP.P.sc[s].coef_y;
+    F.loss_part[s] = SP.loss_part[s]; F.pose_part[s] = SP.pose_part[s]; F.stats[s] = SP.stats[s];
+  }
+  for (int j = 0; j < cfg->C; ++j) F.d_pose[j] = io->d_pose[j];
+  F.loss_out = loss_out;
+  F.one = w + pl.off_one;
+  {
+    ProfScope ps(st, kTagFinish, 1);
+    final_kernel<real><<<1 + cfg->B * cfg->C, 256, 0, st>>>(F);
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t loss_stream_dispatch(const psfm_loss_cfg* cfg, const psfm_loss_io* io, void* ws_split, void* ws_stream,
+                                 void* loss_out, cudaStream_t st) {
+  if (cfg->real_dtype == PSFM_F64) return run_sweep<double, double>(cfg, io, ws_split, ws_stream, loss_out, st);
+  if (cfg->img_dtype == PSFM_BF16) return run_sweep<float, __nv_bfloat16>(cfg, io, ws_split, ws_stream, loss_out, st);
+  return run_sweep<float, float>(cfg, io, ws_split, ws_stream, loss_out, st);
+}
+
+}  // namespace psfm

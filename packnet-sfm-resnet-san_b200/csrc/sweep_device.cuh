@@ -1,0 +1,109 @@
+// sweep_device.cuh -- per-lane building blocks of the row-sweep kernels (loss_sweep.cu).
+//
+// A warp owns a strip of 32 adjacent columns and marches down the rows; lane l is column
+// c0 - halo + l.  Horizontal neighbours are exchanged with warp shuffles, the vertical 3-row
+// windows live in register rings.  Arithmetic follows SURVEY.md Appendix A (reference
+// losses/multiview_photometric_loss.py:15-54,199-267, geometry/camera.py:111-190,
+// torch grid_sampler_2d bilinear / align_corners=True); the algebra is rearranged (pose and
+// intrinsics pre-multiplied, window statistics of the target image precomputed) but is the same
+// function of the inputs, which the fp64 instantiation checks to 1e-10 against the oracle.
+#pragma once
+#include "psfm_device.cuh"
+
+namespace psfm {
+
+constexpr unsigned kFull = 0xffffffffu;
+
+// reciprocal: exact for double; MUFU.RCP + one Newton step (< 1 ulp) for float
+__device__ __forceinline__ double rrcp(double x) { return 1.0 / x; }
+__device__ __forceinline__ float rrcp(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  const float e = fmaf(-x, r, 1.0f);
+  return fmaf(r, e, r);
+}
+
+template <typename real> __device__ __forceinline__ real shfl_up1(real v) { return __shfl_up_sync(kFull, v, 1); }
+template <typename real> __device__ __forceinline__ real shfl_dn1(real v) { return __shfl_down_sync(kFull, v, 1); }
+
+template <typename real> __device__ __forceinline__ real warp_allsum(real v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
+  return v;
+}
+
+// ------------------------------------------------------------------------------------------
+// SSIM distance of one channel from the 3x3 window SUMS of x, x^2, x*y and the precomputed
+// target statistics my = mean(y), qy = E[y^2] - my^2 + C2 (reference :15-54, :199-216).
+// When GRAD: coef[0..2] = d dist / d (sum x, sum x^2 (already x2 for d x^2/dx), sum xy).
+// ------------------------------------------------------------------------------------------
+template <typename real, bool GRAD>
+__device__ __forceinline__ real ssim_dist_sums(real Sx, real Sxx, real Sxy, real my, real qy, real C1, real C2,
+                                               real* coef) {
+  const real r9 = real(1) / real(9);
+  const real mx = Sx * r9, exx = Sxx * r9, exy = Sxy * r9;
+  const real mx2 = mx * mx, mxy = mx * my;
+  const real a1 = real(2) * mxy + C1;
+  const real v1 = real(2) * (exy - mxy) + C2;
+  const real b1 = mx2 + (my * my + C1);
+  const real v2 = (exx - mx2) + qy;
+  const real inv = rrcp(b1 * v2);
+  const real ssim = (a1 * v1) * inv;
+  const real dist = real(0.5) - real(0.5) * ssim;
+  if (GRAD) {
+    // d dist = -0.5 d ssim inside the clamp range, 0 outside
+    const real act = (dist >= real(0) && dist <= real(1)) ? real(-0.5) * r9 * inv : real(0);
+    coef[0] = act * (real(2) * my * (v1 - a1) - ssim * real(2) * mx * (v2 - b1));
+    coef[1] = act * (real(-2) * ssim * b1);
+    coef[2] = act * (real(2) * a1);
+  }
+  return rmin(rmax(dist, real(0)), real(1));
+}
+
+// ------------------------------------------------------------------------------------------
+// bilinear sample of a 3-plane image at (ix, iy) with value and coordinate gradients
+// (grid_sample bilinear, align_corners=True).  Out-of-image taps are removed through their
+// WEIGHTS (zeros padding) and every address is clamped into the plane, so all 12 loads are
+// unconditional.  PAD == border clips the coordinate and zeroes its gradient where clipped.
+// ------------------------------------------------------------------------------------------
+template <typename real, typename img_t, int PAD>
+__device__ __forceinline__ void sample3(const img_t* __restrict__ img, int plane, int H, int W, real ix, real iy,
+                                        real* out, real* gx, real* gy) {
+  real mx = real(1), my = real(1);
+  if (PAD == PSFM_PAD_BORDER) {
+    if (!(ix > real(0))) { ix = real(0); mx = real(0); }
+    else if (ix >= real(W - 1)) { ix = real(W - 1); mx = real(0); }
+    if (!(iy > real(0))) { iy = real(0); my = real(0); }
+    else if (iy >= real(H - 1)) { iy = real(H - 1); my = real(0); }
+  } else {
+    // fully outside beyond [-1, size]: keep the value there so the int conversion is defined
+    ix = rmin(rmax(ix, real(-2)), real(W + 1));
+    iy = rmin(rmax(iy, real(-2)), real(H + 1));
+  }
+  const real fx = rfloor(ix), fy = rfloor(iy);
+  const int x0 = (int)fx, y0 = (int)fy;
+  const real wx1 = ix - fx, wx0 = (fx + real(1)) - ix;
+  const real wy1 = iy - fy, wy0 = (fy + real(1)) - iy;
+  const bool bx0 = (unsigned)x0 < (unsigned)W, bx1 = (unsigned)(x0 + 1) < (unsigned)W;
+  const bool by0 = (unsigned)y0 < (unsigned)H, by1 = (unsigned)(y0 + 1) < (unsigned)H;
+  const real ax0 = bx0 ? wx0 : real(0), ax1 = bx1 ? wx1 : real(0);
+  const real ay0 = by0 ? wy0 : real(0), ay1 = by1 ? wy1 : real(0);
+  const real sx0 = bx0 ? mx : real(0), sx1 = bx1 ? mx : real(0);
+  const real sy0 = by0 ? my : real(0), sy1 = by1 ? my : real(0);
+  const int xc0 = min(max(x0, 0), W - 1), xc1 = min(max(x0 + 1, 0), W - 1);
+  const int yc0 = min(max(y0, 0), H - 1), yc1 = min(max(y0 + 1, 0), H - 1);
+  const int r0 = yc0 * W, r1 = yc1 * W;
+  const int o00 = r0 + xc0, o01 = r0 + xc1, o10 = r1 + xc0, o11 = r1 + xc1;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    const img_t* p = img + (size_t)c * plane;
+    const real v00 = ldimg<real>(p, o00), v01 = ldimg<real>(p, o01);
+    const real v10 = ldimg<real>(p, o10), v11 = ldimg<real>(p, o11);
+    const real top = ax0 * v00 + ax1 * v01, bot = ax0 * v10 + ax1 * v11;
+    out[c] = ay0 * top + ay1 * bot;
+    gx[c] = ay0 * (sx1 * v01 - sx0 * v00) + ay1 * (sx1 * v11 - sx0 * v10);
+    gy[c] = ax0 * (sy1 * v10 - sy0 * v00) + ax1 * (sy1 * v11 - sy0 * v01);
+  }
+}
+
+}  // namespace psfm
