@@ -105,23 +105,45 @@ __global__ void __launch_bounds__(32 * kPrepWarps) prep_kernel(const SweepParams
 #pragma unroll
     for (int k = 0; k < PSFM_MAX_SCALES; ++k) dp[k] = real(0);
 
-    for (int t = r0 - 1; t <= r1; ++t) {
-      const int p = t - 1;
+    // software pipeline: the loads of row t + 1 are issued before row t is processed
+    real yn[3], xn[3] = {real(0), real(0), real(0)}, dn[PSFM_MAX_SCALES] = {real(0), real(0), real(0), real(0)};
+    auto load_row = [&](int t) {
       const int o = reflect1(t, H) * W + su;
-      real y[3], ya[3], yc[3], hyn[6];
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
-        y[c] = ldimg<real>(image + (size_t)c * plane, o);
+        yn[c] = ldimg<real>(image + (size_t)c * plane, o);
+        if (P.automask) xn[c] = ldimg<real>(ctx + (size_t)c * plane, o);
+      }
+      if (j == 0 && smooth) {
+#pragma unroll
+        for (int k = 0; k < PSFM_MAX_SCALES; ++k)
+          if (k < S.ns) dn[k] = __ldg((const real*)P.sc[S.scale[k]].invd + (size_t)b * plane + o);
+      }
+    };
+    load_row(r0 - 1);
+    for (int t = r0 - 1; t <= r1; ++t) {
+      const int p = t - 1;
+      const bool emit = inner && p >= r0 && p < r1;
+      const int op = p * W + u;
+      real y[3], ya[3], yc[3], hyn[6], x[3], dcur[PSFM_MAX_SCALES];
+#pragma unroll
+      for (int c = 0; c < 3; ++c) { y[c] = yn[c]; x[c] = xn[c]; }
+#pragma unroll
+      for (int k = 0; k < PSFM_MAX_SCALES; ++k) dcur[k] = dn[k];
+      real idprev = real(0);
+      if (j > 0 && emit) idprev = idval[op];
+      load_row(t + 1);
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
         ya[c] = shfl_up1(y[c]);
         yc[c] = shfl_dn1(y[c]);
         hyn[c] = ya[c] + y[c] + yc[c];
         hyn[3 + c] = ya[c] * ya[c] + y[c] * y[c] + yc[c] * yc[c];
       }
-      real x[3] = {real(0), real(0), real(0)}, hxn[9];
+      real hxn[9];
       if (P.automask) {
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
-          x[c] = ldimg<real>(ctx + (size_t)c * plane, o);
           const real z = x[c] * y[c];
           const real xa = shfl_up1(x[c]), xc = shfl_dn1(x[c]);
           const real za = shfl_up1(z), zc = shfl_dn1(z);
@@ -130,8 +152,6 @@ __global__ void __launch_bounds__(32 * kPrepWarps) prep_kernel(const SweepParams
           hxn[c * 3 + 2] = za + z + zc;
         }
       }
-      const bool emit = inner && p >= r0 && p < r1;
-      const int op = p * W + u;
       real wx = real(0), wy = real(0);
       if (emit) {
         real my[3], qy[3];
@@ -158,7 +178,7 @@ __global__ void __launch_bounds__(32 * kPrepWarps) prep_kernel(const SweepParams
             ls += rabs(xp[c] - yp[c]);
           }
           const real val = ssim_w * (ds * r3) + (real(1) - ssim_w) * (ls * r3);
-          if (j == 0 || val < idval[op]) { idval[op] = val; idsel[op] = (uint8_t)(2 * j + 1); }
+          if (j == 0 || val < idprev) { idval[op] = val; idsel[op] = (uint8_t)(2 * j + 1); }
         }
         if (j == 0 && smooth) {
           if (u + 1 < W) wx = rexp(-((rabs(yp[0] - ycp[0]) + rabs(yp[1] - ycp[1]) + rabs(yp[2] - ycp[2])) * r3));
@@ -173,8 +193,7 @@ __global__ void __launch_bounds__(32 * kPrepWarps) prep_kernel(const SweepParams
 #pragma unroll
         for (int k = 0; k < PSFM_MAX_SCALES; ++k) {
           if (k < S.ns) {
-            const real* invd = (const real*)P.sc[S.scale[k]].invd + (size_t)b * plane;
-            const real dt = invd[o];
+            const real dt = dcur[k];
             const real dr = shfl_dn1(dp[k]);
             if (emit) {
               sums[k][0] += dp[k];
@@ -287,8 +306,8 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
   const bool col_inner = (lane >= 2) && (lane < 30) && col_real;
   const int r0 = chunk * S.chunk_h, r1 = min(r0 + S.chunk_h, H);
 
-  real* ring = (real*)smem_raw + (size_t)j * 3 * kRing * 32 + lane;        // [slot][kRing][32]
-  real* photo_s = (real*)smem_raw + (size_t)C * 3 * kRing * 32;            // [2][C][32]
+  real* ring = (real*)smem_raw + (size_t)j * 4 * kRing * 32 + lane;        // [4 slots][kRing][32]
+  real* photo_s = (real*)smem_raw + (size_t)C * 4 * kRing * 32;            // [2][C][32]
   real* dpart_s = photo_s + 2 * C * 32;                                    // [2][C][32]
 
   const ScaleDesc& SD = P.sc[s];
@@ -347,13 +366,47 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
     for (int c = 0; c < 3; ++c) { xr[a][c] = real(0); yr[a][c] = real(0); }
   }
 #pragma unroll
-  for (int k = 0; k < 3 * kRing; ++k) ring[k * 32] = real(0);
+  for (int k = 0; k < 4 * kRing; ++k) ring[k * 32] = real(0);
   real S0a[3] = {real(0), real(0), real(0)}, Sva[3] = {real(0), real(0), real(0)}, S1a[3] = {real(0), real(0), real(0)};
   real loss_acc = real(0), w_cur = real(0), w_old = real(0);
   real d0 = real(0), d1 = real(0), d2 = real(0), d3 = real(0);   // raw inverse depths of rows t, t-1, t-2, t-3
   real dsum_prev = real(0);
   int prev_q = -1;
   real* d_out = (real*)SD.d_invd + (size_t)b * plane;
+
+  // gather pipeline: geometry of `row`, the 12 tap loads go in flight, consumed one step later
+  real tap[12], wgt[8];
+  auto start_row = [&](int row, real draw) {
+    real dd = draw;
+    if (premap) { real ch; dd = premap_fork<real>(draw, (real)P.premap_lo, (real)P.premap_hi, ch); }
+    const real D = rrcp(rmax(dd, real(1e-6)));                    // utils/depth.py:120
+    const real fv = (real)reflect1(row, H);
+    const real p0 = (A0[0] + A1[0] * fv) * D + mt[0];
+    const real p1 = (A0[1] + A1[1] * fv) * D + mt[1];
+    const real p2 = (A0[2] + A1[2] * fv) * D + mt[2];
+    const real iz = rrcp(rmax(p2, real(1e-5)));                   // camera.py:179
+    const real ix = p0 * iz, iy = p1 * iz;
+    sample3_issue<real, img_t, PAD>(ctx, plane, H, W, ix, iy, wgt, tap);
+    real* rs = ring + (row & 3) * kRing * 32;
+    rs[6 * 32] = D;
+    rs[7 * 32] = (p2 >= real(1e-5)) ? iz : -iz;                   // sign flags the clamp
+    rs[8 * 32] = ix;
+    rs[9 * 32] = iy;
+  };
+  real ynx[3], mynx[3], qynx[3];
+  real dnx = __ldg(invd + reflect1(r0 - 2, H) * W + su);
+  real dpre = __ldg(invd + reflect1(r0 - 1, H) * W + su);
+  {
+    const int on = reflect1(r0 - 2, H) * W + su;
+    const int opn = min(max(r0 - 3, 0), H - 1) * W + su;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      ynx[c] = ldimg<real>(image + c * plane, on);
+      mynx[c] = __ldg(ymom + c * plane + opn);
+      qynx[c] = __ldg(ymom + (3 + c) * plane + opn);
+    }
+  }
+  start_row(r0 - 2, dnx);
 
   auto finalize_row = [&](int par) {      // context 0 adds the other contexts' parts and stores the row
     if (j == 0 && prev_q >= 0) {
@@ -368,33 +421,46 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
     constexpr int PH = decltype(phc)::value, Q = (PH + 1) % 3, P1 = (PH + 2) % 3;
     const int p = t - 1, q = t - 2;
     const int par = t & 1;
-    // ---------------- gather row t -----------------------------------------------------------------
+    // ---------------- loads with depth-independent addresses: prefetch row t + 1, late operands of t ----
+    const bool p_real = (p >= 0) && (p < H) && col_real;
+    real yt[3], my[3], qy[3];
+    real idv = real_inf<real>(), wxq = real(0), wyq = real(0), wym = real(0), m = real(1);
+    int ids = 255;
     {
-      const int sv = reflect1(t, H);
-      const int o = sv * W + su;
-      d3 = d2; d2 = d1; d1 = d0;
-      d0 = invd[o];
-      real dd = d0;
-      if (premap) { real ch; dd = premap_fork<real>(d0, (real)P.premap_lo, (real)P.premap_hi, ch); }
-      const real D = rrcp(rmax(dd, real(1e-6)));                    // utils/depth.py:120
-      const real fv = (real)sv;
-      const real p0 = (A0[0] + A1[0] * fv) * D + mt[0];
-      const real p1 = (A0[1] + A1[1] * fv) * D + mt[1];
-      const real p2 = (A0[2] + A1[2] * fv) * D + mt[2];
-      const real iz = rrcp(rmax(p2, real(1e-5)));                   // camera.py:179
-      const real ix = p0 * iz, iy = p1 * iz;
-      real x[3], gx[3], gy[3];
-      sample3<real, img_t, PAD>(ctx, plane, H, W, ix, iy, x, gx, gy);
-      real* rs = ring + PH * kRing * 32;
 #pragma unroll
-      for (int c = 0; c < 3; ++c) { rs[c * 32] = gx[c]; rs[(3 + c) * 32] = gy[c]; }
-      rs[6 * 32] = D;
-      rs[7 * 32] = (p2 >= real(1e-5)) ? iz : -iz;                   // sign flags the clamp
-      rs[8 * 32] = ix;
-      rs[9 * 32] = iy;
+      for (int c = 0; c < 3; ++c) { yt[c] = ynx[c]; my[c] = mynx[c]; qy[c] = qynx[c]; }
+      d3 = d2; d2 = d1; d1 = d0;
+      d0 = dnx;
+      dnx = dpre;
+      dpre = __ldg(invd + reflect1(t + 2, H) * W + su);
+      const int on = reflect1(t + 1, H) * W + su;
+      const int opn = min(max(p + 1, 0), H - 1) * W + su;
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
-        const real y = ldimg<real>(image + (size_t)c * plane, o);
+        ynx[c] = ldimg<real>(image + c * plane, on);
+        mynx[c] = __ldg(ymom + c * plane + opn);
+        qynx[c] = __ldg(ymom + (3 + c) * plane + opn);
+      }
+      if (P.automask && p_real) { idv = __ldg(idval + p * W + u); ids = (int)__ldg(idsel + p * W + u); }
+      if (RARE && maskp) m = p_real ? ldimg<real>(maskp, p * W + u) : real(0);
+      if (j == 0 && smooth) {
+        const int qc = min(max(q, 0), H - 1);
+        wxq = __ldg(wxy + qc * W + su);
+        wyq = __ldg(wxy + plane + qc * W + su);
+        wym = __ldg(wxy + plane + max(qc - 1, 0) * W + su);
+      }
+    }
+    // ---------------- finish the gather of row t (issued one step ago), start the one of row t + 1 ----
+    {
+      real x[3], gx[3], gy[3];
+      sample3_finish<real>(wgt, tap, x, gx, gy);
+      real* rs = ring + (t & 3) * kRing * 32;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) { rs[c * 32] = gx[c]; rs[(3 + c) * 32] = gy[c]; }
+      start_row(t + 1, dnx);
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const real y = yt[c];
         const real z = x[c] * y;
         xr[PH][c] = x[c];
         yr[PH][c] = y;
@@ -406,24 +472,19 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
       }
     }
     // ---------------- SSIM + L1 at row p, candidate min across the contexts --------------------------
-    const bool p_real = (p >= 0) && (p < H) && col_real;
     real coef[9];
     real F[9];
     {
-      const int op = min(max(p, 0), H - 1) * W + su;
       real ds = real(0), ls = real(0);
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
-        const real my = ymom[(size_t)c * plane + op], qy = ymom[(size_t)(3 + c) * plane + op];
         ds += ssim_dist_sums<real, true>(h[0][c * 3] + h[1][c * 3] + h[2][c * 3],
                                          h[0][c * 3 + 1] + h[1][c * 3 + 1] + h[2][c * 3 + 1],
-                                         h[0][c * 3 + 2] + h[1][c * 3 + 2] + h[2][c * 3 + 2], my, qy, C1, C2,
+                                         h[0][c * 3 + 2] + h[1][c * 3 + 2] + h[2][c * 3 + 2], my[c], qy[c], C1, C2,
                                          &coef[c * 3]);
         ls += rabs(xr[P1][c] - yr[P1][c]);
       }
       const real photo = ssim_w * (ds * r3) + k1 * ls;
-      real m = real(1);
-      if (RARE && maskp) m = p_real ? ldimg<real>(maskp, (size_t)p * W + u) : real(0);
       real best = photo * m;
       int sel = mycand;
       if (C > 1) {
@@ -437,8 +498,8 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
         }
       }
       if (P.automask && p_real) {
-        const real vi = idval[p * W + u] * m;
-        const int ki = (int)idsel[p * W + u];
+        const real vi = idv * m;
+        const int ki = ids;
         if (vi < best || (vi == best && ki < sel)) { best = vi; sel = ki; }
       }
       w_old = w_cur;
@@ -458,7 +519,7 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
       }
       const bool q_ok = (q >= r0) && (q < r1) && col_inner;
       const real mv0 = (q == 1) ? real(2) : real(1), mv2 = (q == H - 2) ? real(2) : real(1);
-      const real* rq = ring + Q * kRing * 32;
+      const real* rq = ring + (q & 3) * kRing * 32;
       real gix = real(0), giy = real(0);
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
@@ -491,10 +552,6 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
         real gs = real(0);
         if (smooth) {
           const real dl = shfl_up1(d2), dr = shfl_dn1(d2);
-          const int qc = min(max(q, 0), H - 1);
-          const real wxq = wxy[qc * W + su];
-          const real wyq = wxy[(size_t)plane + qc * W + su];
-          const real wym = wxy[(size_t)plane + max(qc - 1, 0) * W + su];
           const real wxl = shfl_up1(wxq);
           real qq = real(0);
           if (u + 1 < W) qq += coef_x * rsign(d2 - dr) * wxq;
@@ -770,7 +827,7 @@ static cudaError_t run_sweep(const psfm_loss_cfg* cfg, const psfm_loss_io* io, v
       prep_kernel<real, img_t><<<dim3(cdiv(S.pstrips * S.pchunks, kPrepWarps), cfg->B), 32 * kPrepWarps, 0, st>>>(SP);
       if (cfg->smooth_w > 0.0) stats_kernel<real><<<dim3(cfg->B, S.ns), 128, 0, st>>>(SP);
     }
-    const size_t smem = ((size_t)cfg->C * 3 * kRing * 32 + (size_t)4 * cfg->C * 32) * sizeof(real);
+    const size_t smem = ((size_t)cfg->C * 4 * kRing * 32 + (size_t)4 * cfg->C * 32) * sizeof(real);
     const dim3 grid(S.nstrips * S.nchunks, S.ns, cfg->B);
     const int threads = 32 * cfg->C;
     ProfScope ps(st, kTagFused, 1);

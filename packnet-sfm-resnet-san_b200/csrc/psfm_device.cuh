@@ -28,9 +28,9 @@ template <typename real> __device__ __forceinline__ real rsign(real x) {
 }
 
 // image element load with conversion to the arithmetic type (read-only path)
-template <typename real> __device__ __forceinline__ real ldimg(const float* p, size_t i) { return (real)__ldg(p + i); }
-template <typename real> __device__ __forceinline__ real ldimg(const double* p, size_t i) { return (real)__ldg(p + i); }
-template <typename real> __device__ __forceinline__ real ldimg(const __nv_bfloat16* p, size_t i) {
+template <typename real, typename I> __device__ __forceinline__ real ldimg(const float* p, I i) { return (real)__ldg(p + i); }
+template <typename real, typename I> __device__ __forceinline__ real ldimg(const double* p, I i) { return (real)__ldg(p + i); }
+template <typename real, typename I> __device__ __forceinline__ real ldimg(const __nv_bfloat16* p, I i) {
   return (real)__bfloat162float(__ldg(p + i));
 }
 

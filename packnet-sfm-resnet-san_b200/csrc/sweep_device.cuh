@@ -62,13 +62,16 @@ __device__ __forceinline__ real ssim_dist_sums(real Sx, real Sxx, real Sxy, real
 
 // ------------------------------------------------------------------------------------------
 // bilinear sample of a 3-plane image at (ix, iy) with value and coordinate gradients
-// (grid_sample bilinear, align_corners=True).  Out-of-image taps are removed through their
-// WEIGHTS (zeros padding) and every address is clamped into the plane, so all 12 loads are
-// unconditional.  PAD == border clips the coordinate and zeroes its gradient where clipped.
+// (grid_sample bilinear, align_corners=True), split in two so that the 12 loads can be in flight
+// while other rows are processed.  Out-of-image taps are removed through their WEIGHTS (zeros
+// padding) and every address is clamped into the plane, so all loads are unconditional.
+// PAD == border clips the coordinate and zeroes its gradient where clipped.
+//   wgt[8] = {ax0, ax1, ay0, ay1, sx0, sx1, sy0, sy1}: value weights and d/d(ix,iy) tap signs
+//   tap[c * 4 + {0,1,2,3}] = {v00, v01, v10, v11} of channel c
 // ------------------------------------------------------------------------------------------
 template <typename real, typename img_t, int PAD>
-__device__ __forceinline__ void sample3(const img_t* __restrict__ img, int plane, int H, int W, real ix, real iy,
-                                        real* out, real* gx, real* gy) {
+__device__ __forceinline__ void sample3_issue(const img_t* __restrict__ img, int plane, int H, int W, real ix, real iy,
+                                              real* wgt, real* tap) {
   real mx = real(1), my = real(1);
   if (PAD == PSFM_PAD_BORDER) {
     if (!(ix > real(0))) { ix = real(0); mx = real(0); }
@@ -86,19 +89,29 @@ __device__ __forceinline__ void sample3(const img_t* __restrict__ img, int plane
   const real wy1 = iy - fy, wy0 = (fy + real(1)) - iy;
   const bool bx0 = (unsigned)x0 < (unsigned)W, bx1 = (unsigned)(x0 + 1) < (unsigned)W;
   const bool by0 = (unsigned)y0 < (unsigned)H, by1 = (unsigned)(y0 + 1) < (unsigned)H;
-  const real ax0 = bx0 ? wx0 : real(0), ax1 = bx1 ? wx1 : real(0);
-  const real ay0 = by0 ? wy0 : real(0), ay1 = by1 ? wy1 : real(0);
-  const real sx0 = bx0 ? mx : real(0), sx1 = bx1 ? mx : real(0);
-  const real sy0 = by0 ? my : real(0), sy1 = by1 ? my : real(0);
+  wgt[0] = bx0 ? wx0 : real(0); wgt[1] = bx1 ? wx1 : real(0);
+  wgt[2] = by0 ? wy0 : real(0); wgt[3] = by1 ? wy1 : real(0);
+  wgt[4] = bx0 ? mx : real(0); wgt[5] = bx1 ? mx : real(0);
+  wgt[6] = by0 ? my : real(0); wgt[7] = by1 ? my : real(0);
   const int xc0 = min(max(x0, 0), W - 1), xc1 = min(max(x0 + 1, 0), W - 1);
   const int yc0 = min(max(y0, 0), H - 1), yc1 = min(max(y0 + 1, 0), H - 1);
   const int r0 = yc0 * W, r1 = yc1 * W;
   const int o00 = r0 + xc0, o01 = r0 + xc1, o10 = r1 + xc0, o11 = r1 + xc1;
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
-    const img_t* p = img + (size_t)c * plane;
-    const real v00 = ldimg<real>(p, o00), v01 = ldimg<real>(p, o01);
-    const real v10 = ldimg<real>(p, o10), v11 = ldimg<real>(p, o11);
+    const img_t* p = img + c * plane;
+    tap[c * 4 + 0] = ldimg<real>(p, o00); tap[c * 4 + 1] = ldimg<real>(p, o01);
+    tap[c * 4 + 2] = ldimg<real>(p, o10); tap[c * 4 + 3] = ldimg<real>(p, o11);
+  }
+}
+
+template <typename real>
+__device__ __forceinline__ void sample3_finish(const real* wgt, const real* tap, real* out, real* gx, real* gy) {
+  const real ax0 = wgt[0], ax1 = wgt[1], ay0 = wgt[2], ay1 = wgt[3];
+  const real sx0 = wgt[4], sx1 = wgt[5], sy0 = wgt[6], sy1 = wgt[7];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    const real v00 = tap[c * 4], v01 = tap[c * 4 + 1], v10 = tap[c * 4 + 2], v11 = tap[c * 4 + 3];
     const real top = ax0 * v00 + ax1 * v01, bot = ax0 * v10 + ax1 * v11;
     out[c] = ay0 * top + ay1 * bot;
     gx[c] = ay0 * (sx1 * v01 - sx0 * v00) + ay1 * (sx1 * v11 - sx0 * v10);
