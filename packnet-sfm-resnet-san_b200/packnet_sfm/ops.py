@@ -160,7 +160,8 @@ class _PhotometricLossFn(torch.autograd.Function):
                 _C.check(_C.lib.psfm_loss_forward(*plan.args(), _C.ptr(plan.out), st))
         ctx.plan, ctx.mode, ctx.consumed = plan, mode, False
         ctx.counts = (n, Cn)
-        return plan.out
+        out, plan.out = plan.out, None      # the node must not reference its own output (reference cycle)
+        return out
 
     @staticmethod
     def backward(ctx, grad_out):
