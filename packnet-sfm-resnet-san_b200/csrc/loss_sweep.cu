@@ -30,21 +30,34 @@ constexpr int kPrepWarps = 4;        // independent warps per prep CTA
 constexpr int kInner = 28;           // columns a sweep warp produces (32 lanes - 2 halo each side)
 constexpr int kRing = 10;            // per-row values parked in shared memory between forward and adjoint
 
+constexpr int kRec = 8;              // reals per pixel record written by the prep kernel
+
 struct SweepSet {                    // scales of equal resolution sharing the same images
   int ns;
   int scale[PSFM_MAX_SCALES];
   int H, W;
   int nstrips, nchunks, chunk_h;     // sweep kernel decomposition
   int pstrips, pchunks, pchunk_h;    // prep kernel decomposition
-  void* ymom;                        // real [B][6][H][W]: mean(y) x3, E[y^2]-mean(y)^2+C2 x3
-  void* wxy;                         // real [B][2][H][W]: exp(-mean|dx I|), exp(-mean|dy I|)
-  void* idval;                       // real [B][H][W] min identity photometric value (automask)
-  uint8_t* idsel;                    // u8   [B][H][W] its candidate index (2j+1)
+  void* rec;                         // real [B][H][W][kRec]: mean(y) x3, E[y^2]-mean(y)^2+C2 x3,
+                                     //   min identity photometric value (automask), its candidate index
+  void* wxy;                         // real [B][H][W][2]: exp(-mean|dx I|), exp(-mean|dy I|)
+};
+
+template <typename real> struct SweepConsts {   // hyper-parameters pre-converted to the arithmetic type
+  real ssim_w3;                      // ssim_loss_weight / 3
+  real k1;                           // (1 - ssim_loss_weight) / 3
+  real C1, C2;
+  real inv_count;                    // weight of one pixel in the photometric mean (same for a set)
+  real premap_lo, premap_hi;
+  real pad_;
+  real coef_x[PSFM_MAX_SCALES], coef_y[PSFM_MAX_SCALES], sf[PSFM_MAX_SCALES];   // per scale id
 };
 
 struct SweepParams {
   LossParams P;
   SweepSet set;
+  SweepConsts<float> cf;
+  SweepConsts<double> cd;
   // per scale (indexed by the scale id)
   double* prep_part[PSFM_MAX_SCALES];   // [B][punits][kPrepVals]
   void* stats[PSFM_MAX_SCALES];         // real [B][4]: clamped mean, coupling constant, SX, SY
@@ -58,7 +71,7 @@ struct SweepParams {
 // row p = t - 1.  Pass j handles context j (pass 0 also the image-only outputs).
 // ------------------------------------------------------------------------------------------
 template <typename real, typename img_t>
-__global__ void __launch_bounds__(32 * kPrepWarps) prep_kernel(const SweepParams SP) {
+__global__ void __launch_bounds__(32 * kPrepWarps, 4) prep_kernel(const SweepParams SP) {
   const LossParams& P = SP.P;
   const SweepSet& S = SP.set;
   const int lane = threadIdx.x & 31;
@@ -73,10 +86,8 @@ __global__ void __launch_bounds__(32 * kPrepWarps) prep_kernel(const SweepParams
   const bool inner = (lane >= 1) && (lane <= kPrepInner) && (u < W);
   const ScaleDesc& S0 = P.sc[S.scale[0]];
   const img_t* image = (const img_t*)S0.image + (size_t)b * 3 * plane;
-  real* ymom = (real*)S.ymom + (size_t)b * 6 * plane;
-  real* wxy = (real*)S.wxy + (size_t)b * 2 * plane;
-  real* idval = (real*)S.idval + (size_t)b * plane;
-  uint8_t* idsel = S.idsel + (size_t)b * plane;
+  real* rec = (real*)S.rec + (size_t)b * plane * kRec;
+  real* wxy = (real*)S.wxy + (size_t)b * plane * 2;
   const real ssim_w = (real)P.ssim_w, C1 = (real)P.C1, C2 = (real)P.C2;
   const real r3 = real(1) / real(3), r9 = real(1) / real(9);
   const bool smooth = P.smooth_w > 0.0;
@@ -131,7 +142,7 @@ __global__ void __launch_bounds__(32 * kPrepWarps) prep_kernel(const SweepParams
 #pragma unroll
       for (int k = 0; k < PSFM_MAX_SCALES; ++k) dcur[k] = dn[k];
       real idprev = real(0);
-      if (j > 0 && emit) idprev = idval[op];
+      if (j > 0 && emit) idprev = rec[(size_t)op * kRec + 6];
       load_row(t + 1);
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
@@ -163,8 +174,8 @@ __global__ void __launch_bounds__(32 * kPrepWarps) prep_kernel(const SweepParams
         if (j == 0) {
 #pragma unroll
           for (int c = 0; c < 3; ++c) {
-            ymom[(size_t)c * plane + op] = my[c];
-            ymom[(size_t)(3 + c) * plane + op] = qy[c];
+            rec[(size_t)op * kRec + c] = my[c];
+            rec[(size_t)op * kRec + 3 + c] = qy[c];
           }
         }
         if (P.automask) {
@@ -178,13 +189,13 @@ __global__ void __launch_bounds__(32 * kPrepWarps) prep_kernel(const SweepParams
             ls += rabs(xp[c] - yp[c]);
           }
           const real val = ssim_w * (ds * r3) + (real(1) - ssim_w) * (ls * r3);
-          if (j == 0 || val < idprev) { idval[op] = val; idsel[op] = (uint8_t)(2 * j + 1); }
+          if (j == 0 || val < idprev) { rec[(size_t)op * kRec + 6] = val; rec[(size_t)op * kRec + 7] = (real)(2 * j + 1); }
         }
         if (j == 0 && smooth) {
           if (u + 1 < W) wx = rexp(-((rabs(yp[0] - ycp[0]) + rabs(yp[1] - ycp[1]) + rabs(yp[2] - ycp[2])) * r3));
           if (p + 1 < H) wy = rexp(-((rabs(yp[0] - y[0]) + rabs(yp[1] - y[1]) + rabs(yp[2] - y[2])) * r3));
-          wxy[op] = wx;
-          wxy[(size_t)plane + op] = wy;
+          wxy[(size_t)op * 2] = wx;
+          wxy[(size_t)op * 2 + 1] = wy;
         }
       }
       if (j == 0 && smooth) {
@@ -268,8 +279,9 @@ __global__ void __launch_bounds__(128) stats_kernel(const SweepParams SP) {
 // ------------------------------------------------------------------------------------------
 // sweep kernel: grid (nstrips * nchunks, ns, B), 32 * C threads (warp j = context j).
 // Lane l is column c0 - 2 + l (2 halo columns per side: SSIM needs +-1, its adjoint +-1 more).
-// Step t gathers row t, evaluates SSIM / the candidate min at row p = t - 1 and the adjoint
-// (d/d inv_depth, d/d pose) at row q = t - 2.
+// Step t finishes the gather of row t (issued one step earlier), starts the gather of row t + 1,
+// evaluates SSIM / the candidate min at row p = t - 1 and the adjoint (d/d inv_depth, d/d pose)
+// at row q = t - 2.
 // ------------------------------------------------------------------------------------------
 template <typename real> struct SweepCam {
   real ki[9];   // reference `Kinv` (camera.py:73-81)
@@ -290,12 +302,47 @@ __device__ __forceinline__ void sweep_cam(SweepCam<real>& c, const LossParams& P
 
 template <int V> struct IntC { static constexpr int value = V; };
 
-template <typename real, typename img_t, int PAD, bool RARE>
-__global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
+template <typename real> __device__ __forceinline__ const SweepConsts<real>& sweep_consts(const SweepParams& SP);
+template <> __device__ __forceinline__ const SweepConsts<float>& sweep_consts<float>(const SweepParams& SP) { return SP.cf; }
+template <> __device__ __forceinline__ const SweepConsts<double>& sweep_consts<double>(const SweepParams& SP) { return SP.cd; }
+
+// one pixel record of the prep kernel: 8 reals, 16-byte vector loads
+__device__ __forceinline__ void load_rec(const float* p, float* o) {
+  const float4 a = __ldg((const float4*)p), b = __ldg((const float4*)p + 1);
+  o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
+}
+__device__ __forceinline__ void load_rec(const double* p, double* o) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const double2 v = __ldg((const double2*)p + i);
+    o[2 * i] = v.x; o[2 * i + 1] = v.y;
+  }
+}
+__device__ __forceinline__ void load_pair(const float* p, float& a, float& b) {
+  const float2 v = __ldg((const float2*)p);
+  a = v.x; b = v.y;
+}
+__device__ __forceinline__ void load_pair(const double* p, double& a, double& b) {
+  const double2 v = __ldg((const double2*)p);
+  a = v.x; b = v.y;
+}
+
+// mag * sign(x) with sign(0) = 0
+__device__ __forceinline__ float signed_by(float mag, float x) {
+  const float s = __int_as_float(__float_as_int(mag) ^ (__float_as_int(x) & 0x80000000));
+  return x == 0.0f ? 0.0f : s;
+}
+__device__ __forceinline__ double signed_by(double mag, double x) {
+  return x > 0.0 ? mag : (x < 0.0 ? -mag : 0.0);
+}
+
+template <typename real, typename img_t, int PAD, bool RARE, int CT>
+__global__ void __launch_bounds__(CT ? 32 * CT : 256) sweep_kernel(const SweepParams SP) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const LossParams& P = SP.P;
   const SweepSet& S = SP.set;
-  const int C = P.C;
+  const SweepConsts<real>& K = sweep_consts<real>(SP);
+  const int C = CT ? CT : P.C;
   const int lane = threadIdx.x & 31, j = threadIdx.x >> 5;
   const int unit = blockIdx.x, nunits = gridDim.x;
   const int strip = unit % S.nstrips, chunk = unit / S.nstrips;
@@ -311,13 +358,11 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
   real* dpart_s = photo_s + 2 * C * 32;                                    // [2][C][32]
 
   const ScaleDesc& SD = P.sc[s];
-  const img_t* image = (const img_t*)SD.image + (size_t)b * 3 * plane;
-  const img_t* ctx = (const img_t*)SD.ctx[j] + (size_t)b * 3 * plane;
+  const img_t* img0 = (const img_t*)SD.image + (size_t)b * 3 * plane;
+  const img_t* ctx0 = (const img_t*)SD.ctx[j] + (size_t)b * 3 * plane;
   const real* invd = (const real*)SD.invd + (size_t)b * plane;
-  const real* ymom = (const real*)S.ymom + (size_t)b * 6 * plane;
-  const real* wxy = (const real*)S.wxy + (size_t)b * 2 * plane;
-  const real* idval = (const real*)S.idval + (size_t)b * plane;
-  const uint8_t* idsel = S.idsel + (size_t)b * plane;
+  const real* rec = (const real*)S.rec + (size_t)b * plane * kRec;
+  const real* wxy = (const real*)S.wxy + (size_t)b * plane * 2;
   const img_t* maskp = (RARE && SD.mask) ? (const img_t*)SD.mask + (size_t)b * plane : nullptr;
   const bool premap = RARE && P.premap;
   const bool smooth = P.smooth_w > 0.0;
@@ -326,7 +371,7 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
   real A0[3], A1[3], mt[3];
   {
     SweepCam<real> cam;
-    sweep_cam<real>(cam, P, b, j, (real)SD.sf);
+    sweep_cam<real>(cam, P, b, j, K.sf[s]);
     real M[9];
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
@@ -343,10 +388,6 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
       A1[i] = M[i * 3] * cam.ki[1] + M[i * 3 + 1] * cam.ki[4] + M[i * 3 + 2] * cam.ki[7];
     }
   }
-  const real ssim_w = (real)P.ssim_w, C1 = (real)P.C1, C2 = (real)P.C2;
-  const real r3 = real(1) / real(3);
-  const real k1 = (real(1) - ssim_w) * r3;
-  const real inv_count = (real)SD.inv_count;
   const real mu0 = (u == 1) ? real(2) : real(1), mu2 = (u == W - 2) ? real(2) : real(1);
   const int mycand = P.automask ? 2 * j : j;
   real inv_m = real(1), cb = real(0);
@@ -355,7 +396,6 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
     inv_m = real(1) / st[0];
     cb = st[1];
   }
-  const real coef_x = (real)SD.coef_x, coef_y = (real)SD.coef_y;
 
   real h[3][9], hF[3][9], xr[3][3], yr[3][3];
 #pragma unroll
@@ -370,6 +410,7 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
   real S0a[3] = {real(0), real(0), real(0)}, Sva[3] = {real(0), real(0), real(0)}, S1a[3] = {real(0), real(0), real(0)};
   real loss_acc = real(0), w_cur = real(0), w_old = real(0);
   real d0 = real(0), d1 = real(0), d2 = real(0), d3 = real(0);   // raw inverse depths of rows t, t-1, t-2, t-3
+  real wy_prev = real(0);                                          // edge weight wy of row q - 1
   real dsum_prev = real(0);
   int prev_q = -1;
   real* d_out = (real*)SD.d_invd + (size_t)b * plane;
@@ -378,7 +419,7 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
   real tap[12], wgt[8];
   auto start_row = [&](int row, real draw) {
     real dd = draw;
-    if (premap) { real ch; dd = premap_fork<real>(draw, (real)P.premap_lo, (real)P.premap_hi, ch); }
+    if (premap) { real ch; dd = premap_fork<real>(draw, K.premap_lo, K.premap_hi, ch); }
     const real D = rrcp(rmax(dd, real(1e-6)));                    // utils/depth.py:120
     const real fv = (real)reflect1(row, H);
     const real p0 = (A0[0] + A1[0] * fv) * D + mt[0];
@@ -386,32 +427,31 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
     const real p2 = (A0[2] + A1[2] * fv) * D + mt[2];
     const real iz = rrcp(rmax(p2, real(1e-5)));                   // camera.py:179
     const real ix = p0 * iz, iy = p1 * iz;
-    sample3_issue<real, img_t, PAD>(ctx, plane, H, W, ix, iy, wgt, tap);
+    sample3_issue<real, img_t, PAD>(ctx0, plane, H, W, ix, iy, wgt, tap);
     real* rs = ring + (row & 3) * kRing * 32;
     rs[6 * 32] = D;
     rs[7 * 32] = (p2 >= real(1e-5)) ? iz : -iz;                   // sign flags the clamp
     rs[8 * 32] = ix;
     rs[9 * 32] = iy;
   };
-  real ynx[3], mynx[3], qynx[3];
+  // prefetched operands of the next step: target row, pixel record (statistics + automask candidate)
+  real ynx[3], recn[kRec];
   real dnx = __ldg(invd + reflect1(r0 - 2, H) * W + su);
   real dpre = __ldg(invd + reflect1(r0 - 1, H) * W + su);
   {
     const int on = reflect1(r0 - 2, H) * W + su;
-    const int opn = min(max(r0 - 3, 0), H - 1) * W + su;
 #pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      ynx[c] = ldimg<real>(image + c * plane, on);
-      mynx[c] = __ldg(ymom + c * plane + opn);
-      qynx[c] = __ldg(ymom + (3 + c) * plane + opn);
-    }
+    for (int c = 0; c < 3; ++c) ynx[c] = ldimg<real>(img0 + c * plane, on);
+    load_rec(rec + (min(max(r0 - 3, 0), H - 1) * W + su) * kRec, recn);
   }
   start_row(r0 - 2, dnx);
 
   auto finalize_row = [&](int par) {      // context 0 adds the other contexts' parts and stores the row
     if (j == 0 && prev_q >= 0) {
       real tot = dsum_prev;
-      for (int jj = 1; jj < C; ++jj) tot += dpart_s[(par * C + jj) * 32 + lane];
+#pragma unroll
+      for (int jj = 1; jj < 8; ++jj)
+        if (jj < C) tot += dpart_s[(par * C + jj) * 32 + lane];
       d_out[prev_q * W + u] = tot;
     }
     prev_q = -1;
@@ -421,34 +461,25 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
     constexpr int PH = decltype(phc)::value, Q = (PH + 1) % 3, P1 = (PH + 2) % 3;
     const int p = t - 1, q = t - 2;
     const int par = t & 1;
-    // ---------------- loads with depth-independent addresses: prefetch row t + 1, late operands of t ----
+    // ---------------- operands prefetched one step ago; issue the prefetch of the next step -----------
     const bool p_real = (p >= 0) && (p < H) && col_real;
-    real yt[3], my[3], qy[3];
-    real idv = real_inf<real>(), wxq = real(0), wyq = real(0), wym = real(0), m = real(1);
-    int ids = 255;
+    real yt[3], rc[kRec];
+    real wxq = real(0), wyq = real(0), m = real(1);
     {
 #pragma unroll
-      for (int c = 0; c < 3; ++c) { yt[c] = ynx[c]; my[c] = mynx[c]; qy[c] = qynx[c]; }
+      for (int c = 0; c < 3; ++c) yt[c] = ynx[c];
+#pragma unroll
+      for (int k = 0; k < kRec; ++k) rc[k] = recn[k];
       d3 = d2; d2 = d1; d1 = d0;
       d0 = dnx;
       dnx = dpre;
       dpre = __ldg(invd + reflect1(t + 2, H) * W + su);
       const int on = reflect1(t + 1, H) * W + su;
-      const int opn = min(max(p + 1, 0), H - 1) * W + su;
 #pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        ynx[c] = ldimg<real>(image + c * plane, on);
-        mynx[c] = __ldg(ymom + c * plane + opn);
-        qynx[c] = __ldg(ymom + (3 + c) * plane + opn);
-      }
-      if (P.automask && p_real) { idv = __ldg(idval + p * W + u); ids = (int)__ldg(idsel + p * W + u); }
+      for (int c = 0; c < 3; ++c) ynx[c] = ldimg<real>(img0 + c * plane, on);
+      load_rec(rec + (min(max(p + 1, 0), H - 1) * W + su) * kRec, recn);
       if (RARE && maskp) m = p_real ? ldimg<real>(maskp, p * W + u) : real(0);
-      if (j == 0 && smooth) {
-        const int qc = min(max(q, 0), H - 1);
-        wxq = __ldg(wxy + qc * W + su);
-        wyq = __ldg(wxy + plane + qc * W + su);
-        wym = __ldg(wxy + plane + max(qc - 1, 0) * W + su);
-      }
+      if (j == 0 && smooth) load_pair(wxy + (min(max(q, 0), H - 1) * W + su) * 2, wxq, wyq);
     }
     // ---------------- finish the gather of row t (issued one step ago), start the one of row t + 1 ----
     {
@@ -472,7 +503,6 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
       }
     }
     // ---------------- SSIM + L1 at row p, candidate min across the contexts --------------------------
-    real coef[9];
     real F[9];
     {
       real ds = real(0), ls = real(0);
@@ -480,11 +510,11 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
       for (int c = 0; c < 3; ++c) {
         ds += ssim_dist_sums<real, true>(h[0][c * 3] + h[1][c * 3] + h[2][c * 3],
                                          h[0][c * 3 + 1] + h[1][c * 3 + 1] + h[2][c * 3 + 1],
-                                         h[0][c * 3 + 2] + h[1][c * 3 + 2] + h[2][c * 3 + 2], my[c], qy[c], C1, C2,
-                                         &coef[c * 3]);
+                                         h[0][c * 3 + 2] + h[1][c * 3 + 2] + h[2][c * 3 + 2], rc[c], rc[3 + c], K.C1,
+                                         K.C2, &F[c * 3]);
         ls += rabs(xr[P1][c] - yr[P1][c]);
       }
-      const real photo = ssim_w * (ds * r3) + k1 * ls;
+      const real photo = K.ssim_w3 * ds + K.k1 * ls;
       real best = photo * m;
       int sel = mycand;
       if (C > 1) {
@@ -492,22 +522,25 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
         __syncthreads();
         best = real_inf<real>();
         sel = 0;
-        for (int jj = 0; jj < C; ++jj) {
-          const real v = photo_s[(par * C + jj) * 32 + lane] * m;
-          if (v < best) { best = v; sel = P.automask ? 2 * jj : jj; }
+#pragma unroll
+        for (int jj = 0; jj < 8; ++jj) {
+          if (jj < C) {
+            const real v = photo_s[(par * C + jj) * 32 + lane] * m;
+            if (v < best) { best = v; sel = P.automask ? 2 * jj : jj; }
+          }
         }
       }
       if (P.automask && p_real) {
-        const real vi = idv * m;
-        const int ki = ids;
+        const real vi = rc[6] * m;
+        const int ki = (int)rc[7];
         if (vi < best || (vi == best && ki < sel)) { best = vi; sel = ki; }
       }
       w_old = w_cur;
-      w_cur = (p_real && sel == mycand) ? inv_count * m : real(0);
+      w_cur = (p_real && sel == mycand) ? K.inv_count * m : real(0);
       if (j == 0 && p_real && col_inner && p >= r0 && p < r1) loss_acc += best;
-      const real wf = w_cur * ssim_w * r3;
+      const real wf = w_cur * K.ssim_w3;
 #pragma unroll
-      for (int k = 0; k < 9; ++k) F[k] = (w_cur != real(0)) ? wf * coef[k] : real(0);
+      for (int k = 0; k < 9; ++k) F[k] *= wf;                      // the coefficients are always finite
     }
     finalize_row(par ^ 1);
     // ---------------- adjoint at row q ----------------------------------------------------------------
@@ -520,6 +553,7 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
       const bool q_ok = (q >= r0) && (q < r1) && col_inner;
       const real mv0 = (q == 1) ? real(2) : real(1), mv2 = (q == H - 2) ? real(2) : real(1);
       const real* rq = ring + (q & 3) * kRing * 32;
+      const real wk = w_old * K.k1;
       real gix = real(0), giy = real(0);
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
@@ -527,7 +561,7 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
         const real sb = mv0 * hF[PH][c * 3 + 1] + hF[Q][c * 3 + 1] + mv2 * hF[P1][c * 3 + 1];
         const real sc = mv0 * hF[PH][c * 3 + 2] + hF[Q][c * 3 + 2] + mv2 * hF[P1][c * 3 + 2];
         const real xq = xr[Q][c], yq = yr[Q][c];
-        const real dl = sa + xq * sb + yq * sc + (w_old * k1) * rsign(xq - yq);
+        const real dl = sa + xq * sb + yq * sc + signed_by(wk, xq - yq);
         gix += dl * rq[c * 32];
         giy += dl * rq[(3 + c) * 32];
       }
@@ -540,7 +574,7 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
       const real fq = (real)q;
       const real dD = (A0[0] + A1[0] * fq) * dp0 + (A0[1] + A1[1] * fq) * dp1 + (A0[2] + A1[2] * fq) * dp2;
       real chain = real(1), dd = d2;
-      if (premap) dd = premap_fork<real>(d2, (real)P.premap_lo, (real)P.premap_hi, chain);
+      if (premap) dd = premap_fork<real>(d2, K.premap_lo, K.premap_hi, chain);
       const real dphoto = (q_ok && dd >= real(1e-6)) ? -(D * D) * dD * chain : real(0);
       {
         const real e0 = dp0 * D, e1 = dp1 * D, e2 = dp2 * D;
@@ -553,12 +587,14 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
         if (smooth) {
           const real dl = shfl_up1(d2), dr = shfl_dn1(d2);
           const real wxl = shfl_up1(wxq);
+          const real cx = K.coef_x[s], cy = K.coef_y[s];
           real qq = real(0);
-          if (u + 1 < W) qq += coef_x * rsign(d2 - dr) * wxq;
-          if (u >= 1) qq -= coef_x * rsign(dl - d2) * wxl;
-          if (q + 1 < H) qq += coef_y * rsign(d2 - d1) * wyq;
-          if (q >= 1) qq -= coef_y * rsign(d3 - d2) * wym;
+          if (u + 1 < W) qq += signed_by(cx * wxq, d2 - dr);
+          if (u >= 1) qq -= signed_by(cx * wxl, dl - d2);
+          if (q + 1 < H) qq += signed_by(cy * wyq, d2 - d1);
+          if (q >= 1) qq -= signed_by(cy * wy_prev, d3 - d2);
           gs = qq * inv_m - cb;
+          wy_prev = wyq;
         }
         if (q_ok) {
           if (C > 1) { dsum_prev = dphoto + gs; prev_q = q; }
@@ -578,7 +614,6 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
   }
   if (C > 1) {
     __syncthreads();
-    // the loop ran ceil((chunk_h + 4) / 3) * 3 steps; the last one had parity of (last t)
     const int last_t = t0 + ((r1 + 1 - t0) / 3) * 3 + 2;
     finalize_row(last_t & 1);
   }
@@ -586,7 +621,7 @@ __global__ void __launch_bounds__(256) sweep_kernel(const SweepParams SP) {
   // ---- epilogue: pose partials (converted from the (u, v, 1) basis) and the loss partial -----------
   {
     SweepCam<real> cam;
-    sweep_cam<real>(cam, P, b, j, (real)SD.sf);
+    sweep_cam<real>(cam, P, b, j, K.sf[s]);
     const real fu = (real)su;
     real G[12];
 #pragma unroll
@@ -702,8 +737,7 @@ bool stream_eligible(const psfm_loss_cfg* cfg) {
 struct SweepPlan {
   int nsets;
   SweepSet sets[PSFM_MAX_SCALES];
-  size_t off_ymom[PSFM_MAX_SCALES], off_wxy[PSFM_MAX_SCALES], off_idval[PSFM_MAX_SCALES],
-      off_idsel[PSFM_MAX_SCALES];                                         // per scale (a set uses its first scale's)
+  size_t off_rec[PSFM_MAX_SCALES], off_wxy[PSFM_MAX_SCALES];                                         // per scale (a set uses its first scale's)
   size_t off_prep[PSFM_MAX_SCALES], off_stats[PSFM_MAX_SCALES], off_loss[PSFM_MAX_SCALES],
       off_pose[PSFM_MAX_SCALES];                                          // per scale
   int nunits[PSFM_MAX_SCALES];
@@ -763,10 +797,8 @@ static void make_plan(const psfm_loss_cfg* cfg, const psfm_loss_io* io, SweepPla
     const int minc = Hs < kMinChunk ? Hs : kMinChunk;
     const size_t worst = (size_t)cdiv(Ws, kInner) * cdiv(Hs, minc);
     const size_t pworst = (size_t)cdiv(Ws, kPrepInner) * cdiv(Hs, minc);
-    pl.off_ymom[s] = off;  off = al(off + px * 6 * rs);
+    pl.off_rec[s] = off;   off = al(off + px * kRec * rs);
     pl.off_wxy[s] = off;   off = al(off + px * 2 * rs);
-    pl.off_idval[s] = off; off = al(off + px * rs);
-    pl.off_idsel[s] = off; off = al(off + px);
     pl.off_prep[s] = off;  off = al(off + (size_t)cfg->B * pworst * kPrepVals * sizeof(double));
     pl.off_stats[s] = off; off = al(off + (size_t)cfg->B * 4 * rs);
     pl.off_loss[s] = off;  off = al(off + (size_t)cfg->B * worst * sizeof(double));
@@ -787,15 +819,40 @@ size_t stream_workspace_bytes(const psfm_loss_cfg* cfg) {
 
 void build_params(const psfm_loss_cfg* cfg, const psfm_loss_io* io, void* ws, LossParams& P);   // loss_kernels.cu
 
-template <typename real, typename img_t, int PAD, bool RARE>
-static cudaError_t launch_sweep(const SweepParams& SP, dim3 grid, int threads, size_t smem, cudaStream_t st) {
-  auto kern = sweep_kernel<real, img_t, PAD, RARE>;
+template <typename real>
+static void fill_consts(SweepConsts<real>& c, const LossParams& P, int s0) {
+  c.ssim_w3 = (real)P.ssim_w / real(3);
+  c.k1 = (real(1) - (real)P.ssim_w) / real(3);
+  c.C1 = (real)P.C1; c.C2 = (real)P.C2;
+  c.inv_count = (real)P.sc[s0].inv_count;
+  c.premap_lo = (real)P.premap_lo; c.premap_hi = (real)P.premap_hi;
+  c.pad_ = real(0);
+  for (int s = 0; s < PSFM_MAX_SCALES; ++s) {
+    c.coef_x[s] = s < P.n ? (real)P.sc[s].coef_x : real(0);
+    c.coef_y[s] = s < P.n ? (real)P.sc[s].coef_y : real(0);
+    c.sf[s] = s < P.n ? (real)P.sc[s].sf : real(1);
+  }
+}
+
+template <typename real, typename img_t, int PAD, bool RARE, int CT>
+static cudaError_t launch_sweep_ct(const SweepParams& SP, dim3 grid, int threads, size_t smem, cudaStream_t st) {
+  auto kern = sweep_kernel<real, img_t, PAD, RARE, CT>;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
   }
   kern<<<grid, threads, smem, st>>>(SP);
   return cudaSuccess;
+}
+
+// the common context counts get their own instantiation (unrolled candidate min, tighter launch bounds)
+template <typename real, typename img_t, int PAD, bool RARE>
+static cudaError_t launch_sweep(const SweepParams& SP, dim3 grid, int threads, size_t smem, cudaStream_t st) {
+  if (!RARE) {
+    if (SP.P.C == 2) return launch_sweep_ct<real, img_t, PAD, RARE, 2>(SP, grid, threads, smem, st);
+    if (SP.P.C == 4) return launch_sweep_ct<real, img_t, PAD, RARE, 4>(SP, grid, threads, smem, st);
+  }
+  return launch_sweep_ct<real, img_t, PAD, RARE, 0>(SP, grid, threads, smem, st);
 }
 
 template <typename real, typename img_t>
@@ -817,10 +874,10 @@ static cudaError_t run_sweep(const psfm_loss_cfg* cfg, const psfm_loss_io* io, v
   for (int i = 0; i < pl.nsets; ++i) {
     SP.set = pl.sets[i];
     const int s0 = SP.set.scale[0];
-    SP.set.ymom = w + pl.off_ymom[s0];
+    SP.set.rec = w + pl.off_rec[s0];
     SP.set.wxy = w + pl.off_wxy[s0];
-    SP.set.idval = w + pl.off_idval[s0];
-    SP.set.idsel = (uint8_t*)(w + pl.off_idsel[s0]);
+    fill_consts(SP.cf, SP.P, s0);
+    fill_consts(SP.cd, SP.P, s0);
     const SweepSet& S = SP.set;
     {
       ProfScope ps(st, kTagFwd, cfg->smooth_w > 0.0 ? 2 : 1);
@@ -865,3 +922,4 @@ cudaError_t loss_stream_dispatch(const psfm_loss_cfg* cfg, const psfm_loss_io* i
 }
 
 }  // namespace psfm
+

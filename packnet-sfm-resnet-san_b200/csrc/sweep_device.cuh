@@ -23,6 +23,14 @@ __device__ __forceinline__ float rrcp(float x) {
   return fmaf(r, e, r);
 }
 
+// reciprocal for the SSIM denominator: MUFU.RCP alone (1 ulp) is ample for a value in [0, 1]
+__device__ __forceinline__ double rrcp_fast(double x) { return 1.0 / x; }
+__device__ __forceinline__ float rrcp_fast(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
 template <typename real> __device__ __forceinline__ real shfl_up1(real v) { return __shfl_up_sync(kFull, v, 1); }
 template <typename real> __device__ __forceinline__ real shfl_dn1(real v) { return __shfl_down_sync(kFull, v, 1); }
 
@@ -47,14 +55,18 @@ __device__ __forceinline__ real ssim_dist_sums(real Sx, real Sxx, real Sxy, real
   const real v1 = real(2) * (exy - mxy) + C2;
   const real b1 = mx2 + (my * my + C1);
   const real v2 = (exx - mx2) + qy;
-  const real inv = rrcp(b1 * v2);
+  const real inv = rrcp_fast(b1 * v2);
   const real ssim = (a1 * v1) * inv;
   const real dist = real(0.5) - real(0.5) * ssim;
   if (GRAD) {
-    // d dist = -0.5 d ssim inside the clamp range, 0 outside
-    const real act = (dist >= real(0) && dist <= real(1)) ? real(-0.5) * r9 * inv : real(0);
-    coef[0] = act * (real(2) * my * (v1 - a1) - ssim * real(2) * mx * (v2 - b1));
-    coef[1] = act * (real(-2) * ssim * b1);
+    // d dist = -0.5 d ssim inside the clamp range, 0 outside.  Outside (which includes a non-finite
+    // ssim from a degenerate window of a padding row) every factor is replaced by a finite one, so
+    // the coefficients are always finite and can be scaled by a zero selection weight.
+    const bool in = (dist >= real(0)) && (dist <= real(1));
+    const real act = in ? real(-0.5) * r9 * inv : real(0);
+    const real ss = in ? ssim : real(0);
+    coef[0] = act * (real(2) * my * (v1 - a1) - ss * real(2) * mx * (v2 - b1));
+    coef[1] = act * (real(-2) * ss * b1);
     coef[2] = act * (real(2) * a1);
   }
   return rmin(rmax(dist, real(0)), real(1));
