@@ -360,6 +360,9 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256) sweep_kernel(const SweepPa
   const ScaleDesc& SD = P.sc[s];
   const img_t* img0 = (const img_t*)SD.image + (size_t)b * 3 * plane;
   const img_t* ctx0 = (const img_t*)SD.ctx[j] + (size_t)b * 3 * plane;
+  // per-plane base pointers, made opaque so that every load is one IMAD.WIDE off a 32-bit pixel offset
+  const img_t *img1 = img0 + plane, *img2 = img0 + 2 * plane, *ctx1 = ctx0 + plane, *ctx2 = ctx0 + 2 * plane;
+  asm volatile("" : "+l"(img0), "+l"(img1), "+l"(img2), "+l"(ctx0), "+l"(ctx1), "+l"(ctx2));
   const real* invd = (const real*)SD.invd + (size_t)b * plane;
   const real* rec = (const real*)S.rec + (size_t)b * plane * kRec;
   const real* wxy = (const real*)S.wxy + (size_t)b * plane * 2;
@@ -427,7 +430,7 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256) sweep_kernel(const SweepPa
     const real p2 = (A0[2] + A1[2] * fv) * D + mt[2];
     const real iz = rrcp(rmax(p2, real(1e-5)));                   // camera.py:179
     const real ix = p0 * iz, iy = p1 * iz;
-    sample3_issue<real, img_t, PAD>(ctx0, plane, H, W, ix, iy, wgt, tap);
+    sample3_issue<real, img_t, PAD>(ctx0, ctx1, ctx2, H, W, ix, iy, wgt, tap);
     real* rs = ring + (row & 3) * kRing * 32;
     rs[6 * 32] = D;
     rs[7 * 32] = (p2 >= real(1e-5)) ? iz : -iz;                   // sign flags the clamp
@@ -441,7 +444,7 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256) sweep_kernel(const SweepPa
   {
     const int on = reflect1(r0 - 2, H) * W + su;
 #pragma unroll
-    for (int c = 0; c < 3; ++c) ynx[c] = ldimg<real>(img0 + c * plane, on);
+    ynx[0] = ldimg<real>(img0, on); ynx[1] = ldimg<real>(img1, on); ynx[2] = ldimg<real>(img2, on);
     load_rec(rec + (min(max(r0 - 3, 0), H - 1) * W + su) * kRec, recn);
   }
   start_row(r0 - 2, dnx);
@@ -476,7 +479,7 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256) sweep_kernel(const SweepPa
       dpre = __ldg(invd + reflect1(t + 2, H) * W + su);
       const int on = reflect1(t + 1, H) * W + su;
 #pragma unroll
-      for (int c = 0; c < 3; ++c) ynx[c] = ldimg<real>(img0 + c * plane, on);
+      ynx[0] = ldimg<real>(img0, on); ynx[1] = ldimg<real>(img1, on); ynx[2] = ldimg<real>(img2, on);
       load_rec(rec + (min(max(p + 1, 0), H - 1) * W + su) * kRec, recn);
       if (RARE && maskp) m = p_real ? ldimg<real>(maskp, p * W + u) : real(0);
       if (j == 0 && smooth) load_pair(wxy + (min(max(q, 0), H - 1) * W + su) * 2, wxq, wyq);

@@ -82,7 +82,8 @@ __device__ __forceinline__ real ssim_dist_sums(real Sx, real Sxx, real Sxy, real
 //   tap[c * 4 + {0,1,2,3}] = {v00, v01, v10, v11} of channel c
 // ------------------------------------------------------------------------------------------
 template <typename real, typename img_t, int PAD>
-__device__ __forceinline__ void sample3_issue(const img_t* __restrict__ img, int plane, int H, int W, real ix, real iy,
+__device__ __forceinline__ void sample3_issue(const img_t* __restrict__ p0, const img_t* __restrict__ p1,
+                                              const img_t* __restrict__ p2, int H, int W, real ix, real iy,
                                               real* wgt, real* tap) {
   real mx = real(1), my = real(1);
   if (PAD == PSFM_PAD_BORDER) {
@@ -109,11 +110,11 @@ __device__ __forceinline__ void sample3_issue(const img_t* __restrict__ img, int
   const int yc0 = min(max(y0, 0), H - 1), yc1 = min(max(y0 + 1, 0), H - 1);
   const int r0 = yc0 * W, r1 = yc1 * W;
   const int o00 = r0 + xc0, o01 = r0 + xc1, o10 = r1 + xc0, o11 = r1 + xc1;
+  const img_t* pl[3] = {p0, p1, p2};
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
-    const img_t* p = img + c * plane;
-    tap[c * 4 + 0] = ldimg<real>(p, o00); tap[c * 4 + 1] = ldimg<real>(p, o01);
-    tap[c * 4 + 2] = ldimg<real>(p, o10); tap[c * 4 + 3] = ldimg<real>(p, o11);
+    tap[c * 4 + 0] = ldimg<real>(pl[c], o00); tap[c * 4 + 1] = ldimg<real>(pl[c], o01);
+    tap[c * 4 + 2] = ldimg<real>(pl[c], o10); tap[c * 4 + 3] = ldimg<real>(pl[c], o11);
   }
 }
 
