@@ -147,6 +147,70 @@ int psfm_warp_backward(int B, int H, int W, int img_dtype, int real_dtype, int p
 int psfm_resize(int N, int Hi, int Wi, int Ho, int Wo, int dtype, int mode, const void* in, void* out,
                 void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Building-block operators: the reference functions of this path for callers that use them
+ * directly (not through MultiViewPhotometricLoss.forward).  All tensors are contiguous and of the
+ * arithmetic type `dt` (PSFM_F32 | PSFM_F64).  Scratch: psfm_block_workspace_bytes(B, N) bytes,
+ * N = elements per batch item the reduction runs over.
+ * ------------------------------------------------------------------------------------------- */
+size_t psfm_block_workspace_bytes(int B, size_t N);
+
+/* Camera.reconstruct (geometry/camera.py:111-147): out[B,3,H,W] = Twc (Kinv (u,v,1) * depth);
+ * Twc = [B,4,4] world<-camera matrix or NULL for frame 'c' / an identity pose.
+ * Backward: d_depth[B,1,H,W] from grad_out[B,3,H,W]. */
+int psfm_reconstruct(int B, int H, int W, int dt, const void* depth, const void* K, const void* Twc, void* out,
+                     void* stream);
+int psfm_reconstruct_backward(int B, int H, int W, int dt, const void* K, const void* Twc, const void* grad_out,
+                              void* d_depth, void* stream);
+
+/* Camera.project (geometry/camera.py:149-190): out[B,H,W,2] = normalised coordinates of
+ * K (Tcw X), Z clamped at 1e-5; Tcw = [B,4,4] or NULL.  Backward: dX[B,3,H,W] and, when Tcw and
+ * d_Tcw are given, d_Tcw[B,4,4] (rows 0-2). */
+int psfm_project(int B, int H, int W, int dt, const void* X, const void* K, const void* Tcw, void* out, void* stream);
+int psfm_project_backward(int B, int H, int W, int dt, const void* X, const void* K, const void* Tcw,
+                          const void* grad_out, void* dX, void* d_Tcw, void* workspace, size_t workspace_bytes,
+                          void* stream);
+
+/* Pose.transform_points (geometry/pose.py:80-86): out[B,3,N] = R X + t.  Backward: dX, d_mat[B,4,4]. */
+int psfm_transform_points(int B, size_t N, int dt, const void* mat, const void* X, void* out, void* stream);
+int psfm_transform_points_backward(int B, size_t N, int dt, const void* mat, const void* X, const void* grad_out,
+                                   void* dX, void* d_mat, void* workspace, size_t workspace_bytes, void* stream);
+
+/* SSIM / calc_photometric_loss (losses/multiview_photometric_loss.py:15-54,199-267) of x, y [B,3,H,W]:
+ *   mode 0 SSIM index [B,3,H,W]; mode 1 clamp((1-SSIM)/2,0,1) [B,3,H,W];
+ *   mode 2 ssim_w * mean_c(mode 1) + (1-ssim_w) * mean_c|x-y| [B,1,H,W]; mode 3 |x-y| [B,3,H,W].
+ * Backward: dx (and dy when not NULL) from grad_out of the output's shape. */
+int psfm_photometric_map(int B, int H, int W, int dt, int mode, double ssim_w, double C1, double C2, const void* x,
+                         const void* y, void* out, void* stream);
+int psfm_photometric_map_backward(int B, int H, int W, int dt, int mode, double ssim_w, double C1, double C2,
+                                  const void* x, const void* y, const void* grad_out, void* dx, void* dy, void* stream);
+
+/* inv_depths_normalize (utils/depth.py:146-162): out = d / max(mean over the N elements of each
+ * batch item, 1e-6); mean_out[B] is kept for the backward. */
+int psfm_normalize(int B, size_t N, int dt, const void* d, void* out, void* mean_out, void* workspace,
+                   size_t workspace_bytes, void* stream);
+int psfm_normalize_backward(int B, size_t N, int dt, const void* d, const void* mean, const void* grad_out, void* dd,
+                            void* workspace, size_t workspace_bytes, void* stream);
+
+/* calc_smoothness maps (utils/depth.py:165-198, utils/image.py:85-113): sx[B,1,H,W-1], sy[B,1,H-1,W]
+ * from normalised inverse depths dn[B,1,H,W] and image[B,3,H,W].  Backward w.r.t. dn. */
+int psfm_smoothness_maps(int B, int H, int W, int dt, const void* dn, const void* image, void* sx, void* sy,
+                         void* stream);
+int psfm_smoothness_maps_backward(int B, int H, int W, int dt, const void* image, const void* gsx, const void* gsy,
+                                  void* ddn, void* stream);
+
+/* reduce_photometric_loss for one scale (losses/multiview_photometric_loss.py:269-297): K candidates
+ * (host array of device pointers), each [B,Cg,H,W]; op PSFM_REDUCE_MIN | PSFM_REDUCE_MEAN; out real[1];
+ * argmin int32[B,H,W] (min only).  Backward writes d_cands[k] for upstream grad_out real[1]. */
+int psfm_reduce_candidates(int K, int B, int Cg, int H, int W, int dt, int op, const void* const* cands, void* out,
+                           int32_t* argmin, void* workspace, size_t workspace_bytes, void* stream);
+int psfm_reduce_candidates_backward(int K, int B, int Cg, int H, int W, int dt, int op, const int32_t* argmin,
+                                    const void* grad_out, void* const* d_cands, void* stream);
+
+/* mean |x| over n elements (calc_smoothness_loss, :320-322) and its backward. */
+int psfm_abs_mean(size_t n, int dt, const void* x, void* out, void* workspace, size_t workspace_bytes, void* stream);
+int psfm_abs_mean_backward(size_t n, int dt, const void* x, const void* grad_out, void* dx, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

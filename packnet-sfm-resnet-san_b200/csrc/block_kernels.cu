@@ -1,0 +1,721 @@
+// block_kernels.cu -- the reference's building-block functions of the photometric-loss path as
+// stand-alone operators (each with its backward), for callers that use them directly instead of
+// MultiViewPhotometricLoss.forward:
+//   reconstruct / project      Camera.reconstruct, Camera.project        (geometry/camera.py:111-190)
+//   transform_points           Pose.transform_points                      (geometry/pose.py:80-86)
+//   ssim / photometric map     SSIM, calc_photometric_loss                (losses/multiview_photometric_loss.py:15-54,199-267)
+//   normalize / smoothness     inv_depths_normalize, calc_smoothness      (utils/depth.py:146-198, utils/image.py:85-113)
+//   reductions                 reduce_photometric_loss, |x|.mean()        (losses/...:269-297,301-327)
+// All tensors are contiguous `real` (fp32 or fp64).  Reductions are deterministic (block partials
+// in fixed slots + a fixed-order finish).
+#include <cuda_runtime.h>
+#include "psfm_device.cuh"
+#include "profile.h"
+
+namespace psfm {
+
+constexpr int kBT = 256;
+
+static inline unsigned nblk_for(size_t n) { return (unsigned)((n + kBT - 1) / kBT); }
+
+// lifting matrix of the reference (`Kinv`, camera.py:73-81) of batch item b
+template <typename real> __device__ __forceinline__ void load_kinv(const real* K, int b, real* ki) {
+#pragma unroll
+  for (int i = 0; i < 9; ++i) ki[i] = K[b * 9 + i];
+  const real fx = ki[0], fy = ki[4], cx = ki[2], cy = ki[5];
+  ki[0] = real(1) / fx;
+  ki[4] = real(1) / fy;
+  ki[2] = real(-1) * cx / fx;
+  ki[5] = real(-1) * cy / fy;
+}
+
+// [B, nblk, 12] partials -> d mat [B,4,4] (rows 0-2), fixed order
+template <typename real>
+__global__ void __launch_bounds__(32) mat_finish_kernel(const real* part, int nblk, real* d_mat) {
+  const int b = blockIdx.x, t = threadIdx.x;
+  if (t < 12) {
+    double a = 0.0;
+    for (int i = 0; i < nblk; ++i) a += (double)part[((size_t)b * nblk + i) * 12 + t];
+    d_mat[(size_t)b * 16 + t] = (real)a;
+  } else if (t < 16) {
+    d_mat[(size_t)b * 16 + t] = real(0);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Camera.reconstruct: X = [R|t] (Kinv (u, v, 1) * depth), [R|t] = Twc rows or identity when null
+// ------------------------------------------------------------------------------------------
+template <typename real>
+__global__ void __launch_bounds__(kBT) reconstruct_kernel(int H, int W, const real* depth, const real* K,
+                                                          const real* Twc, real* out) {
+  const int b = blockIdx.y;
+  const size_t plane = (size_t)H * W, i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  if (i >= plane) return;
+  real ki[9];
+  load_kinv<real>(K, b, ki);
+  const real u = (real)(int)(i % W), v = (real)(int)(i / W), d = depth[b * plane + i];
+  real X[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) X[k] = (ki[k * 3] * u + ki[k * 3 + 1] * v + ki[k * 3 + 2]) * d;
+  if (Twc) {
+    const real* T = Twc + (size_t)b * 16;
+    const real x0 = X[0], x1 = X[1], x2 = X[2];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) X[k] = T[k * 4] * x0 + T[k * 4 + 1] * x1 + T[k * 4 + 2] * x2 + T[k * 4 + 3];
+  }
+#pragma unroll
+  for (int k = 0; k < 3; ++k) out[((size_t)b * 3 + k) * plane + i] = X[k];
+}
+
+template <typename real>
+__global__ void __launch_bounds__(kBT) reconstruct_bwd_kernel(int H, int W, const real* K, const real* Twc,
+                                                              const real* gout, real* d_depth) {
+  const int b = blockIdx.y;
+  const size_t plane = (size_t)H * W, i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  if (i >= plane) return;
+  real ki[9];
+  load_kinv<real>(K, b, ki);
+  const real u = (real)(int)(i % W), v = (real)(int)(i / W);
+  real g[3], ray[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    g[k] = gout[((size_t)b * 3 + k) * plane + i];
+    ray[k] = ki[k * 3] * u + ki[k * 3 + 1] * v + ki[k * 3 + 2];
+  }
+  if (Twc) {   // d/d Xc = R^T g
+    const real* T = Twc + (size_t)b * 16;
+    const real g0 = g[0], g1 = g[1], g2 = g[2];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) g[k] = T[k] * g0 + T[4 + k] * g1 + T[8 + k] * g2;
+  }
+  d_depth[b * plane + i] = ray[0] * g[0] + ray[1] * g[1] + ray[2] * g[2];
+}
+
+// ------------------------------------------------------------------------------------------
+// Camera.project: p = K ([R|t] X); Z = max(p2, 1e-5); out[b, v, u] = (2 (p0/Z)/(W-1) - 1, 2 (p1/Z)/(H-1) - 1)
+// ------------------------------------------------------------------------------------------
+template <typename real>
+__device__ __forceinline__ void project_point(const real* K, const real* Tcw, int b, const real* X, real* Xc, real* p) {
+  if (Tcw) {
+    const real* T = Tcw + (size_t)b * 16;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) Xc[k] = T[k * 4] * X[0] + T[k * 4 + 1] * X[1] + T[k * 4 + 2] * X[2] + T[k * 4 + 3];
+  } else {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) Xc[k] = X[k];
+  }
+  const real* Kb = K + b * 9;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) p[k] = Kb[k * 3] * Xc[0] + Kb[k * 3 + 1] * Xc[1] + Kb[k * 3 + 2] * Xc[2];
+}
+
+template <typename real>
+__global__ void __launch_bounds__(kBT) project_kernel(int H, int W, const real* X, const real* K, const real* Tcw,
+                                                      real* out) {
+  const int b = blockIdx.y;
+  const size_t plane = (size_t)H * W, i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  if (i >= plane) return;
+  real x[3], Xc[3], p[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) x[k] = X[((size_t)b * 3 + k) * plane + i];
+  project_point<real>(K, Tcw, b, x, Xc, p);
+  const real Z = rmax(p[2], real(1e-5));
+  out[(b * plane + i) * 2] = real(2) * (p[0] / Z) / real(W - 1) - real(1);
+  out[(b * plane + i) * 2 + 1] = real(2) * (p[1] / Z) / real(H - 1) - real(1);
+}
+
+template <typename real>
+__global__ void __launch_bounds__(kBT) project_bwd_kernel(int H, int W, const real* X, const real* K, const real* Tcw,
+                                                          const real* gout, real* dX, real* part) {
+  const int b = blockIdx.y;
+  const size_t plane = (size_t)H * W, i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  __shared__ real scratch[12 * (kBT / 32)];
+  real acc[12];
+#pragma unroll
+  for (int k = 0; k < 12; ++k) acc[k] = real(0);
+  if (i < plane) {
+    real x[3], Xc[3], p[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) x[k] = X[((size_t)b * 3 + k) * plane + i];
+    project_point<real>(K, Tcw, b, x, Xc, p);
+    const real Z = rmax(p[2], real(1e-5));
+    const real gxn = gout[(b * plane + i) * 2], gyn = gout[(b * plane + i) * 2 + 1];
+    real dp[3];
+    dp[0] = gxn * real(2) / real(W - 1) / Z;
+    dp[1] = gyn * real(2) / real(H - 1) / Z;
+    dp[2] = (p[2] >= real(1e-5)) ? -(dp[0] * p[0] + dp[1] * p[1]) / Z : real(0);
+    const real* Kb = K + b * 9;
+    real dXc[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) dXc[k] = Kb[k] * dp[0] + Kb[3 + k] * dp[1] + Kb[6 + k] * dp[2];
+    if (Tcw) {
+      const real* T = Tcw + (size_t)b * 16;
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        dX[((size_t)b * 3 + k) * plane + i] = T[k] * dXc[0] + T[4 + k] * dXc[1] + T[8 + k] * dXc[2];
+        acc[k * 4] = dXc[k] * x[0]; acc[k * 4 + 1] = dXc[k] * x[1]; acc[k * 4 + 2] = dXc[k] * x[2]; acc[k * 4 + 3] = dXc[k];
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) dX[((size_t)b * 3 + k) * plane + i] = dXc[k];
+    }
+  }
+  if (part) {
+    block_reduce<real, 12>(acc, scratch);
+    if (threadIdx.x < 12) part[((size_t)b * gridDim.x + blockIdx.x) * 12 + threadIdx.x] = acc[threadIdx.x];
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Pose.transform_points: out = R X + t on [B,3,N]
+// ------------------------------------------------------------------------------------------
+template <typename real>
+__global__ void __launch_bounds__(kBT) transform_kernel(size_t N, const real* mat, const real* X, real* out) {
+  const int b = blockIdx.y;
+  const size_t i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  if (i >= N) return;
+  const real* T = mat + (size_t)b * 16;
+  const real x0 = X[((size_t)b * 3) * N + i], x1 = X[((size_t)b * 3 + 1) * N + i], x2 = X[((size_t)b * 3 + 2) * N + i];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) out[((size_t)b * 3 + k) * N + i] = T[k * 4] * x0 + T[k * 4 + 1] * x1 + T[k * 4 + 2] * x2 + T[k * 4 + 3];
+}
+
+template <typename real>
+__global__ void __launch_bounds__(kBT) transform_bwd_kernel(size_t N, const real* mat, const real* X, const real* gout,
+                                                            real* dX, real* part) {
+  const int b = blockIdx.y;
+  const size_t i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  __shared__ real scratch[12 * (kBT / 32)];
+  real acc[12];
+#pragma unroll
+  for (int k = 0; k < 12; ++k) acc[k] = real(0);
+  if (i < N) {
+    const real* T = mat + (size_t)b * 16;
+    real g[3], x[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { g[k] = gout[((size_t)b * 3 + k) * N + i]; x[k] = X[((size_t)b * 3 + k) * N + i]; }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      dX[((size_t)b * 3 + k) * N + i] = T[k] * g[0] + T[4 + k] * g[1] + T[8 + k] * g[2];
+      acc[k * 4] = g[k] * x[0]; acc[k * 4 + 1] = g[k] * x[1]; acc[k * 4 + 2] = g[k] * x[2]; acc[k * 4 + 3] = g[k];
+    }
+  }
+  block_reduce<real, 12>(acc, scratch);
+  if (threadIdx.x < 12) part[((size_t)b * gridDim.x + blockIdx.x) * 12 + threadIdx.x] = acc[threadIdx.x];
+}
+
+// ------------------------------------------------------------------------------------------
+// SSIM (3x3, reflection padding) and the photometric map.
+//   mode 0: SSIM index            [B,3,H,W]   (free function SSIM, losses/...:15-54)
+//   mode 1: clamp((1-SSIM)/2,0,1) [B,3,H,W]   (method SSIM, :199-216)
+//   mode 2: ssim_w * mean_c(mode 1) + (1 - ssim_w) * mean_c |x - y|   [B,1,H,W]   (:236-245)
+//   mode 3: |x - y|               [B,3,H,W]   (ssim_loss_weight == 0, :247)
+// ------------------------------------------------------------------------------------------
+template <typename real> struct Win { real sx, sy, sxx, syy, sxy; };
+
+template <typename real>
+__device__ __forceinline__ Win<real> window_sums(const real* x, const real* y, int H, int W, int v, int u) {
+  Win<real> w = {real(0), real(0), real(0), real(0), real(0)};
+#pragma unroll
+  for (int dy = -1; dy <= 1; ++dy)
+#pragma unroll
+    for (int dx = -1; dx <= 1; ++dx) {
+      const size_t o = (size_t)reflect1(v + dy, H) * W + reflect1(u + dx, W);
+      const real a = x[o], b = y[o];
+      w.sx += a; w.sy += b; w.sxx += a * a; w.syy += b * b; w.sxy += a * b;
+    }
+  return w;
+}
+
+// value f (SSIM index, or its clamped distance when `dist`) and df / d(sum x, sum x^2, sum xy)
+template <typename real>
+__device__ __forceinline__ real ssim_value_grad(const Win<real>& w, real C1, real C2, bool dist, real* c) {
+  const real r9 = real(1) / real(9);
+  const real mx = w.sx * r9, my = w.sy * r9, exx = w.sxx * r9, eyy = w.syy * r9, exy = w.sxy * r9;
+  const real sx = exx - mx * mx, sy = eyy - my * my, sxy = exy - mx * my;
+  const real a1 = real(2) * mx * my + C1, v1 = real(2) * sxy + C2;
+  const real b1 = mx * mx + my * my + C1, v2 = sx + sy + C2;
+  const real inv = real(1) / (b1 * v2);
+  const real ssim = (a1 * v1) * inv;
+  real k = r9;
+  real val = ssim;
+  if (dist) {
+    const real d = (real(1) - ssim) / real(2);
+    k = (d >= real(0) && d <= real(1)) ? real(-0.5) * r9 : real(0);
+    val = rmin(rmax(d, real(0)), real(1));
+  }
+  c[0] = k * (real(2) * my * (v1 - a1) * inv - ssim * real(2) * mx * (v2 - b1) * inv);
+  c[1] = k * (-ssim * b1 * inv);
+  c[2] = k * (real(2) * a1 * inv);
+  return val;
+}
+
+template <typename real>
+__global__ void __launch_bounds__(kBT) photo_map_kernel(int H, int W, int mode, real ssim_w, real C1, real C2,
+                                                        const real* x, const real* y, real* out) {
+  const int b = blockIdx.y;
+  const size_t plane = (size_t)H * W, i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  if (i >= plane) return;
+  const int v = (int)(i / W), u = (int)(i % W);
+  real ds = real(0), ls = real(0);
+#pragma unroll
+  for (int ch = 0; ch < 3; ++ch) {
+    const real* xc = x + ((size_t)b * 3 + ch) * plane;
+    const real* yc = y + ((size_t)b * 3 + ch) * plane;
+    const real l1 = rabs(xc[i] - yc[i]);
+    real val = real(0), c[3];
+    if (mode != 3) val = ssim_value_grad<real>(window_sums<real>(xc, yc, H, W, v, u), C1, C2, mode != 0, c);
+    if (mode == 3) out[((size_t)b * 3 + ch) * plane + i] = l1;
+    else if (mode != 2) out[((size_t)b * 3 + ch) * plane + i] = val;
+    ds += val;
+    ls += l1;
+  }
+  if (mode == 2) out[b * plane + i] = ssim_w * (ds / real(3)) + (real(1) - ssim_w) * (ls / real(3));
+}
+
+// number of window offsets d in {-1,0,1} with reflect(p + d) == q
+__device__ __forceinline__ int reflect_mult(int p, int q, int n) {
+  int m = 0;
+#pragma unroll
+  for (int d = -1; d <= 1; ++d) m += (reflect1(p + d, n) == q) ? 1 : 0;
+  return m;
+}
+
+// d loss / d x (and / d y) of the maps above given gout (3 channels for modes 0, 1, 3; 1 channel for mode 2)
+template <typename real>
+__global__ void __launch_bounds__(kBT) photo_map_bwd_kernel(int H, int W, int mode, real ssim_w, real C1, real C2,
+                                                            const real* x, const real* y, const real* gout, real* dx,
+                                                            real* dy) {
+  const int b = blockIdx.y;
+  const size_t plane = (size_t)H * W, i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  if (i >= plane) return;
+  const int v = (int)(i / W), u = (int)(i % W);
+#pragma unroll
+  for (int ch = 0; ch < 3; ++ch) {
+    const real* xc = x + ((size_t)b * 3 + ch) * plane;
+    const real* yc = y + ((size_t)b * 3 + ch) * plane;
+    const real* g = (mode == 2) ? gout + b * plane : gout + ((size_t)b * 3 + ch) * plane;
+    const real xq = xc[i], yq = yc[i];
+    real ax = real(0), ay = real(0);
+    if (mode != 3) {
+      const real scale = (mode == 2) ? ssim_w / real(3) : real(1);
+      for (int pv = v - 1; pv <= v + 1; ++pv) {
+        if (pv < 0 || pv >= H) continue;
+        const int mv = reflect_mult(pv, v, H);
+        for (int pu = u - 1; pu <= u + 1; ++pu) {
+          if (pu < 0 || pu >= W) continue;
+          const int m = mv * reflect_mult(pu, u, W);
+          if (m == 0) continue;
+          const real w = g[(size_t)pv * W + pu] * scale * (real)m;
+          const Win<real> win = window_sums<real>(xc, yc, H, W, pv, pu);
+          real c[3];
+          ssim_value_grad<real>(win, C1, C2, mode != 0, c);
+          ax += w * (c[0] + real(2) * xq * c[1] + yq * c[2]);
+          if (dy) {
+            const Win<real> sw = {win.sy, win.sx, win.syy, win.sxx, win.sxy};
+            ssim_value_grad<real>(sw, C1, C2, mode != 0, c);
+            ay += w * (c[0] + real(2) * yq * c[1] + xq * c[2]);
+          }
+        }
+      }
+    }
+    if (mode >= 2) {
+      const real l = (mode == 2) ? g[i] * (real(1) - ssim_w) / real(3) : g[i];
+      const real s = rsign(xq - yq);
+      ax += l * s;
+      ay -= l * s;
+    }
+    dx[((size_t)b * 3 + ch) * plane + i] = ax;
+    if (dy) dy[((size_t)b * 3 + ch) * plane + i] = ay;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// deterministic per-batch-item sums: part[b][blk] = sum over the block's elements of x (* y),
+// then a fixed-order finish.  op 0: x, op 1: x * y, op 2: |x|.
+// ------------------------------------------------------------------------------------------
+template <typename real>
+__global__ void __launch_bounds__(kBT) rowsum_kernel(size_t N, int op, const real* x, const real* y, double* part) {
+  const int b = blockIdx.y;
+  const size_t i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  __shared__ real scratch[kBT / 32];
+  real v[1] = {real(0)};
+  if (i < N) {
+    const real a = x[b * N + i];
+    v[0] = op == 0 ? a : (op == 1 ? a * y[b * N + i] : rabs(a));
+  }
+  block_reduce<real, 1>(v, scratch);
+  if (threadIdx.x == 0) part[(size_t)b * gridDim.x + blockIdx.x] = (double)v[0];
+}
+
+// out[b] = scale * sum_blk part[b][blk]   (one block per b; when total != 0 a single block sums all b)
+template <typename real>
+__global__ void __launch_bounds__(256) rowsum_finish_kernel(const double* part, int nblk, double scale, real* out) {
+  __shared__ double sh[256];
+  const int b = blockIdx.x;
+  double a = 0.0;
+  for (int i = threadIdx.x; i < nblk; i += 256) a += part[(size_t)b * nblk + i];
+  sh[threadIdx.x] = a;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) out[b] = (real)(sh[0] * scale);
+}
+
+// inv_depths_normalize (utils/depth.py:146-162): out = d / max(mean_b, 1e-6)
+template <typename real>
+__global__ void __launch_bounds__(kBT) normalize_kernel(size_t N, const real* d, const real* mean, real* out) {
+  const int b = blockIdx.y;
+  const size_t i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  if (i < N) out[b * N + i] = d[b * N + i] / rmax(mean[b], real(1e-6));
+}
+
+// d d = g / m - [mean >= 1e-6] * dot_b / (N m^2),  dot_b = sum_i g_i d_i
+template <typename real>
+__global__ void __launch_bounds__(kBT) normalize_bwd_kernel(size_t N, const real* g, const real* mean, const real* dot,
+                                                            real* dd) {
+  const int b = blockIdx.y;
+  const size_t i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  if (i >= N) return;
+  const real m = rmax(mean[b], real(1e-6));
+  const real c = (mean[b] >= real(1e-6)) ? dot[b] / ((real)N * m * m) : real(0);
+  dd[b * N + i] = g[b * N + i] / m - c;
+}
+
+// calc_smoothness maps (utils/depth.py:165-198): sx [B,1,H,W-1], sy [B,1,H-1,W] from the normalised
+// inverse depth dn [B,1,H,W] and the image [B,3,H,W]
+template <typename real>
+__device__ __forceinline__ real edge_weight(const real* img, size_t plane, size_t o, size_t o2) {
+  real ig = real(0);
+#pragma unroll
+  for (int c = 0; c < 3; ++c) ig += rabs(img[c * plane + o] - img[c * plane + o2]);
+  return rexp(-(ig / real(3)));
+}
+
+template <typename real>
+__global__ void __launch_bounds__(kBT) smooth_maps_kernel(int H, int W, const real* dn, const real* img, real* sx,
+                                                          real* sy) {
+  const int b = blockIdx.y;
+  const size_t plane = (size_t)H * W, i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  if (i >= plane) return;
+  const int v = (int)(i / W), u = (int)(i % W);
+  const real* d = dn + b * plane;
+  const real* im = img + (size_t)b * 3 * plane;
+  if (u + 1 < W) sx[(size_t)b * H * (W - 1) + (size_t)v * (W - 1) + u] = (d[i] - d[i + 1]) * edge_weight<real>(im, plane, i, i + 1);
+  if (v + 1 < H) sy[(size_t)b * (H - 1) * W + i] = (d[i] - d[i + W]) * edge_weight<real>(im, plane, i, i + W);
+}
+
+template <typename real>
+__global__ void __launch_bounds__(kBT) smooth_maps_bwd_kernel(int H, int W, const real* img, const real* gsx,
+                                                              const real* gsy, real* ddn) {
+  const int b = blockIdx.y;
+  const size_t plane = (size_t)H * W, i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  if (i >= plane) return;
+  const int v = (int)(i / W), u = (int)(i % W);
+  const real* im = img + (size_t)b * 3 * plane;
+  const real* gx = gsx + (size_t)b * H * (W - 1) + (size_t)v * (W - 1);
+  const real* gy = gsy + (size_t)b * (H - 1) * W;
+  real a = real(0);
+  if (u + 1 < W) a += gx[u] * edge_weight<real>(im, plane, i, i + 1);
+  if (u >= 1) a -= gx[u - 1] * edge_weight<real>(im, plane, i - 1, i);
+  if (v + 1 < H) a += gy[i] * edge_weight<real>(im, plane, i, i + W);
+  if (v >= 1) a -= gy[i - W] * edge_weight<real>(im, plane, i - W, i);
+  ddn[b * plane + i] = a;
+}
+
+// ------------------------------------------------------------------------------------------
+// reduce_photometric_loss for one scale (losses/...:269-297): candidates k = 0..K-1, each [B,Cg,H,W].
+//   op min : mean over (b, pixel) of the min over all K * Cg channels (first index wins ties)
+//   op mean: sum_k mean(cand_k) / K
+// ------------------------------------------------------------------------------------------
+constexpr int kMaxCand = 16;
+struct CandPtrs { const void* p[kMaxCand]; void* g[kMaxCand]; };
+
+template <typename real>
+__global__ void __launch_bounds__(kBT) cand_reduce_kernel(int K, int Cg, size_t plane, int op, CandPtrs cp,
+                                                          int32_t* argmin, double* part) {
+  const int b = blockIdx.y;
+  const size_t i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  __shared__ real scratch[kBT / 32];
+  real v[1] = {real(0)};
+  if (i < plane) {
+    if (op == PSFM_REDUCE_MIN) {
+      real best = real(0);
+      int sel = -1;
+      for (int k = 0; k < K; ++k)
+        for (int c = 0; c < Cg; ++c) {
+          const real a = ((const real*)cp.p[k])[((size_t)b * Cg + c) * plane + i];
+          if (sel < 0 || a < best) { best = a; sel = k * Cg + c; }
+        }
+      argmin[b * plane + i] = sel;
+      v[0] = best;
+    } else {
+      for (int k = 0; k < K; ++k)
+        for (int c = 0; c < Cg; ++c) v[0] += ((const real*)cp.p[k])[((size_t)b * Cg + c) * plane + i];
+    }
+  }
+  block_reduce<real, 1>(v, scratch);
+  if (threadIdx.x == 0) part[(size_t)b * gridDim.x + blockIdx.x] = (double)v[0];
+}
+
+template <typename real>
+__global__ void __launch_bounds__(kBT) cand_reduce_bwd_kernel(int K, int Cg, size_t plane, int op, real scale,
+                                                              const real* gout, const int32_t* argmin, CandPtrs cp) {
+  const int b = blockIdx.y;
+  const size_t i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  if (i >= plane) return;
+  const real g = gout[0] * scale;
+  const int sel = (op == PSFM_REDUCE_MIN) ? argmin[b * plane + i] : -1;
+  for (int k = 0; k < K; ++k)
+    for (int c = 0; c < Cg; ++c)
+      ((real*)cp.g[k])[((size_t)b * Cg + c) * plane + i] = (op != PSFM_REDUCE_MIN || sel == k * Cg + c) ? g : real(0);
+}
+
+// d mean|x| / dx = sign(x) * g / n
+template <typename real>
+__global__ void __launch_bounds__(kBT) abs_mean_bwd_kernel(size_t n, real scale, const real* x, const real* gout, real* dx) {
+  const size_t i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  if (i < n) dx[i] = rsign(x[i]) * gout[0] * scale;
+}
+
+}  // namespace psfm
+
+// ------------------------------------------------------------------------------------------
+// C ABI (declared in include/psfm.h)
+// ------------------------------------------------------------------------------------------
+int psfm_fail(int code, const char* fmt, ...);      // psfm_abi.cu: sets the thread-local error string
+
+using namespace psfm;
+
+#define PSFM_BLOCK_CHECK(cond, msg) do { if (!(cond)) return psfm_fail(PSFM_ERR_INVALID, msg); } while (0)
+#define PSFM_DT_CHECK(dt) PSFM_BLOCK_CHECK((dt) == PSFM_F32 || (dt) == PSFM_F64, "real_dtype must be f32|f64")
+// run `call` with real = float or double according to dt
+#define PSFM_DISPATCH(dt, ...) do { if ((dt) == PSFM_F64) { typedef double real; __VA_ARGS__; } else { typedef float real; __VA_ARGS__; } } while (0)
+
+static int launch_result(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) return PSFM_OK;
+  return psfm_fail(PSFM_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
+}
+
+static inline size_t al256(size_t x) { return (x + 255) / 256 * 256; }
+
+extern "C" {
+
+size_t psfm_block_workspace_bytes(int B, size_t N) {
+  if (B < 1 || N < 1) return 0;
+  return al256((size_t)B * nblk_for(N) * 12 * sizeof(double)) + al256((size_t)B * sizeof(double)) + 256;
+}
+
+int psfm_reconstruct(int B, int H, int W, int dt, const void* depth, const void* K, const void* Twc, void* out,
+                     void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(B >= 1 && H >= 1 && W >= 1 && depth && K && out, "psfm_reconstruct: bad argument");
+  const dim3 grid(nblk_for((size_t)H * W), B);
+  count_launches(1);
+  PSFM_DISPATCH(dt, (reconstruct_kernel<real><<<grid, kBT, 0, (cudaStream_t)stream>>>(
+                        H, W, (const real*)depth, (const real*)K, (const real*)Twc, (real*)out)));
+  return launch_result("psfm_reconstruct");
+}
+
+int psfm_reconstruct_backward(int B, int H, int W, int dt, const void* K, const void* Twc, const void* grad_out,
+                              void* d_depth, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(B >= 1 && H >= 1 && W >= 1 && K && grad_out && d_depth, "psfm_reconstruct_backward: bad argument");
+  const dim3 grid(nblk_for((size_t)H * W), B);
+  count_launches(1);
+  PSFM_DISPATCH(dt, (reconstruct_bwd_kernel<real><<<grid, kBT, 0, (cudaStream_t)stream>>>(
+                        H, W, (const real*)K, (const real*)Twc, (const real*)grad_out, (real*)d_depth)));
+  return launch_result("psfm_reconstruct_backward");
+}
+
+int psfm_project(int B, int H, int W, int dt, const void* X, const void* K, const void* Tcw, void* out, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(B >= 1 && H >= 2 && W >= 2 && X && K && out, "psfm_project: bad argument");
+  const dim3 grid(nblk_for((size_t)H * W), B);
+  count_launches(1);
+  PSFM_DISPATCH(dt, (project_kernel<real><<<grid, kBT, 0, (cudaStream_t)stream>>>(
+                        H, W, (const real*)X, (const real*)K, (const real*)Tcw, (real*)out)));
+  return launch_result("psfm_project");
+}
+
+int psfm_project_backward(int B, int H, int W, int dt, const void* X, const void* K, const void* Tcw,
+                          const void* grad_out, void* dX, void* d_Tcw, void* ws, size_t ws_bytes, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(B >= 1 && H >= 2 && W >= 2 && X && K && grad_out && dX, "psfm_project_backward: bad argument");
+  const bool pose = Tcw && d_Tcw;
+  if (pose && (!ws || ws_bytes < psfm_block_workspace_bytes(B, (size_t)H * W)))
+    return psfm_fail(PSFM_ERR_WORKSPACE, "psfm_project_backward: workspace too small");
+  const unsigned nb = nblk_for((size_t)H * W);
+  count_launches(pose ? 2 : 1);
+  PSFM_DISPATCH(dt, {
+    project_bwd_kernel<real><<<dim3(nb, B), kBT, 0, (cudaStream_t)stream>>>(
+        H, W, (const real*)X, (const real*)K, (const real*)Tcw, (const real*)grad_out, (real*)dX, pose ? (real*)ws : nullptr);
+    if (pose) mat_finish_kernel<real><<<B, 32, 0, (cudaStream_t)stream>>>((const real*)ws, (int)nb, (real*)d_Tcw);
+  });
+  return launch_result("psfm_project_backward");
+}
+
+int psfm_transform_points(int B, size_t N, int dt, const void* mat, const void* X, void* out, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(B >= 1 && N >= 1 && mat && X && out, "psfm_transform_points: bad argument");
+  count_launches(1);
+  PSFM_DISPATCH(dt, (transform_kernel<real><<<dim3(nblk_for(N), B), kBT, 0, (cudaStream_t)stream>>>(
+                        N, (const real*)mat, (const real*)X, (real*)out)));
+  return launch_result("psfm_transform_points");
+}
+
+int psfm_transform_points_backward(int B, size_t N, int dt, const void* mat, const void* X, const void* grad_out,
+                                   void* dX, void* d_mat, void* ws, size_t ws_bytes, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(B >= 1 && N >= 1 && mat && X && grad_out && dX && d_mat, "psfm_transform_points_backward: bad argument");
+  if (!ws || ws_bytes < psfm_block_workspace_bytes(B, N))
+    return psfm_fail(PSFM_ERR_WORKSPACE, "psfm_transform_points_backward: workspace too small");
+  const unsigned nb = nblk_for(N);
+  count_launches(2);
+  PSFM_DISPATCH(dt, {
+    transform_bwd_kernel<real><<<dim3(nb, B), kBT, 0, (cudaStream_t)stream>>>(
+        N, (const real*)mat, (const real*)X, (const real*)grad_out, (real*)dX, (real*)ws);
+    mat_finish_kernel<real><<<B, 32, 0, (cudaStream_t)stream>>>((const real*)ws, (int)nb, (real*)d_mat);
+  });
+  return launch_result("psfm_transform_points_backward");
+}
+
+int psfm_photometric_map(int B, int H, int W, int dt, int mode, double ssim_w, double C1, double C2, const void* x,
+                         const void* y, void* out, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(B >= 1 && H >= 2 && W >= 2 && x && y && out && mode >= 0 && mode <= 3, "psfm_photometric_map: bad argument");
+  count_launches(1);
+  PSFM_DISPATCH(dt, (photo_map_kernel<real><<<dim3(nblk_for((size_t)H * W), B), kBT, 0, (cudaStream_t)stream>>>(
+                        H, W, mode, (real)ssim_w, (real)C1, (real)C2, (const real*)x, (const real*)y, (real*)out)));
+  return launch_result("psfm_photometric_map");
+}
+
+int psfm_photometric_map_backward(int B, int H, int W, int dt, int mode, double ssim_w, double C1, double C2,
+                                  const void* x, const void* y, const void* grad_out, void* dx, void* dy, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(B >= 1 && H >= 2 && W >= 2 && x && y && grad_out && dx && mode >= 0 && mode <= 3,
+                   "psfm_photometric_map_backward: bad argument");
+  count_launches(1);
+  PSFM_DISPATCH(dt, (photo_map_bwd_kernel<real><<<dim3(nblk_for((size_t)H * W), B), kBT, 0, (cudaStream_t)stream>>>(
+                        H, W, mode, (real)ssim_w, (real)C1, (real)C2, (const real*)x, (const real*)y,
+                        (const real*)grad_out, (real*)dx, (real*)dy)));
+  return launch_result("psfm_photometric_map_backward");
+}
+
+int psfm_normalize(int B, size_t N, int dt, const void* d, void* out, void* mean_out, void* ws, size_t ws_bytes,
+                   void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(B >= 1 && N >= 1 && d && out && mean_out, "psfm_normalize: bad argument");
+  if (!ws || ws_bytes < psfm_block_workspace_bytes(B, N)) return psfm_fail(PSFM_ERR_WORKSPACE, "psfm_normalize: workspace too small");
+  const unsigned nb = nblk_for(N);
+  cudaStream_t st = (cudaStream_t)stream;
+  count_launches(3);
+  PSFM_DISPATCH(dt, {
+    rowsum_kernel<real><<<dim3(nb, B), kBT, 0, st>>>(N, 0, (const real*)d, nullptr, (double*)ws);
+    rowsum_finish_kernel<real><<<B, 256, 0, st>>>((const double*)ws, (int)nb, 1.0 / (double)N, (real*)mean_out);
+    normalize_kernel<real><<<dim3(nb, B), kBT, 0, st>>>(N, (const real*)d, (const real*)mean_out, (real*)out);
+  });
+  return launch_result("psfm_normalize");
+}
+
+int psfm_normalize_backward(int B, size_t N, int dt, const void* d, const void* mean, const void* grad_out, void* dd,
+                            void* ws, size_t ws_bytes, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(B >= 1 && N >= 1 && d && mean && grad_out && dd, "psfm_normalize_backward: bad argument");
+  if (!ws || ws_bytes < psfm_block_workspace_bytes(B, N))
+    return psfm_fail(PSFM_ERR_WORKSPACE, "psfm_normalize_backward: workspace too small");
+  const unsigned nb = nblk_for(N);
+  cudaStream_t st = (cudaStream_t)stream;
+  char* dot = (char*)ws + al256((size_t)B * nb * 12 * sizeof(double));
+  count_launches(3);
+  PSFM_DISPATCH(dt, {
+    rowsum_kernel<real><<<dim3(nb, B), kBT, 0, st>>>(N, 1, (const real*)grad_out, (const real*)d, (double*)ws);
+    rowsum_finish_kernel<real><<<B, 256, 0, st>>>((const double*)ws, (int)nb, 1.0, (real*)dot);
+    normalize_bwd_kernel<real><<<dim3(nb, B), kBT, 0, st>>>(N, (const real*)grad_out, (const real*)mean, (const real*)dot, (real*)dd);
+  });
+  return launch_result("psfm_normalize_backward");
+}
+
+int psfm_smoothness_maps(int B, int H, int W, int dt, const void* dn, const void* image, void* sx, void* sy, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(B >= 1 && H >= 2 && W >= 2 && dn && image && sx && sy, "psfm_smoothness_maps: bad argument");
+  count_launches(1);
+  PSFM_DISPATCH(dt, (smooth_maps_kernel<real><<<dim3(nblk_for((size_t)H * W), B), kBT, 0, (cudaStream_t)stream>>>(
+                        H, W, (const real*)dn, (const real*)image, (real*)sx, (real*)sy)));
+  return launch_result("psfm_smoothness_maps");
+}
+
+int psfm_smoothness_maps_backward(int B, int H, int W, int dt, const void* image, const void* gsx, const void* gsy,
+                                  void* ddn, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(B >= 1 && H >= 2 && W >= 2 && image && gsx && gsy && ddn, "psfm_smoothness_maps_backward: bad argument");
+  count_launches(1);
+  PSFM_DISPATCH(dt, (smooth_maps_bwd_kernel<real><<<dim3(nblk_for((size_t)H * W), B), kBT, 0, (cudaStream_t)stream>>>(
+                        H, W, (const real*)image, (const real*)gsx, (const real*)gsy, (real*)ddn)));
+  return launch_result("psfm_smoothness_maps_backward");
+}
+
+int psfm_reduce_candidates(int K, int B, int Cg, int H, int W, int dt, int op, const void* const* cands, void* out,
+                           int32_t* argmin, void* ws, size_t ws_bytes, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(K >= 1 && K <= kMaxCand && B >= 1 && Cg >= 1 && H >= 1 && W >= 1 && cands && out,
+                   "psfm_reduce_candidates: bad argument (1..16 candidates)");
+  if (op != PSFM_REDUCE_MIN && op != PSFM_REDUCE_MEAN) return psfm_fail(PSFM_ERR_INVALID, "Unknown photometric_reduce_op: %d", op);
+  PSFM_BLOCK_CHECK(op != PSFM_REDUCE_MIN || argmin, "psfm_reduce_candidates: argmin is NULL");
+  const size_t plane = (size_t)H * W;
+  if (!ws || ws_bytes < psfm_block_workspace_bytes(B, plane)) return psfm_fail(PSFM_ERR_WORKSPACE, "psfm_reduce_candidates: workspace too small");
+  CandPtrs cp;
+  for (int k = 0; k < kMaxCand; ++k) { cp.p[k] = k < K ? cands[k] : nullptr; cp.g[k] = nullptr; }
+  const unsigned nb = nblk_for(plane);
+  const double scale = op == PSFM_REDUCE_MIN ? 1.0 / ((double)B * plane) : 1.0 / ((double)K * B * Cg * plane);
+  cudaStream_t st = (cudaStream_t)stream;
+  count_launches(2);
+  PSFM_DISPATCH(dt, {
+    cand_reduce_kernel<real><<<dim3(nb, B), kBT, 0, st>>>(K, Cg, plane, op, cp, argmin, (double*)ws);
+    rowsum_finish_kernel<real><<<1, 256, 0, st>>>((const double*)ws, (int)(nb * B), scale, (real*)out);
+  });
+  return launch_result("psfm_reduce_candidates");
+}
+
+int psfm_reduce_candidates_backward(int K, int B, int Cg, int H, int W, int dt, int op, const int32_t* argmin,
+                                    const void* grad_out, void* const* d_cands, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(K >= 1 && K <= kMaxCand && B >= 1 && Cg >= 1 && grad_out && d_cands, "psfm_reduce_candidates_backward: bad argument");
+  PSFM_BLOCK_CHECK(op != PSFM_REDUCE_MIN || argmin, "psfm_reduce_candidates_backward: argmin is NULL");
+  const size_t plane = (size_t)H * W;
+  CandPtrs cp;
+  for (int k = 0; k < kMaxCand; ++k) { cp.p[k] = nullptr; cp.g[k] = k < K ? d_cands[k] : nullptr; }
+  const double scale = op == PSFM_REDUCE_MIN ? 1.0 / ((double)B * plane) : 1.0 / ((double)K * B * Cg * plane);
+  count_launches(1);
+  PSFM_DISPATCH(dt, (cand_reduce_bwd_kernel<real><<<dim3(nblk_for(plane), B), kBT, 0, (cudaStream_t)stream>>>(
+                        K, Cg, plane, op, (real)scale, (const real*)grad_out, argmin, cp)));
+  return launch_result("psfm_reduce_candidates_backward");
+}
+
+int psfm_abs_mean(size_t n, int dt, const void* x, void* out, void* ws, size_t ws_bytes, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(n >= 1 && x && out, "psfm_abs_mean: bad argument");
+  if (!ws || ws_bytes < psfm_block_workspace_bytes(1, n)) return psfm_fail(PSFM_ERR_WORKSPACE, "psfm_abs_mean: workspace too small");
+  const unsigned nb = nblk_for(n);
+  cudaStream_t st = (cudaStream_t)stream;
+  count_launches(2);
+  PSFM_DISPATCH(dt, {
+    rowsum_kernel<real><<<dim3(nb, 1), kBT, 0, st>>>(n, 2, (const real*)x, nullptr, (double*)ws);
+    rowsum_finish_kernel<real><<<1, 256, 0, st>>>((const double*)ws, (int)nb, 1.0 / (double)n, (real*)out);
+  });
+  return launch_result("psfm_abs_mean");
+}
+
+int psfm_abs_mean_backward(size_t n, int dt, const void* x, const void* grad_out, void* dx, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(n >= 1 && x && grad_out && dx, "psfm_abs_mean_backward: bad argument");
+  count_launches(1);
+  PSFM_DISPATCH(dt, (abs_mean_bwd_kernel<real><<<nblk_for(n), kBT, 0, (cudaStream_t)stream>>>(
+                        n, (real)(1.0 / (double)n), (const real*)x, (const real*)grad_out, (real*)dx)));
+  return launch_result("psfm_abs_mean_backward");
+}
+
+}  // extern "C"

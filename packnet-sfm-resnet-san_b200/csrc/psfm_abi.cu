@@ -57,7 +57,7 @@ ProfScope::~ProfScope() {
 }
 }  // namespace psfm
 
-static int fail(int code, const char* fmt, ...) {
+int psfm_fail(int code, const char* fmt, ...) {
   va_list ap;
   va_start(ap, fmt);
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
@@ -67,47 +67,47 @@ static int fail(int code, const char* fmt, ...) {
 
 static int cuda_result(cudaError_t e, const char* what) {
   if (e == cudaSuccess) return PSFM_OK;
-  return fail(PSFM_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
+  return psfm_fail(PSFM_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
 }
 
 static int check_cfg(const psfm_loss_cfg* c) {
-  if (!c) return fail(PSFM_ERR_INVALID, "cfg is NULL");
-  if (c->B < 1) return fail(PSFM_ERR_INVALID, "B must be >= 1 (got %d)", c->B);
-  if (c->C < 1 || c->C > PSFM_MAX_CTX) return fail(PSFM_ERR_INVALID, "C must be in 1..%d (got %d)", PSFM_MAX_CTX, c->C);
+  if (!c) return psfm_fail(PSFM_ERR_INVALID, "cfg is NULL");
+  if (c->B < 1) return psfm_fail(PSFM_ERR_INVALID, "B must be >= 1 (got %d)", c->B);
+  if (c->C < 1 || c->C > PSFM_MAX_CTX) return psfm_fail(PSFM_ERR_INVALID, "C must be in 1..%d (got %d)", PSFM_MAX_CTX, c->C);
   if (c->n < 1 || c->n > PSFM_MAX_SCALES)
-    return fail(PSFM_ERR_INVALID, "n must be in 1..%d (got %d)", PSFM_MAX_SCALES, c->n);
-  if (c->H < 2 || c->W < 2) return fail(PSFM_ERR_INVALID, "image must be at least 2x2 (got %dx%d)", c->H, c->W);
+    return psfm_fail(PSFM_ERR_INVALID, "n must be in 1..%d (got %d)", PSFM_MAX_SCALES, c->n);
+  if (c->H < 2 || c->W < 2) return psfm_fail(PSFM_ERR_INVALID, "image must be at least 2x2 (got %dx%d)", c->H, c->W);
   for (int s = 0; s < c->n; ++s)
     if (c->Hs[s] < 2 || c->Ws[s] < 2)
-      return fail(PSFM_ERR_INVALID, "scale %d must be at least 2x2 (got %dx%d)", s, c->Hs[s], c->Ws[s]);
-  if (c->real_dtype != PSFM_F32 && c->real_dtype != PSFM_F64) return fail(PSFM_ERR_INVALID, "real_dtype must be f32|f64");
+      return psfm_fail(PSFM_ERR_INVALID, "scale %d must be at least 2x2 (got %dx%d)", s, c->Hs[s], c->Ws[s]);
+  if (c->real_dtype != PSFM_F32 && c->real_dtype != PSFM_F64) return psfm_fail(PSFM_ERR_INVALID, "real_dtype must be f32|f64");
   if (c->real_dtype == PSFM_F64 && c->img_dtype != PSFM_F64)
-    return fail(PSFM_ERR_INVALID, "f64 arithmetic requires f64 images");
+    return psfm_fail(PSFM_ERR_INVALID, "f64 arithmetic requires f64 images");
   if (c->real_dtype == PSFM_F32 && c->img_dtype != PSFM_F32 && c->img_dtype != PSFM_BF16)
-    return fail(PSFM_ERR_INVALID, "f32 arithmetic requires f32 or bf16 images");
+    return psfm_fail(PSFM_ERR_INVALID, "f32 arithmetic requires f32 or bf16 images");
   if (c->padding != PSFM_PAD_ZEROS && c->padding != PSFM_PAD_BORDER)
-    return fail(PSFM_ERR_INVALID, "padding must be zeros|border");
+    return psfm_fail(PSFM_ERR_INVALID, "padding must be zeros|border");
   if (c->reduce_op != PSFM_REDUCE_MIN && c->reduce_op != PSFM_REDUCE_MEAN)
-    return fail(PSFM_ERR_INVALID, "Unknown photometric_reduce_op: %d", c->reduce_op);
+    return psfm_fail(PSFM_ERR_INVALID, "Unknown photometric_reduce_op: %d", c->reduce_op);
   if (c->automask && c->reduce_op != PSFM_REDUCE_MIN)
-    return fail(PSFM_ERR_INVALID, "For automasking only the min photometric_reduce_op is supported.");
+    return psfm_fail(PSFM_ERR_INVALID, "For automasking only the min photometric_reduce_op is supported.");
   const int groups = (c->automask ? 2 : 1) * c->C * (c->ssim_w > 0.0 ? 1 : 3);
-  if (groups > 254) return fail(PSFM_ERR_INVALID, "too many candidates (%d)", groups);
+  if (groups > 254) return psfm_fail(PSFM_ERR_INVALID, "too many candidates (%d)", groups);
   return PSFM_OK;
 }
 
 static int check_io(const psfm_loss_cfg* c, const psfm_loss_io* io, bool need_grads) {
-  if (!io) return fail(PSFM_ERR_INVALID, "io is NULL");
-  if (!io->K || !io->ref_K) return fail(PSFM_ERR_INVALID, "K / ref_K is NULL");
+  if (!io) return psfm_fail(PSFM_ERR_INVALID, "io is NULL");
+  if (!io->K || !io->ref_K) return psfm_fail(PSFM_ERR_INVALID, "K / ref_K is NULL");
   for (int j = 0; j < c->C; ++j) {
-    if (!io->pose[j]) return fail(PSFM_ERR_INVALID, "pose[%d] is NULL", j);
-    if (need_grads && !io->d_pose[j]) return fail(PSFM_ERR_INVALID, "d_pose[%d] is NULL", j);
+    if (!io->pose[j]) return psfm_fail(PSFM_ERR_INVALID, "pose[%d] is NULL", j);
+    if (need_grads && !io->d_pose[j]) return psfm_fail(PSFM_ERR_INVALID, "d_pose[%d] is NULL", j);
   }
   for (int s = 0; s < c->n; ++s) {
-    if (!io->image[s] || !io->inv_depth[s]) return fail(PSFM_ERR_INVALID, "image/inv_depth[%d] is NULL", s);
+    if (!io->image[s] || !io->inv_depth[s]) return psfm_fail(PSFM_ERR_INVALID, "image/inv_depth[%d] is NULL", s);
     for (int j = 0; j < c->C; ++j)
-      if (!io->ctx[s][j]) return fail(PSFM_ERR_INVALID, "ctx[%d][%d] is NULL", s, j);
-    if (need_grads && !io->d_inv_depth[s]) return fail(PSFM_ERR_INVALID, "d_inv_depth[%d] is NULL", s);
+      if (!io->ctx[s][j]) return psfm_fail(PSFM_ERR_INVALID, "ctx[%d][%d] is NULL", s, j);
+    if (need_grads && !io->d_inv_depth[s]) return psfm_fail(PSFM_ERR_INVALID, "d_inv_depth[%d] is NULL", s);
   }
   return PSFM_OK;
 }
@@ -151,10 +151,10 @@ int psfm_loss_forward(const psfm_loss_cfg* cfg, const psfm_loss_io* io, void* wo
   if (rc) return rc;
   if ((rc = check_io(cfg, io, false))) return rc;
   for (int s = 0; s < cfg->n; ++s)
-    if (!io->sel[s]) return fail(PSFM_ERR_INVALID, "sel[%d] is NULL", s);
-  if (!loss_out || !workspace) return fail(PSFM_ERR_INVALID, "loss_out / workspace is NULL");
+    if (!io->sel[s]) return psfm_fail(PSFM_ERR_INVALID, "sel[%d] is NULL", s);
+  if (!loss_out || !workspace) return psfm_fail(PSFM_ERR_INVALID, "loss_out / workspace is NULL");
   if (workspace_bytes < psfm::loss_workspace_bytes(cfg))
-    return fail(PSFM_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes, psfm::loss_workspace_bytes(cfg));
+    return psfm_fail(PSFM_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes, psfm::loss_workspace_bytes(cfg));
   return cuda_result(psfm::loss_forward_dispatch(cfg, io, workspace, loss_out, (cudaStream_t)stream), "psfm_loss_forward");
 }
 
@@ -164,10 +164,10 @@ int psfm_loss_backward(const psfm_loss_cfg* cfg, const psfm_loss_io* io, void* w
   if (rc) return rc;
   if ((rc = check_io(cfg, io, true))) return rc;
   for (int s = 0; s < cfg->n; ++s)
-    if (!io->sel[s]) return fail(PSFM_ERR_INVALID, "sel[%d] is NULL", s);
-  if (!grad_loss || !workspace) return fail(PSFM_ERR_INVALID, "grad_loss / workspace is NULL");
+    if (!io->sel[s]) return psfm_fail(PSFM_ERR_INVALID, "sel[%d] is NULL", s);
+  if (!grad_loss || !workspace) return psfm_fail(PSFM_ERR_INVALID, "grad_loss / workspace is NULL");
   if (workspace_bytes < psfm::loss_workspace_bytes(cfg))
-    return fail(PSFM_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes, psfm::loss_workspace_bytes(cfg));
+    return psfm_fail(PSFM_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes, psfm::loss_workspace_bytes(cfg));
   return cuda_result(psfm::loss_backward_dispatch(cfg, io, workspace, grad_loss, (cudaStream_t)stream),
                      "psfm_loss_backward");
 }
@@ -177,26 +177,26 @@ int psfm_loss_forward_backward(const psfm_loss_cfg* cfg, const psfm_loss_io* io,
   int rc = check_cfg(cfg);
   if (rc) return rc;
   if ((rc = check_io(cfg, io, true))) return rc;
-  if (!loss_out || !workspace) return fail(PSFM_ERR_INVALID, "loss_out / workspace is NULL");
+  if (!loss_out || !workspace) return psfm_fail(PSFM_ERR_INVALID, "loss_out / workspace is NULL");
   if (workspace_bytes < psfm::loss_workspace_bytes(cfg))
-    return fail(PSFM_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes, psfm::loss_workspace_bytes(cfg));
+    return psfm_fail(PSFM_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes, psfm::loss_workspace_bytes(cfg));
   return cuda_result(psfm::loss_fused_dispatch(cfg, io, workspace, loss_out, (cudaStream_t)stream),
                      "psfm_loss_forward_backward");
 }
 
 int psfm_scale_inplace(void* x, const void* scale, size_t count, int real_dtype, void* stream) {
-  if ((!x && count) || !scale) return fail(PSFM_ERR_INVALID, "x / scale is NULL");
-  if (real_dtype != PSFM_F32 && real_dtype != PSFM_F64) return fail(PSFM_ERR_INVALID, "real_dtype must be f32|f64");
+  if ((!x && count) || !scale) return psfm_fail(PSFM_ERR_INVALID, "x / scale is NULL");
+  if (real_dtype != PSFM_F32 && real_dtype != PSFM_F64) return psfm_fail(PSFM_ERR_INVALID, "real_dtype must be f32|f64");
   return cuda_result(psfm::scale_dispatch(x, scale, count, real_dtype, (cudaStream_t)stream), "psfm_scale_inplace");
 }
 
 static int check_warp(int B, int H, int W, int img_dtype, int real_dtype, int padding) {
-  if (B < 1 || H < 2 || W < 2) return fail(PSFM_ERR_INVALID, "bad shape B=%d H=%d W=%d", B, H, W);
-  if (real_dtype != PSFM_F32 && real_dtype != PSFM_F64) return fail(PSFM_ERR_INVALID, "real_dtype must be f32|f64");
-  if (real_dtype == PSFM_F64 && img_dtype != PSFM_F64) return fail(PSFM_ERR_INVALID, "f64 arithmetic requires f64 images");
+  if (B < 1 || H < 2 || W < 2) return psfm_fail(PSFM_ERR_INVALID, "bad shape B=%d H=%d W=%d", B, H, W);
+  if (real_dtype != PSFM_F32 && real_dtype != PSFM_F64) return psfm_fail(PSFM_ERR_INVALID, "real_dtype must be f32|f64");
+  if (real_dtype == PSFM_F64 && img_dtype != PSFM_F64) return psfm_fail(PSFM_ERR_INVALID, "f64 arithmetic requires f64 images");
   if (real_dtype == PSFM_F32 && img_dtype != PSFM_F32 && img_dtype != PSFM_BF16)
-    return fail(PSFM_ERR_INVALID, "f32 arithmetic requires f32 or bf16 images");
-  if (padding != PSFM_PAD_ZEROS && padding != PSFM_PAD_BORDER) return fail(PSFM_ERR_INVALID, "padding must be zeros|border");
+    return psfm_fail(PSFM_ERR_INVALID, "f32 arithmetic requires f32 or bf16 images");
+  if (padding != PSFM_PAD_ZEROS && padding != PSFM_PAD_BORDER) return psfm_fail(PSFM_ERR_INVALID, "padding must be zeros|border");
   return PSFM_OK;
 }
 
@@ -204,7 +204,7 @@ int psfm_warp_forward(int B, int H, int W, int img_dtype, int real_dtype, int pa
                       const void* depth, const void* K, const void* ref_K, const void* pose, void* out, void* stream) {
   int rc = check_warp(B, H, W, img_dtype, real_dtype, padding);
   if (rc) return rc;
-  if (!ref_image || !depth || !K || !ref_K || !pose || !out) return fail(PSFM_ERR_INVALID, "NULL pointer argument");
+  if (!ref_image || !depth || !K || !ref_K || !pose || !out) return psfm_fail(PSFM_ERR_INVALID, "NULL pointer argument");
   return cuda_result(psfm::warp_forward_dispatch(B, H, W, img_dtype, real_dtype, padding, ref_image, depth, K, ref_K,
                                                  pose, out, (cudaStream_t)stream), "psfm_warp_forward");
 }
@@ -221,21 +221,21 @@ int psfm_warp_backward(int B, int H, int W, int img_dtype, int real_dtype, int p
   int rc = check_warp(B, H, W, img_dtype, real_dtype, padding);
   if (rc) return rc;
   if (!ref_image || !depth || !K || !ref_K || !pose || !grad_out || !d_depth || !d_pose || !workspace)
-    return fail(PSFM_ERR_INVALID, "NULL pointer argument");
+    return psfm_fail(PSFM_ERR_INVALID, "NULL pointer argument");
   if (d_ref_image && img_dtype == PSFM_BF16)
-    return fail(PSFM_ERR_INVALID, "gradient w.r.t. a bf16 reference image is not supported");
+    return psfm_fail(PSFM_ERR_INVALID, "gradient w.r.t. a bf16 reference image is not supported");
   if (workspace_bytes < psfm::warp_workspace_bytes(B, H, W, real_dtype))
-    return fail(PSFM_ERR_WORKSPACE, "workspace too small");
+    return psfm_fail(PSFM_ERR_WORKSPACE, "workspace too small");
   return cuda_result(psfm::warp_backward_dispatch(B, H, W, img_dtype, real_dtype, padding, ref_image, depth, K, ref_K,
                                                   pose, grad_out, d_depth, d_pose, d_ref_image, workspace,
                                                   (cudaStream_t)stream), "psfm_warp_backward");
 }
 
 int psfm_resize(int N, int Hi, int Wi, int Ho, int Wo, int dtype, int mode, const void* in, void* out, void* stream) {
-  if (N < 1 || Hi < 1 || Wi < 1 || Ho < 1 || Wo < 1) return fail(PSFM_ERR_INVALID, "bad resize shape");
-  if (dtype != PSFM_F32 && dtype != PSFM_BF16 && dtype != PSFM_F64) return fail(PSFM_ERR_INVALID, "bad dtype");
-  if (mode != 0 && mode != 1) return fail(PSFM_ERR_INVALID, "mode must be 0 (bilinear) or 1 (nearest)");
-  if (!in || !out) return fail(PSFM_ERR_INVALID, "NULL pointer argument");
+  if (N < 1 || Hi < 1 || Wi < 1 || Ho < 1 || Wo < 1) return psfm_fail(PSFM_ERR_INVALID, "bad resize shape");
+  if (dtype != PSFM_F32 && dtype != PSFM_BF16 && dtype != PSFM_F64) return psfm_fail(PSFM_ERR_INVALID, "bad dtype");
+  if (mode != 0 && mode != 1) return psfm_fail(PSFM_ERR_INVALID, "mode must be 0 (bilinear) or 1 (nearest)");
+  if (!in || !out) return psfm_fail(PSFM_ERR_INVALID, "NULL pointer argument");
   return cuda_result(psfm::resize_dispatch(N, Hi, Wi, Ho, Wo, dtype, mode, in, out, (cudaStream_t)stream), "psfm_resize");
 }
 

@@ -20,7 +20,12 @@ REDUCE = {'min': 0, 'mean': 1}
 EXPORTS = ('psfm_abi_version', 'psfm_last_error', 'psfm_launch_count', 'psfm_profile_enable', 'psfm_profile_read',
            'psfm_loss_workspace_bytes', 'psfm_loss_forward',
            'psfm_loss_backward', 'psfm_loss_forward_backward', 'psfm_scale_inplace', 'psfm_warp_forward',
-           'psfm_warp_workspace_bytes', 'psfm_warp_backward', 'psfm_resize')
+           'psfm_warp_workspace_bytes', 'psfm_warp_backward', 'psfm_resize',
+           'psfm_block_workspace_bytes', 'psfm_reconstruct', 'psfm_reconstruct_backward', 'psfm_project',
+           'psfm_project_backward', 'psfm_transform_points', 'psfm_transform_points_backward',
+           'psfm_photometric_map', 'psfm_photometric_map_backward', 'psfm_normalize', 'psfm_normalize_backward',
+           'psfm_smoothness_maps', 'psfm_smoothness_maps_backward', 'psfm_reduce_candidates',
+           'psfm_reduce_candidates_backward', 'psfm_abs_mean', 'psfm_abs_mean_backward')
 
 
 class LossCfg(C.Structure):
@@ -76,6 +81,29 @@ def _load():
     lib.psfm_warp_backward.argtypes = [i, i, i, i, i, i, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, sz, vp]
     lib.psfm_resize.restype = i
     lib.psfm_resize.argtypes = [i, i, i, i, i, i, i, vp, vp, vp]
+    d = C.c_double
+    lib.psfm_block_workspace_bytes.restype = sz
+    lib.psfm_block_workspace_bytes.argtypes = [i, sz]
+    for name, args in (
+            ('psfm_reconstruct', [i, i, i, i, vp, vp, vp, vp, vp]),
+            ('psfm_reconstruct_backward', [i, i, i, i, vp, vp, vp, vp, vp]),
+            ('psfm_project', [i, i, i, i, vp, vp, vp, vp, vp]),
+            ('psfm_project_backward', [i, i, i, i, vp, vp, vp, vp, vp, vp, vp, sz, vp]),
+            ('psfm_transform_points', [i, sz, i, vp, vp, vp, vp]),
+            ('psfm_transform_points_backward', [i, sz, i, vp, vp, vp, vp, vp, vp, sz, vp]),
+            ('psfm_photometric_map', [i, i, i, i, i, d, d, d, vp, vp, vp, vp]),
+            ('psfm_photometric_map_backward', [i, i, i, i, i, d, d, d, vp, vp, vp, vp, vp, vp]),
+            ('psfm_normalize', [i, sz, i, vp, vp, vp, vp, sz, vp]),
+            ('psfm_normalize_backward', [i, sz, i, vp, vp, vp, vp, vp, sz, vp]),
+            ('psfm_smoothness_maps', [i, i, i, i, vp, vp, vp, vp, vp]),
+            ('psfm_smoothness_maps_backward', [i, i, i, i, vp, vp, vp, vp, vp]),
+            ('psfm_reduce_candidates', [i, i, i, i, i, i, i, C.POINTER(vp), vp, vp, vp, sz, vp]),
+            ('psfm_reduce_candidates_backward', [i, i, i, i, i, i, i, vp, vp, C.POINTER(vp), vp]),
+            ('psfm_abs_mean', [sz, i, vp, vp, vp, sz, vp]),
+            ('psfm_abs_mean_backward', [sz, i, vp, vp, vp, vp])):
+        fn = getattr(lib, name)
+        fn.restype = i
+        fn.argtypes = args
     if lib.psfm_abi_version() != 1:
         raise ImportError('libpsfm_b200.so ABI version mismatch: %d' % lib.psfm_abi_version())
     return lib

@@ -1,0 +1,349 @@
+"""Building-block operators of the photometric-loss path over the C ABI (include/psfm.h,
+csrc/block_kernels.cu): what `Camera.reconstruct/project`, `Pose.transform_points`, `SSIM`,
+`calc_photometric_loss`, `reduce_photometric_loss`, `inv_depths_normalize` and `calc_smoothness`
+of the reference compute, one kernel each, with hand-written backward kernels.  PyTorch only
+allocates the buffers and records the autograd edges.
+"""
+import ctypes as C
+
+import torch
+
+from . import _C
+
+
+def _real(t):
+    if t.dtype not in (torch.float32, torch.float64):
+        raise ValueError('float32 or float64 tensors expected, got %s' % t.dtype)
+    return _C.F64 if t.dtype == torch.float64 else _C.F32
+
+
+def _ws(B, N, device):
+    n = int(_C.lib.psfm_block_workspace_bytes(int(B), int(N)))
+    return torch.empty(n, dtype=torch.uint8, device=device), n
+
+
+def _batched_K(K, B, like):
+    if K.dim() == 2:
+        K = K.unsqueeze(0).expand(B, 3, 3)
+    if tuple(K.shape) != (B, 3, 3):
+        raise ValueError('intrinsics must be [B,3,3], got %s' % (tuple(K.shape),))
+    return K.to(like.dtype).contiguous()
+
+
+def _no_grad_supported(t, what):
+    if t is not None and t.requires_grad:
+        raise NotImplementedError('gradient w.r.t. %s is outside the accelerated path' % what)
+
+
+class _Reconstruct(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, depth, K, Twc):
+        _C.require_cuda(depth, K, Twc)
+        B, _, H, W = depth.shape
+        depth = depth.contiguous()
+        K = _batched_K(K, B, depth)
+        Twc = None if Twc is None else Twc.to(depth.dtype).contiguous()
+        out = torch.empty((B, 3, H, W), dtype=depth.dtype, device=depth.device)
+        with torch.cuda.device(depth.device):
+            _C.check(_C.lib.psfm_reconstruct(B, H, W, _real(depth), _C.ptr(depth), _C.ptr(K), _C.ptr(Twc), _C.ptr(out),
+                                             _C.stream_ptr(depth.device)))
+        ctx.save_for_backward(K, Twc)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        K, Twc = ctx.saved_tensors
+        g = g.contiguous()
+        B, _, H, W = g.shape
+        d_depth = torch.empty((B, 1, H, W), dtype=g.dtype, device=g.device)
+        with torch.cuda.device(g.device):
+            _C.check(_C.lib.psfm_reconstruct_backward(B, H, W, _real(g), _C.ptr(K), _C.ptr(Twc), _C.ptr(g),
+                                                      _C.ptr(d_depth), _C.stream_ptr(g.device)))
+        return d_depth, None, None
+
+
+def reconstruct_op(depth, K, Twc=None):
+    """Camera.reconstruct: depth [B,1,H,W] -> points [B,3,H,W]; differentiable w.r.t. depth."""
+    _real(depth)
+    _no_grad_supported(K, 'K')
+    _no_grad_supported(Twc, 'the camera pose of reconstruct')
+    return _Reconstruct.apply(depth, K, Twc)
+
+
+class _Project(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, X, K, Tcw):
+        _C.require_cuda(X, K, Tcw)
+        B, _, H, W = X.shape
+        X = X.contiguous()
+        K = _batched_K(K, B, X)
+        Tcw = None if Tcw is None else Tcw.to(X.dtype).contiguous()
+        out = torch.empty((B, H, W, 2), dtype=X.dtype, device=X.device)
+        with torch.cuda.device(X.device):
+            _C.check(_C.lib.psfm_project(B, H, W, _real(X), _C.ptr(X), _C.ptr(K), _C.ptr(Tcw), _C.ptr(out),
+                                         _C.stream_ptr(X.device)))
+        ctx.save_for_backward(X, K, Tcw)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        X, K, Tcw = ctx.saved_tensors
+        g = g.contiguous()
+        B, _, H, W = X.shape
+        dX = torch.empty_like(X)
+        d_T = None if Tcw is None else torch.empty((B, 4, 4), dtype=X.dtype, device=X.device)
+        ws, n = _ws(B, H * W, X.device)
+        with torch.cuda.device(X.device):
+            _C.check(_C.lib.psfm_project_backward(B, H, W, _real(X), _C.ptr(X), _C.ptr(K), _C.ptr(Tcw), _C.ptr(g),
+                                                  _C.ptr(dX), _C.ptr(d_T), _C.ptr(ws), n, _C.stream_ptr(X.device)))
+        return dX, None, d_T
+
+
+def project_op(X, K, Tcw=None):
+    """Camera.project: points [B,3,H,W] -> normalised coordinates [B,H,W,2]; differentiable w.r.t.
+    the points and the [B,4,4] pose."""
+    _real(X)
+    _no_grad_supported(K, 'K')
+    return _Project.apply(X, K, Tcw)
+
+
+class _TransformPoints(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, mat, X):
+        _C.require_cuda(mat, X)
+        B = X.shape[0]
+        X = X.contiguous()
+        mat = mat.to(X.dtype).contiguous()
+        if tuple(mat.shape) != (B, 4, 4):
+            raise ValueError('pose matrices must be [B,4,4] with the batch of the points')
+        N = X.numel() // (B * 3)
+        out = torch.empty_like(X)
+        with torch.cuda.device(X.device):
+            _C.check(_C.lib.psfm_transform_points(B, N, _real(X), _C.ptr(mat), _C.ptr(X), _C.ptr(out),
+                                                  _C.stream_ptr(X.device)))
+        ctx.save_for_backward(mat, X)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        mat, X = ctx.saved_tensors
+        g = g.contiguous()
+        B = X.shape[0]
+        N = X.numel() // (B * 3)
+        dX, d_mat = torch.empty_like(X), torch.empty_like(mat)
+        ws, n = _ws(B, N, X.device)
+        with torch.cuda.device(X.device):
+            _C.check(_C.lib.psfm_transform_points_backward(B, N, _real(X), _C.ptr(mat), _C.ptr(X), _C.ptr(g), _C.ptr(dX),
+                                                           _C.ptr(d_mat), _C.ptr(ws), n, _C.stream_ptr(X.device)))
+        return d_mat, dX
+
+
+def transform_points_op(mat, points):
+    """Pose.transform_points: R X + t on [B,3,H,W] (or [B,3,N]) points."""
+    _real(points)
+    return _TransformPoints.apply(mat, points)
+
+
+MODE_SSIM, MODE_SSIM_DIST, MODE_PHOTO, MODE_L1 = 0, 1, 2, 3
+
+
+class _PhotoMap(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, y, mode, ssim_w, C1, C2):
+        _C.require_cuda(x, y)
+        if x.shape != y.shape or x.dim() != 4 or x.shape[1] != 3:
+            raise ValueError('SSIM / photometric maps take two [B,3,H,W] images')
+        x = x.contiguous()
+        y = y.to(x.dtype).contiguous()
+        B, _, H, W = x.shape
+        out = torch.empty((B, 1 if mode == MODE_PHOTO else 3, H, W), dtype=x.dtype, device=x.device)
+        with torch.cuda.device(x.device):
+            _C.check(_C.lib.psfm_photometric_map(B, H, W, _real(x), mode, ssim_w, C1, C2, _C.ptr(x), _C.ptr(y),
+                                                 _C.ptr(out), _C.stream_ptr(x.device)))
+        ctx.save_for_backward(x, y)
+        ctx.args = (mode, ssim_w, C1, C2)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        x, y = ctx.saved_tensors
+        mode, ssim_w, C1, C2 = ctx.args
+        g = g.contiguous()
+        B, _, H, W = x.shape
+        dx = torch.empty_like(x)
+        dy = torch.empty_like(y) if ctx.needs_input_grad[1] else None
+        with torch.cuda.device(x.device):
+            _C.check(_C.lib.psfm_photometric_map_backward(B, H, W, _real(x), mode, ssim_w, C1, C2, _C.ptr(x), _C.ptr(y),
+                                                          _C.ptr(g), _C.ptr(dx), _C.ptr(dy), _C.stream_ptr(x.device)))
+        return dx, dy, None, None, None, None
+
+
+def ssim_op(x, y, C1=1e-4, C2=9e-4, distance=False):
+    """SSIM index of two [B,3,H,W] images (3x3 windows, reflection padding), or with
+    `distance` the loss map clamp((1 - SSIM) / 2, 0, 1)."""
+    _real(x)
+    return _PhotoMap.apply(x, y, MODE_SSIM_DIST if distance else MODE_SSIM, 0.0, float(C1), float(C2))
+
+
+def photometric_map_op(t_est, image, ssim_loss_weight, C1, C2, clip_loss=0.0, mask=None):
+    """calc_photometric_loss for one scale (reference :218-267): [B,1,H,W] map
+    alpha * SSIM-distance.mean(1) + (1 - alpha) * L1.mean(1), or the 3-channel L1 when alpha == 0.
+    The rarely used clip / mask options are applied on top of the kernel's map: the clip threshold is
+    a detached scalar statistic exactly as in the reference (:249-253)."""
+    _real(t_est)
+    alpha = float(ssim_loss_weight)
+    p = _PhotoMap.apply(t_est, image, MODE_PHOTO if alpha > 0.0 else MODE_L1, alpha, float(C1), float(C2))
+    if clip_loss > 0.0:
+        d = p.detach()
+        p = torch.clamp(p, max=float(d.mean() + clip_loss * d.std()))
+    if mask is not None:
+        p = p * mask
+    return p
+
+
+class _ReduceCandidates(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, op, *cands):
+        _C.require_cuda(*cands)
+        K = len(cands)
+        cands = [c.contiguous() for c in cands]
+        B, Cg, H, W = cands[0].shape
+        for c in cands:
+            if c.shape != cands[0].shape or c.dtype != cands[0].dtype:
+                raise ValueError('photometric candidates must share one shape and dtype')
+        dev, dt = cands[0].device, cands[0].dtype
+        out = torch.empty(1, dtype=dt, device=dev)
+        argmin = torch.empty((B, H, W), dtype=torch.int32, device=dev) if op == _C.REDUCE['min'] else None
+        ptrs = (C.c_void_p * K)(*[c.data_ptr() for c in cands])
+        ws, n = _ws(B, H * W, dev)
+        with torch.cuda.device(dev):
+            _C.check(_C.lib.psfm_reduce_candidates(K, B, Cg, H, W, _real(cands[0]), op, ptrs, _C.ptr(out),
+                                                   _C.ptr(argmin), _C.ptr(ws), n, _C.stream_ptr(dev)))
+        ctx.argmin, ctx.meta = argmin, (K, B, Cg, H, W, dt, dev, op)
+        return out.view(())
+
+    @staticmethod
+    def backward(ctx, g):
+        K, B, Cg, H, W, dt, dev, op = ctx.meta
+        g = g.to(dt).contiguous().view(1)
+        grads = [torch.empty((B, Cg, H, W), dtype=dt, device=dev) for _ in range(K)]
+        ptrs = (C.c_void_p * K)(*[t.data_ptr() for t in grads])
+        with torch.cuda.device(dev):
+            _C.check(_C.lib.psfm_reduce_candidates_backward(K, B, Cg, H, W, _C.F64 if dt == torch.float64 else _C.F32,
+                                                            op, _C.ptr(ctx.argmin), _C.ptr(g), ptrs, _C.stream_ptr(dev)))
+        return (None,) + tuple(grads)
+
+
+def reduce_candidates_op(candidates, op):
+    """reduce_photometric_loss for one scale: 'min' -> mean of the per-pixel min over all candidate
+    channels (first index wins ties); 'mean' -> average of the candidates' means."""
+    if op not in _C.REDUCE:
+        raise NotImplementedError('Unknown photometric_reduce_op: {}'.format(op))
+    if len(candidates) > 16:
+        raise ValueError('at most 16 photometric candidates per scale')
+    _real(candidates[0])
+    return _ReduceCandidates.apply(_C.REDUCE[op], *candidates)
+
+
+class _AbsMean(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        _C.require_cuda(x)
+        x = x.contiguous()
+        out = torch.empty(1, dtype=x.dtype, device=x.device)
+        ws, n = _ws(1, x.numel(), x.device)
+        with torch.cuda.device(x.device):
+            _C.check(_C.lib.psfm_abs_mean(x.numel(), _real(x), _C.ptr(x), _C.ptr(out), _C.ptr(ws), n,
+                                          _C.stream_ptr(x.device)))
+        ctx.save_for_backward(x)
+        return out.view(())
+
+    @staticmethod
+    def backward(ctx, g):
+        x, = ctx.saved_tensors
+        g = g.to(x.dtype).contiguous().view(1)
+        dx = torch.empty_like(x)
+        with torch.cuda.device(x.device):
+            _C.check(_C.lib.psfm_abs_mean_backward(x.numel(), _real(x), _C.ptr(x), _C.ptr(g), _C.ptr(dx),
+                                                   _C.stream_ptr(x.device)))
+        return dx
+
+
+def abs_mean_op(x):
+    """x.abs().mean() with a deterministic reduction."""
+    _real(x)
+    return _AbsMean.apply(x)
+
+
+class _Normalize(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, d):
+        _C.require_cuda(d)
+        d = d.contiguous()
+        B = d.shape[0]
+        N = d.numel() // B
+        out = torch.empty_like(d)
+        mean = torch.empty(B, dtype=d.dtype, device=d.device)
+        ws, n = _ws(B, N, d.device)
+        with torch.cuda.device(d.device):
+            _C.check(_C.lib.psfm_normalize(B, N, _real(d), _C.ptr(d), _C.ptr(out), _C.ptr(mean), _C.ptr(ws), n,
+                                           _C.stream_ptr(d.device)))
+        ctx.save_for_backward(d, mean)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        d, mean = ctx.saved_tensors
+        g = g.contiguous()
+        B = d.shape[0]
+        N = d.numel() // B
+        dd = torch.empty_like(d)
+        ws, n = _ws(B, N, d.device)
+        with torch.cuda.device(d.device):
+            _C.check(_C.lib.psfm_normalize_backward(B, N, _real(d), _C.ptr(d), _C.ptr(mean), _C.ptr(g), _C.ptr(dd),
+                                                    _C.ptr(ws), n, _C.stream_ptr(d.device)))
+        return dd
+
+
+def normalize_op(inv_depth):
+    """inv_depths_normalize for one map: divide by the per-image mean clamped at 1e-6."""
+    _real(inv_depth)
+    if inv_depth.dim() != 4 or inv_depth.shape[1] != 1:
+        raise ValueError('inverse depth maps must be [B,1,H,W]')
+    return _Normalize.apply(inv_depth)
+
+
+class _SmoothMaps(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, dn, image):
+        _C.require_cuda(dn, image)
+        dn = dn.contiguous()
+        image = image.to(dn.dtype).contiguous()
+        B, _, H, W = dn.shape
+        if tuple(image.shape) != (B, 3, H, W):
+            raise ValueError('image must be [B,3,H,W] matching the inverse depth map')
+        sx = torch.empty((B, 1, H, W - 1), dtype=dn.dtype, device=dn.device)
+        sy = torch.empty((B, 1, H - 1, W), dtype=dn.dtype, device=dn.device)
+        with torch.cuda.device(dn.device):
+            _C.check(_C.lib.psfm_smoothness_maps(B, H, W, _real(dn), _C.ptr(dn), _C.ptr(image), _C.ptr(sx), _C.ptr(sy),
+                                                 _C.stream_ptr(dn.device)))
+        ctx.save_for_backward(image)
+        return sx, sy
+
+    @staticmethod
+    def backward(ctx, gsx, gsy):
+        image, = ctx.saved_tensors
+        B, _, H, W = image.shape
+        gsx, gsy = gsx.contiguous(), gsy.contiguous()
+        ddn = torch.empty((B, 1, H, W), dtype=image.dtype, device=image.device)
+        with torch.cuda.device(image.device):
+            _C.check(_C.lib.psfm_smoothness_maps_backward(B, H, W, _real(image), _C.ptr(image), _C.ptr(gsx), _C.ptr(gsy),
+                                                          _C.ptr(ddn), _C.stream_ptr(image.device)))
+        return ddn, None
+
+
+def smoothness_op(inv_depth, image):
+    """calc_smoothness for one scale: (smoothness_x [B,1,H,W-1], smoothness_y [B,1,H-1,W]) of the
+    mean-normalised inverse depth, weighted by exp(-mean_c |image gradient|)."""
+    _no_grad_supported(image, 'the image of calc_smoothness')
+    return _SmoothMaps.apply(normalize_op(inv_depth), image)

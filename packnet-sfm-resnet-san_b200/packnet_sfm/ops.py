@@ -12,6 +12,8 @@ import os
 import torch
 
 from . import _C
+from .block_ops import (abs_mean_op, normalize_op, photometric_map_op, project_op, reconstruct_op,  # noqa: F401
+                        reduce_candidates_op, smoothness_op, ssim_op, transform_points_op)
 
 # 'fused': loss and unit-upstream gradients in one sweep (psfm_loss_forward_backward), the
 #          backward only applies the upstream scalar.
