@@ -11,8 +11,9 @@ scales, fp32, zeros padding, automask).  Prints ONE JSON line on rank 0.
 value      frames/s with the inputs resident in HBM; K steps between two CUDA events, max over ranks.
            Steps rotate over several resident input sets whose total footprint exceeds 3x the L2, so
            every step reads its inputs from HBM (no flush launches inside the timed region).
-e2e        the same metric through the public API with HOST (pinned) inputs: H2D copy of the
-           step's inputs + fwd+bwd + D2H read of the loss inside the timed region.
+e2e        the same metric through the public API with HOST (pinned) inputs: H2D copy of every
+           step's inputs (queued one step ahead on a copy stream, so it overlaps the previous
+           step's kernels) + fwd+bwd + D2H read of the loss, all inside the timed region.
 roofline   algorithmic bytes of the dominant kernel / its live CUDA-event time
            (psfm_profile_* hooks), against MEASURED_PEAKS.json.
 cpu_baseline / --impl reference: the CPU oracle (oracle/photometric_oracle.py, a port of the
@@ -313,16 +314,44 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    copy_stream = torch.cuda.Stream()
+
     def run_steps(k, e2e=False):
         """k steps; multi-GPU: one all-reduce of the loss triple per step, waited on one step later
-        so that it overlaps the next step's kernels (all are complete before the region ends)."""
+        so that it overlaps the next step's kernels (all are complete before the region ends).
+        e2e: every step's inputs come from pinned host memory.  The H2D copy of step i + 1 is queued on
+        a copy stream before step i is launched (double buffering over the rotating slots, the usual
+        data-loader prefetch), the loss of step i is read back to the host and waited for every step."""
         pending, h2d, d2h = None, 0, 0
         host_loss = torch.empty(1, dtype=torch.float32).pin_memory()
+        main = torch.cuda.current_stream()
+        ready, done = [None] * R, [None] * R
+
+        def prefetch(idx):
+            s = slots[idx]
+            with torch.cuda.stream(copy_stream):
+                if done[idx] is not None:
+                    copy_stream.wait_event(done[idx])     # the slot's previous step has consumed its inputs
+                n = s.upload()
+                ready[idx] = torch.cuda.Event()
+                ready[idx].record(copy_stream)
+            return n
+
+        if e2e:
+            copy_stream.wait_stream(main)
+            h2d = prefetch(0)
         for i in range(k):
             s = slots[i % R]
             if e2e:
-                h2d = s.upload()
+                if i + 1 < k and R > 1:
+                    prefetch((i + 1) % R)
+                main.wait_event(ready[i % R])
             loss = s.run()
+            if e2e:
+                done[i % R] = torch.cuda.Event()
+                done[i % R].record(main)
+                if R == 1 and i + 1 < k:
+                    prefetch(0)
             if world > 1:
                 if pending is not None:
                     pending.wait()
@@ -330,10 +359,12 @@ def run_ours(args):
                 pending = dist.all_reduce(red, async_op=True)
             if e2e:
                 host_loss.copy_(loss.detach(), non_blocking=True)
-                torch.cuda.current_stream().synchronize()
+                main.synchronize()
                 d2h = host_loss.numel() * 4
         if pending is not None:
             pending.wait()
+        if e2e:
+            main.wait_stream(copy_stream)
         return h2d, d2h
 
     # ---- value: inputs resident, K steps, CUDA events, max over ranks -------------------------------

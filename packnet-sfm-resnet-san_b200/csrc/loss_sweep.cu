@@ -336,8 +336,11 @@ __device__ __forceinline__ double signed_by(double mag, double x) {
   return x > 0.0 ? mag : (x < 0.0 ? -mag : 0.0);
 }
 
+#ifndef PSFM_SWEEP_MINB
+#define PSFM_SWEEP_MINB 1            // resident CTAs per SM the 2-context fp32 instantiation is compiled for
+#endif
 template <typename real, typename img_t, int PAD, bool RARE, int CT>
-__global__ void __launch_bounds__(CT ? 32 * CT : 256) sweep_kernel(const SweepParams SP) {
+__global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) == 4) ? PSFM_SWEEP_MINB : 1) sweep_kernel(const SweepParams SP) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const LossParams& P = SP.P;
   const SweepSet& S = SP.set;
