@@ -1,9 +1,12 @@
 // loss_sweep.cu -- single-pass photometric loss: loss AND gradients in one sweep over the inputs.
 //
-//   prep_kernel    once per resolution (shared by all full-resolution scales): window statistics of
-//                  the target image (mean, variance + C2), edge weights of the smoothness term, the
-//                  automask candidate (min / arg-min of the identity photometric terms) and the raw
-//                  per-image sums the smoothness normalisation needs.
+//   pack_kernel    once per resolution: every context image as a channel-interleaved, zero-bordered
+//                  4-vector image in the arithmetic type, so that one bilinear tap is ONE 16-byte load
+//                  and taps outside the image need no bounds test (zeros padding reads the border).
+//   prep_kernel    once per resolution (shared by all full-resolution scales): per-pixel records with
+//                  the target pixel, its window statistics (mean, variance + C2), the mask, the
+//                  automask candidate (min / arg-min of the identity photometric terms), the edge
+//                  weights of the smoothness term and the raw per-image sums its normalisation needs.
 //   stats_kernel   per (scale, image): clamped mean, smoothness sums, gradient coupling constant.
 //   sweep_kernel   the hot kernel.  One warp = 32 adjacent columns of one (image, scale, context);
 //                  it marches down the rows with the 3-row SSIM window and its adjoint in register
@@ -28,9 +31,9 @@ constexpr int kPrepVals = 3;         // sum d, sum |dx d| wx, sum |dy d| wy
 constexpr int kPrepInner = 30;       // columns a prep warp produces (32 lanes - 1 halo each side)
 constexpr int kPrepWarps = 4;        // independent warps per prep CTA
 constexpr int kInner = 28;           // columns a sweep warp produces (32 lanes - 2 halo each side)
-constexpr int kRing = 10;            // per-row values parked in shared memory between forward and adjoint
 
-constexpr int kRec = 8;              // reals per pixel record written by the prep kernel
+constexpr int kPadLo = 2;            // zero border of the packed context images: taps reach -2 .. size + 2
+constexpr int kPadHi = 3;
 
 struct SweepSet {                    // scales of equal resolution sharing the same images
   int ns;
@@ -38,10 +41,31 @@ struct SweepSet {                    // scales of equal resolution sharing the s
   int H, W;
   int nstrips, nchunks, chunk_h;     // sweep kernel decomposition
   int pstrips, pchunks, pchunk_h;    // prep kernel decomposition
-  void* rec;                         // real [B][H][W][kRec]: mean(y) x3, E[y^2]-mean(y)^2+C2 x3,
-                                     //   min identity photometric value (automask), its candidate index
+  int Hp, Wp;                        // padded size of the packed context images
+  void* ra;                          // real4 [B][H][W]: target pixel y x3, mask value
+  void* rb;                          // real4 [B][H][W]: mean(y) x3, min identity photometric value (automask)
+  void* rc;                          // real4 [B][H][W]: E[y^2]-mean(y)^2+C2 x3, candidate index of that min
   void* wxy;                         // real [B][H][W][2]: exp(-mean|dx I|), exp(-mean|dy I|)
+  void* ctxp[PSFM_MAX_CTX];          // real4 [B][Hp][Wp]: context image (r, g, b, 0), zero border
 };
+
+// 4-vector of the arithmetic type with 16-byte vector loads / stores
+template <typename real> struct alignas(16) Real4 { real x, y, z, w; };
+__device__ __forceinline__ Real4<float> ld4(const Real4<float>* p) {
+  const float4 v = __ldg((const float4*)p);
+  return Real4<float>{v.x, v.y, v.z, v.w};
+}
+__device__ __forceinline__ Real4<double> ld4(const Real4<double>* p) {
+  const double2 a = __ldg((const double2*)p), b = __ldg((const double2*)p + 1);
+  return Real4<double>{a.x, a.y, b.x, b.y};
+}
+__device__ __forceinline__ void st4(Real4<float>* p, float x, float y, float z, float w) {
+  *(float4*)p = make_float4(x, y, z, w);
+}
+__device__ __forceinline__ void st4(Real4<double>* p, double x, double y, double z, double w) {
+  ((double2*)p)[0] = make_double2(x, y);
+  ((double2*)p)[1] = make_double2(z, w);
+}
 
 template <typename real> struct SweepConsts {   // hyper-parameters pre-converted to the arithmetic type
   real ssim_w3;                      // ssim_loss_weight / 3
@@ -66,6 +90,26 @@ struct SweepParams {
 };
 
 // ------------------------------------------------------------------------------------------
+// pack kernel: grid (ceil(Hp * Wp / 256), C, B), 256 threads; one padded pixel per thread.
+// ------------------------------------------------------------------------------------------
+template <typename real, typename img_t>
+__global__ void __launch_bounds__(256) pack_kernel(const SweepParams SP) {
+  const SweepSet& S = SP.set;
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= S.Hp * S.Wp) return;
+  const int j = blockIdx.y, b = blockIdx.z;
+  const int yp = i / S.Wp, xp = i - yp * S.Wp;
+  const int y = yp - kPadLo, x = xp - kPadLo;
+  real r = real(0), g = real(0), bl = real(0);
+  if ((unsigned)y < (unsigned)S.H && (unsigned)x < (unsigned)S.W) {
+    const int plane = S.H * S.W;
+    const img_t* src = (const img_t*)SP.P.sc[S.scale[0]].ctx[j] + (size_t)b * 3 * plane + y * S.W + x;
+    r = ldimg<real>(src, 0); g = ldimg<real>(src, plane); bl = ldimg<real>(src, 2 * plane);
+  }
+  st4((Real4<real>*)S.ctxp[j] + (size_t)b * S.Hp * S.Wp + i, r, g, bl, real(0));
+}
+
+// ------------------------------------------------------------------------------------------
 // prep kernel: grid (ceil(punits / kPrepWarps), B), 32 * kPrepWarps threads; every warp is an
 // independent (strip, chunk) unit.  Lane l is column c0 - 1 + l; step t loads row t and finishes
 // row p = t - 1.  Pass j handles context j (pass 0 also the image-only outputs).
@@ -86,8 +130,11 @@ __global__ void __launch_bounds__(32 * kPrepWarps, 4) prep_kernel(const SweepPar
   const bool inner = (lane >= 1) && (lane <= kPrepInner) && (u < W);
   const ScaleDesc& S0 = P.sc[S.scale[0]];
   const img_t* image = (const img_t*)S0.image + (size_t)b * 3 * plane;
-  real* rec = (real*)S.rec + (size_t)b * plane * kRec;
+  Real4<real>* ra = (Real4<real>*)S.ra + (size_t)b * plane;
+  Real4<real>* rb = (Real4<real>*)S.rb + (size_t)b * plane;
+  Real4<real>* rc = (Real4<real>*)S.rc + (size_t)b * plane;
   real* wxy = (real*)S.wxy + (size_t)b * plane * 2;
+  const img_t* maskp = S0.mask ? (const img_t*)S0.mask + (size_t)b * plane : nullptr;
   const real ssim_w = (real)P.ssim_w, C1 = (real)P.C1, C2 = (real)P.C2;
   const real r3 = real(1) / real(3), r9 = real(1) / real(9);
   const bool smooth = P.smooth_w > 0.0;
@@ -142,7 +189,7 @@ __global__ void __launch_bounds__(32 * kPrepWarps, 4) prep_kernel(const SweepPar
 #pragma unroll
       for (int k = 0; k < PSFM_MAX_SCALES; ++k) dcur[k] = dn[k];
       real idprev = real(0);
-      if (j > 0 && emit) idprev = rec[(size_t)op * kRec + 6];
+      if (j > 0 && emit) idprev = rb[op].w;
       load_row(t + 1);
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
@@ -171,13 +218,7 @@ __global__ void __launch_bounds__(32 * kPrepWarps, 4) prep_kernel(const SweepPar
           my[c] = (hy[0][c] + hy[1][c] + hyn[c]) * r9;
           qy[c] = ((hy[0][3 + c] + hy[1][3 + c] + hyn[3 + c]) * r9 - my[c] * my[c]) + C2;
         }
-        if (j == 0) {
-#pragma unroll
-          for (int c = 0; c < 3; ++c) {
-            rec[(size_t)op * kRec + c] = my[c];
-            rec[(size_t)op * kRec + 3 + c] = qy[c];
-          }
-        }
+        real idv = real_inf<real>(), idk = real(0);
         if (P.automask) {
           real ds = real(0), ls = real(0);
 #pragma unroll
@@ -189,7 +230,13 @@ __global__ void __launch_bounds__(32 * kPrepWarps, 4) prep_kernel(const SweepPar
             ls += rabs(xp[c] - yp[c]);
           }
           const real val = ssim_w * (ds * r3) + (real(1) - ssim_w) * (ls * r3);
-          if (j == 0 || val < idprev) { rec[(size_t)op * kRec + 6] = val; rec[(size_t)op * kRec + 7] = (real)(2 * j + 1); }
+          if (j == 0) { idv = val; idk = real(1); }
+          else if (val < idprev) { rb[op].w = val; rc[op].w = (real)(2 * j + 1); }
+        }
+        if (j == 0) {
+          st4(ra + op, yp[0], yp[1], yp[2], maskp ? ldimg<real>(maskp, op) : real(1));
+          st4(rb + op, my[0], my[1], my[2], idv);
+          st4(rc + op, qy[0], qy[1], qy[2], idk);
         }
         if (j == 0 && smooth) {
           if (u + 1 < W) wx = rexp(-((rabs(yp[0] - ycp[0]) + rabs(yp[1] - ycp[1]) + rabs(yp[2] - ycp[2])) * r3));
@@ -306,18 +353,6 @@ template <typename real> __device__ __forceinline__ const SweepConsts<real>& swe
 template <> __device__ __forceinline__ const SweepConsts<float>& sweep_consts<float>(const SweepParams& SP) { return SP.cf; }
 template <> __device__ __forceinline__ const SweepConsts<double>& sweep_consts<double>(const SweepParams& SP) { return SP.cd; }
 
-// one pixel record of the prep kernel: 8 reals, 16-byte vector loads
-__device__ __forceinline__ void load_rec(const float* p, float* o) {
-  const float4 a = __ldg((const float4*)p), b = __ldg((const float4*)p + 1);
-  o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
-}
-__device__ __forceinline__ void load_rec(const double* p, double* o) {
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const double2 v = __ldg((const double2*)p + i);
-    o[2 * i] = v.x; o[2 * i + 1] = v.y;
-  }
-}
 __device__ __forceinline__ void load_pair(const float* p, float& a, float& b) {
   const float2 v = __ldg((const float2*)p);
   a = v.x; b = v.y;
@@ -339,8 +374,10 @@ __device__ __forceinline__ double signed_by(double mag, double x) {
 #ifndef PSFM_SWEEP_MINB
 #define PSFM_SWEEP_MINB 1            // resident CTAs per SM the 2-context fp32 instantiation is compiled for
 #endif
-template <typename real, typename img_t, int PAD, bool RARE, int CT>
+template <typename real, int PAD, bool RARE, int CT>
 __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) == 4) ? PSFM_SWEEP_MINB : 1) sweep_kernel(const SweepParams SP) {
+  typedef Real4<real> vec4;
+  constexpr int kRing = (PAD == PSFM_PAD_BORDER) ? 11 : 10;     // per-row values parked in shared memory
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const LossParams& P = SP.P;
   const SweepSet& S = SP.set;
@@ -361,15 +398,14 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
   real* dpart_s = photo_s + 2 * C * 32;                                    // [2][C][32]
 
   const ScaleDesc& SD = P.sc[s];
-  const img_t* img0 = (const img_t*)SD.image + (size_t)b * 3 * plane;
-  const img_t* ctx0 = (const img_t*)SD.ctx[j] + (size_t)b * 3 * plane;
-  // per-plane base pointers, made opaque so that every load is one IMAD.WIDE off a 32-bit pixel offset
-  const img_t *img1 = img0 + plane, *img2 = img0 + 2 * plane, *ctx1 = ctx0 + plane, *ctx2 = ctx0 + 2 * plane;
-  asm volatile("" : "+l"(img0), "+l"(img1), "+l"(img2), "+l"(ctx0), "+l"(ctx1), "+l"(ctx2));
+  const vec4* ctxp = (const vec4*)S.ctxp[j] + (size_t)b * S.Hp * S.Wp;
+  const vec4* ra = (const vec4*)S.ra + (size_t)b * plane;
+  const vec4* rb = (const vec4*)S.rb + (size_t)b * plane;
+  const vec4* rcp = (const vec4*)S.rc + (size_t)b * plane;
+  asm volatile("" : "+l"(ctxp), "+l"(ra), "+l"(rb), "+l"(rcp));   // opaque: one IMAD.WIDE per load off a 32-bit offset
   const real* invd = (const real*)SD.invd + (size_t)b * plane;
-  const real* rec = (const real*)S.rec + (size_t)b * plane * kRec;
   const real* wxy = (const real*)S.wxy + (size_t)b * plane * 2;
-  const img_t* maskp = (RARE && SD.mask) ? (const img_t*)SD.mask + (size_t)b * plane : nullptr;
+  const int Wp = S.Wp;
   const bool premap = RARE && P.premap;
   const bool smooth = P.smooth_w > 0.0;
 
@@ -421,8 +457,9 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
   int prev_q = -1;
   real* d_out = (real*)SD.d_invd + (size_t)b * plane;
 
-  // gather pipeline: geometry of `row`, the 12 tap loads go in flight, consumed one step later
-  real tap[12], wgt[8];
+  // gather pipeline: geometry of `row`, the 4 tap loads go in flight, consumed one step later
+  vec4 tap[4];
+  real twx = real(0), twy = real(0);
   auto start_row = [&](int row, real draw) {
     real dd = draw;
     if (premap) { real ch; dd = premap_fork<real>(draw, K.premap_lo, K.premap_hi, ch); }
@@ -433,22 +470,25 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
     const real p2 = (A0[2] + A1[2] * fv) * D + mt[2];
     const real iz = rrcp(rmax(p2, real(1e-5)));                   // camera.py:179
     const real ix = p0 * iz, iy = p1 * iz;
-    sample3_issue<real, img_t, PAD>(ctx0, ctx1, ctx2, H, W, ix, iy, wgt, tap);
+    real mx, my;
+    sample4_issue<real, vec4, PAD>(ctxp, H, W, Wp, kPadLo, ix, iy, twx, twy, mx, my, tap);
     real* rs = ring + (row & 3) * kRing * 32;
-    rs[6 * 32] = D;
-    rs[7 * 32] = (p2 >= real(1e-5)) ? iz : -iz;                   // sign flags the clamp
-    rs[8 * 32] = ix;
-    rs[9 * 32] = iy;
+    rs[6 * 32] = (p2 >= real(1e-5)) ? D : -D;                     // sign flags the clamp of p2
+    rs[7 * 32] = ix;
+    rs[8 * 32] = iy;
+    if (PAD == PSFM_PAD_BORDER) { rs[9 * 32] = iz * mx; rs[10 * 32] = iz * my; }
+    else rs[9 * 32] = iz;
   };
-  // prefetched operands of the next step: target row, pixel record (statistics + automask candidate)
-  real ynx[3], recn[kRec];
+  // prefetched operands of the next steps: target pixel (+ mask) record, statistics records
+  vec4 ran, rbn, rcn;
+  real mcur = real(1);                                             // mask value of row t - 1
   real dnx = __ldg(invd + reflect1(r0 - 2, H) * W + su);
   real dpre = __ldg(invd + reflect1(r0 - 1, H) * W + su);
   {
-    const int on = reflect1(r0 - 2, H) * W + su;
-#pragma unroll
-    ynx[0] = ldimg<real>(img0, on); ynx[1] = ldimg<real>(img1, on); ynx[2] = ldimg<real>(img2, on);
-    load_rec(rec + (min(max(r0 - 3, 0), H - 1) * W + su) * kRec, recn);
+    ran = ld4(ra + reflect1(r0 - 2, H) * W + su);
+    const int orec = min(max(r0 - 3, 0), H - 1) * W + su;
+    rbn = ld4(rb + orec);
+    rcn = ld4(rcp + orec);
   }
   start_row(r0 - 2, dnx);
 
@@ -469,28 +509,34 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
     const int par = t & 1;
     // ---------------- operands prefetched one step ago; issue the prefetch of the next step -----------
     const bool p_real = (p >= 0) && (p < H) && col_real;
-    real yt[3], rc[kRec];
+    real yt[3], myv[3], qyv[3], idmin, idcand;
     real wxq = real(0), wyq = real(0), m = real(1);
     {
-#pragma unroll
-      for (int c = 0; c < 3; ++c) yt[c] = ynx[c];
-#pragma unroll
-      for (int k = 0; k < kRec; ++k) rc[k] = recn[k];
+      yt[0] = ran.x; yt[1] = ran.y; yt[2] = ran.z;
+      myv[0] = rbn.x; myv[1] = rbn.y; myv[2] = rbn.z; idmin = rbn.w;
+      qyv[0] = rcn.x; qyv[1] = rcn.y; qyv[2] = rcn.z; idcand = rcn.w;
+      m = p_real ? mcur : real(0);                                 // 1 without a mask (every record component is consumed)
+      mcur = ran.w;
       d3 = d2; d2 = d1; d1 = d0;
       d0 = dnx;
       dnx = dpre;
       dpre = __ldg(invd + reflect1(t + 2, H) * W + su);
-      const int on = reflect1(t + 1, H) * W + su;
-#pragma unroll
-      ynx[0] = ldimg<real>(img0, on); ynx[1] = ldimg<real>(img1, on); ynx[2] = ldimg<real>(img2, on);
-      load_rec(rec + (min(max(p + 1, 0), H - 1) * W + su) * kRec, recn);
-      if (RARE && maskp) m = p_real ? ldimg<real>(maskp, p * W + u) : real(0);
+      ran = ld4(ra + reflect1(t + 1, H) * W + su);
+      const int orec = min(max(p + 1, 0), H - 1) * W + su;
+      rbn = ld4(rb + orec);
+      rcn = ld4(rcp + orec);
       if (j == 0 && smooth) load_pair(wxy + (min(max(q, 0), H - 1) * W + su) * 2, wxq, wyq);
     }
     // ---------------- finish the gather of row t (issued one step ago), start the one of row t + 1 ----
     {
       real x[3], gx[3], gy[3];
-      sample3_finish<real>(wgt, tap, x, gx, gy);
+      // the 4th components are zero by construction; consuming them keeps their registers allocated until the
+      // loads have landed (a dead component gets re-used at once, and that write-after-write then waits on the
+      // loads' scoreboard: measured 1.3 long-scoreboard stalls per issued instruction)
+      twx += (tap[0].w + tap[1].w) + (tap[2].w + tap[3].w);
+      bilerp<real>(tap[0].x, tap[1].x, tap[2].x, tap[3].x, twx, twy, x[0], gx[0], gy[0]);
+      bilerp<real>(tap[0].y, tap[1].y, tap[2].y, tap[3].y, twx, twy, x[1], gx[1], gy[1]);
+      bilerp<real>(tap[0].z, tap[1].z, tap[2].z, tap[3].z, twx, twy, x[2], gx[2], gy[2]);
       real* rs = ring + (t & 3) * kRing * 32;
 #pragma unroll
       for (int c = 0; c < 3; ++c) { rs[c * 32] = gx[c]; rs[(3 + c) * 32] = gy[c]; }
@@ -512,12 +558,11 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
     real F[9];
     {
       real ds = real(0), ls = real(0);
+      real st[3][8];
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
-        ds += ssim_dist_sums<real, true>(h[0][c * 3] + h[1][c * 3] + h[2][c * 3],
-                                         h[0][c * 3 + 1] + h[1][c * 3 + 1] + h[2][c * 3 + 1],
-                                         h[0][c * 3 + 2] + h[1][c * 3 + 2] + h[2][c * 3 + 2], rc[c], rc[3 + c], K.C1,
-                                         K.C2, &F[c * 3]);
+        ds += ssim_fwd<real>(h[0][c * 3] + h[1][c * 3] + h[2][c * 3], h[0][c * 3 + 1] + h[1][c * 3 + 1] + h[2][c * 3 + 1],
+                             h[0][c * 3 + 2] + h[1][c * 3 + 2] + h[2][c * 3 + 2], myv[c], qyv[c], K.C1, K.C2, st[c]);
         ls += rabs(xr[P1][c] - yr[P1][c]);
       }
       const real photo = K.ssim_w3 * ds + K.k1 * ls;
@@ -536,9 +581,9 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
           }
         }
       }
-      if (P.automask && p_real) {
-        const real vi = rc[6] * m;
-        const int ki = (int)rc[7];
+      if (p_real) {                                                // without automask the record holds +inf
+        const real vi = idmin * m;
+        const int ki = (int)idcand;
         if (vi < best || (vi == best && ki < sel)) { best = vi; sel = ki; }
       }
       w_old = w_cur;
@@ -546,7 +591,7 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
       if (j == 0 && p_real && col_inner && p >= r0 && p < r1) loss_acc += best;
       const real wf = w_cur * K.ssim_w3;
 #pragma unroll
-      for (int k = 0; k < 9; ++k) F[k] *= wf;                      // the coefficients are always finite
+      for (int c = 0; c < 3; ++c) ssim_grad<real>(st[c], myv[c], wf, &F[c * 3]);
     }
     finalize_row(par ^ 1);
     // ---------------- adjoint at row q ----------------------------------------------------------------
@@ -573,10 +618,10 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
       }
       gix = q_ok ? gix : real(0);
       giy = q_ok ? giy : real(0);
-      const real D = rq[6 * 32], izs = rq[7 * 32], ixq = rq[8 * 32], iyq = rq[9 * 32];
-      const real iz = rabs(izs);
-      const real dp0 = gix * iz, dp1 = giy * iz;
-      const real dp2 = (izs > real(0)) ? -(dp0 * ixq + dp1 * iyq) : real(0);
+      const real Ds = rq[6 * 32], ixq = rq[7 * 32], iyq = rq[8 * 32];
+      const real D = rabs(Ds);
+      const real dp0 = gix * rq[9 * 32], dp1 = giy * rq[(PAD == PSFM_PAD_BORDER ? 10 : 9) * 32];
+      const real dp2 = (Ds > real(0)) ? -(dp0 * ixq + dp1 * iyq) : real(0);
       const real fq = (real)q;
       const real dD = (A0[0] + A1[0] * fq) * dp0 + (A0[1] + A1[1] * fq) * dp1 + (A0[2] + A1[2] * fq) * dp2;
       real chain = real(1), dd = d2;
@@ -743,7 +788,7 @@ bool stream_eligible(const psfm_loss_cfg* cfg) {
 struct SweepPlan {
   int nsets;
   SweepSet sets[PSFM_MAX_SCALES];
-  size_t off_rec[PSFM_MAX_SCALES], off_wxy[PSFM_MAX_SCALES];                                         // per scale (a set uses its first scale's)
+  size_t off_rec[PSFM_MAX_SCALES], off_wxy[PSFM_MAX_SCALES], off_ctxp[PSFM_MAX_SCALES];                                         // per scale (a set uses its first scale's)
   size_t off_prep[PSFM_MAX_SCALES], off_stats[PSFM_MAX_SCALES], off_loss[PSFM_MAX_SCALES],
       off_pose[PSFM_MAX_SCALES];                                          // per scale
   int nunits[PSFM_MAX_SCALES];
@@ -784,6 +829,7 @@ static void make_plan(const psfm_loss_cfg* cfg, const psfm_loss_io* io, SweepPla
       S.scale[S.ns++] = k;
       used[k] = true;
     }
+    S.Hp = S.H + kPadLo + kPadHi; S.Wp = S.W + kPadLo + kPadHi;
     S.nstrips = cdiv(S.W, kInner);
     const int forced = env_int("PSFM_SWEEP_CHUNK", 0);
     S.chunk_h = forced > 0 ? (forced < S.H ? forced : S.H)
@@ -803,7 +849,8 @@ static void make_plan(const psfm_loss_cfg* cfg, const psfm_loss_io* io, SweepPla
     const int minc = Hs < kMinChunk ? Hs : kMinChunk;
     const size_t worst = (size_t)cdiv(Ws, kInner) * cdiv(Hs, minc);
     const size_t pworst = (size_t)cdiv(Ws, kPrepInner) * cdiv(Hs, minc);
-    pl.off_rec[s] = off;   off = al(off + px * kRec * rs);
+    pl.off_rec[s] = off;   off = al(off + px * 12 * rs);               // three real4 planes
+    pl.off_ctxp[s] = off;  off = al(off + (size_t)cfg->C * cfg->B * (Hs + kPadLo + kPadHi) * (Ws + kPadLo + kPadHi) * 4 * rs);
     pl.off_wxy[s] = off;   off = al(off + px * 2 * rs);
     pl.off_prep[s] = off;  off = al(off + (size_t)cfg->B * pworst * kPrepVals * sizeof(double));
     pl.off_stats[s] = off; off = al(off + (size_t)cfg->B * 4 * rs);
@@ -840,9 +887,9 @@ static void fill_consts(SweepConsts<real>& c, const LossParams& P, int s0) {
   }
 }
 
-template <typename real, typename img_t, int PAD, bool RARE, int CT>
+template <typename real, int PAD, bool RARE, int CT>
 static cudaError_t launch_sweep_ct(const SweepParams& SP, dim3 grid, int threads, size_t smem, cudaStream_t st) {
-  auto kern = sweep_kernel<real, img_t, PAD, RARE, CT>;
+  auto kern = sweep_kernel<real, PAD, RARE, CT>;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
@@ -852,13 +899,13 @@ static cudaError_t launch_sweep_ct(const SweepParams& SP, dim3 grid, int threads
 }
 
 // the common context counts get their own instantiation (unrolled candidate min, tighter launch bounds)
-template <typename real, typename img_t, int PAD, bool RARE>
+template <typename real, int PAD, bool RARE>
 static cudaError_t launch_sweep(const SweepParams& SP, dim3 grid, int threads, size_t smem, cudaStream_t st) {
   if (!RARE) {
-    if (SP.P.C == 2) return launch_sweep_ct<real, img_t, PAD, RARE, 2>(SP, grid, threads, smem, st);
-    if (SP.P.C == 4) return launch_sweep_ct<real, img_t, PAD, RARE, 4>(SP, grid, threads, smem, st);
+    if (SP.P.C == 2) return launch_sweep_ct<real, PAD, RARE, 2>(SP, grid, threads, smem, st);
+    if (SP.P.C == 4) return launch_sweep_ct<real, PAD, RARE, 4>(SP, grid, threads, smem, st);
   }
-  return launch_sweep_ct<real, img_t, PAD, RARE, 0>(SP, grid, threads, smem, st);
+  return launch_sweep_ct<real, PAD, RARE, 0>(SP, grid, threads, smem, st);
 }
 
 template <typename real, typename img_t>
@@ -875,32 +922,40 @@ static cudaError_t run_sweep(const psfm_loss_cfg* cfg, const psfm_loss_io* io, v
     SP.loss_part[s] = (double*)(w + pl.off_loss[s]);
     SP.pose_part[s] = w + pl.off_pose[s];
   }
-  bool rare = cfg->premap != 0;
-  for (int s = 0; s < cfg->n; ++s) rare = rare || io->mask[s] != nullptr;
+  const bool rare = cfg->premap != 0;     // masks travel in the pixel records and cost nothing extra
   for (int i = 0; i < pl.nsets; ++i) {
     SP.set = pl.sets[i];
     const int s0 = SP.set.scale[0];
-    SP.set.rec = w + pl.off_rec[s0];
+    {
+      const size_t px = (size_t)cfg->B * SP.set.H * SP.set.W * 4 * sizeof(real);
+      SP.set.ra = w + pl.off_rec[s0];
+      SP.set.rb = w + pl.off_rec[s0] + px;
+      SP.set.rc = w + pl.off_rec[s0] + 2 * px;
+      const size_t cpx = (size_t)cfg->B * SP.set.Hp * SP.set.Wp * 4 * sizeof(real);
+      for (int j = 0; j < PSFM_MAX_CTX; ++j) SP.set.ctxp[j] = j < cfg->C ? w + pl.off_ctxp[s0] + j * cpx : nullptr;
+    }
     SP.set.wxy = w + pl.off_wxy[s0];
     fill_consts(SP.cf, SP.P, s0);
     fill_consts(SP.cd, SP.P, s0);
     const SweepSet& S = SP.set;
     {
-      ProfScope ps(st, kTagFwd, cfg->smooth_w > 0.0 ? 2 : 1);
+      ProfScope ps(st, kTagFwd, cfg->smooth_w > 0.0 ? 3 : 2);
+      pack_kernel<real, img_t><<<dim3(cdiv(S.Hp * S.Wp, 256), cfg->C, cfg->B), 256, 0, st>>>(SP);
       prep_kernel<real, img_t><<<dim3(cdiv(S.pstrips * S.pchunks, kPrepWarps), cfg->B), 32 * kPrepWarps, 0, st>>>(SP);
       if (cfg->smooth_w > 0.0) stats_kernel<real><<<dim3(cfg->B, S.ns), 128, 0, st>>>(SP);
     }
-    const size_t smem = ((size_t)cfg->C * 4 * kRing * 32 + (size_t)4 * cfg->C * 32) * sizeof(real);
+    const int ring = cfg->padding == PSFM_PAD_BORDER ? 11 : 10;
+    const size_t smem = ((size_t)cfg->C * 4 * ring * 32 + (size_t)4 * cfg->C * 32) * sizeof(real);
     const dim3 grid(S.nstrips * S.nchunks, S.ns, cfg->B);
     const int threads = 32 * cfg->C;
     ProfScope ps(st, kTagFused, 1);
     cudaError_t e;
     if (cfg->padding == PSFM_PAD_BORDER)
-      e = rare ? launch_sweep<real, img_t, PSFM_PAD_BORDER, true>(SP, grid, threads, smem, st)
-               : launch_sweep<real, img_t, PSFM_PAD_BORDER, false>(SP, grid, threads, smem, st);
+      e = rare ? launch_sweep<real, PSFM_PAD_BORDER, true>(SP, grid, threads, smem, st)
+               : launch_sweep<real, PSFM_PAD_BORDER, false>(SP, grid, threads, smem, st);
     else
-      e = rare ? launch_sweep<real, img_t, PSFM_PAD_ZEROS, true>(SP, grid, threads, smem, st)
-               : launch_sweep<real, img_t, PSFM_PAD_ZEROS, false>(SP, grid, threads, smem, st);
+      e = rare ? launch_sweep<real, PSFM_PAD_ZEROS, true>(SP, grid, threads, smem, st)
+               : launch_sweep<real, PSFM_PAD_ZEROS, false>(SP, grid, threads, smem, st);
     if (e != cudaSuccess) return e;
   }
   FinalParams F;

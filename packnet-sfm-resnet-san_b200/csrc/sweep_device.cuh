@@ -132,4 +132,82 @@ __device__ __forceinline__ void sample3_finish(const real* wgt, const real* tap,
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// The same sample from a packed context image (pack_kernel of loss_sweep.cu): pixels are
+// (r, g, b, 0) 4-vectors with a zero border of kPadLo / kPadHi pixels, row pitch Wp.  One tap is one
+// 16-byte load; taps outside the image read the border, which is exactly what zeros padding
+// contributes to the value and to d/d(ix, iy).  The bilinear form is the factored one
+//   top = v00 + wx (v01 - v00), bot = v10 + wx (v11 - v10), out = top + wy (bot - top),
+//   d/d iy = bot - top, d/d ix = (v01 - v00) + wy ((v11 - v10) - (v01 - v00)).
+// PAD == border clips the coordinate; mx / my are 0 where clipped (zero gradient there).
+// ------------------------------------------------------------------------------------------
+template <typename real, typename vec4, int PAD>
+__device__ __forceinline__ void sample4_issue(const vec4* __restrict__ base, int H, int W, int Wp, int pad_lo, real ix,
+                                              real iy, real& wx, real& wy, real& mx, real& my, vec4* tap) {
+  mx = real(1); my = real(1);
+  if (PAD == PSFM_PAD_BORDER) {
+    if (!(ix > real(0))) { ix = real(0); mx = real(0); }
+    else if (ix >= real(W - 1)) { ix = real(W - 1); mx = real(0); }
+    if (!(iy > real(0))) { iy = real(0); my = real(0); }
+    else if (iy >= real(H - 1)) { iy = real(H - 1); my = real(0); }
+  } else {
+    // fully outside beyond [-1, size]: all four taps land in the zero border
+    ix = rmin(rmax(ix, real(-2)), real(W + 1));
+    iy = rmin(rmax(iy, real(-2)), real(H + 1));
+  }
+  const real fx = rfloor(ix), fy = rfloor(iy);
+  wx = ix - fx; wy = iy - fy;
+  const int o = ((int)fy + pad_lo) * Wp + ((int)fx + pad_lo);
+  const vec4* p0 = base + o;
+  const vec4* p1 = p0 + Wp;
+  tap[0] = ld4(p0); tap[1] = ld4(p0 + 1); tap[2] = ld4(p1); tap[3] = ld4(p1 + 1);
+}
+
+template <typename real>
+__device__ __forceinline__ void bilerp(real v00, real v01, real v10, real v11, real wx, real wy, real& out, real& gx,
+                                       real& gy) {
+  const real dxt = v01 - v00, dxb = v11 - v10;
+  const real top = dxt * wx + v00, bot = dxb * wx + v10;
+  gy = bot - top;
+  out = gy * wy + top;
+  gx = (dxb - dxt) * wy + dxt;
+}
+
+// ------------------------------------------------------------------------------------------
+// SSIM distance of one channel, forward and gradient halves (same function as ssim_dist_sums;
+// the gradient half takes the selection weight so that no separate scaling pass is needed).
+//   fwd: returns clamp((1 - ssim) / 2, 0, 1) and keeps {mx, a1, v1, b1, v2, inv, ssim} in st[7].
+//   grad: coef[0..2] = wgt * d dist / d (sum x, sum x^2 (already x2 for d x^2/dx), sum xy); wgt = 0 is
+//         safe (every factor is finite, also for a degenerate window of a padding row).
+// ------------------------------------------------------------------------------------------
+template <typename real>
+__device__ __forceinline__ real ssim_fwd(real Sx, real Sxx, real Sxy, real my, real qy, real C1, real C2, real* st) {
+  const real r9 = real(1) / real(9);
+  const real mx = Sx * r9;
+  const real mxy = mx * my;
+  const real a1 = real(2) * mxy + C1;
+  const real v1 = (Sxy * (real(2) * r9) + (C1 + C2)) - a1;
+  const real mx2 = mx * mx;
+  const real b1 = mx2 + (my * my + C1);
+  const real v2 = (Sxx * r9 + qy) - mx2;
+  const real inv = rrcp_fast(b1 * v2);
+  const real ssim = (a1 * v1) * inv;
+  const real dist = real(0.5) - real(0.5) * ssim;
+  st[0] = mx; st[1] = a1; st[2] = v1; st[3] = b1; st[4] = v2; st[5] = inv; st[6] = ssim;
+  st[7] = dist;
+  return rmin(rmax(dist, real(0)), real(1));
+}
+
+template <typename real>
+__device__ __forceinline__ void ssim_grad(const real* st, real my, real wgt, real* coef) {
+  const real mx = st[0], a1 = st[1], v1 = st[2], b1 = st[3], v2 = st[4], inv = st[5], dist = st[7];
+  const bool in = (dist >= real(0)) && (dist <= real(1));
+  // d dist = -0.5 d ssim inside the clamp range; act2 = 2 * wgt * (-0.5 / 9) / (b1 v2)
+  const real act2 = in ? (wgt * (real(-1) / real(9))) * inv : real(0);
+  const real ss = in ? st[6] : real(0);
+  coef[0] = act2 * (my * (v1 - a1) - (ss * mx) * (v2 - b1));
+  coef[1] = -act2 * (ss * b1);
+  coef[2] = act2 * a1;
+}
+
 }  // namespace psfm
