@@ -479,9 +479,28 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
     if (PAD == PSFM_PAD_BORDER) { rs[9 * 32] = iz * mx; rs[10 * 32] = iz * my; }
     else rs[9 * 32] = iz;
   };
+  // Consumes the taps in the same step that issued them (at its end): only the sample and its gradients
+  // are carried into the next step.  (Carrying the tap vectors across the loop edge made ptxas copy them
+  // right behind the loads in one of the three unrolled phases -- a full memory latency per three rows.)
+  real xcar[3] = {real(0), real(0), real(0)};
+  auto finish_row = [&](int row) {
+    real gx[3], gy[3];
+    // the 4th components are zero by construction; consuming them keeps their registers allocated until the
+    // loads have landed (a dead component gets re-used at once, and that write-after-write then waits on the
+    // loads' scoreboard: measured 1.3 long-scoreboard stalls per issued instruction)
+    twx += (tap[0].w + tap[1].w) + (tap[2].w + tap[3].w);
+    bilerp<real>(tap[0].x, tap[1].x, tap[2].x, tap[3].x, twx, twy, xcar[0], gx[0], gy[0]);
+    bilerp<real>(tap[0].y, tap[1].y, tap[2].y, tap[3].y, twx, twy, xcar[1], gx[1], gy[1]);
+    bilerp<real>(tap[0].z, tap[1].z, tap[2].z, tap[3].z, twx, twy, xcar[2], gx[2], gy[2]);
+    real* rs = ring + (row & 3) * kRing * 32;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) { rs[c * 32] = gx[c]; rs[(3 + c) * 32] = gy[c]; }
+  };
   // prefetched operands of the next steps: target pixel (+ mask) record, statistics records
   vec4 ran, rbn, rcn;
   real mcur = real(1);                                             // mask value of row t - 1
+  real wxn = real(0), wyn = real(0);                               // edge weights of row q + 1 (context 0 only)
+  if (j == 0 && smooth) load_pair(wxy + (min(max(r0 - 4, 0), H - 1) * W + su) * 2, wxn, wyn);
   real dnx = __ldg(invd + reflect1(r0 - 2, H) * W + su);
   real dpre = __ldg(invd + reflect1(r0 - 1, H) * W + su);
   {
@@ -491,6 +510,7 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
     rcn = ld4(rcp + orec);
   }
   start_row(r0 - 2, dnx);
+  finish_row(r0 - 2);
 
   auto finalize_row = [&](int par) {      // context 0 adds the other contexts' parts and stores the row
     if (j == 0 && prev_q >= 0) {
@@ -525,22 +545,13 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
       const int orec = min(max(p + 1, 0), H - 1) * W + su;
       rbn = ld4(rb + orec);
       rcn = ld4(rcp + orec);
-      if (j == 0 && smooth) load_pair(wxy + (min(max(q, 0), H - 1) * W + su) * 2, wxq, wyq);
+      wxq = wxn; wyq = wyn;
+      if (j == 0 && smooth) load_pair(wxy + (min(max(q + 1, 0), H - 1) * W + su) * 2, wxn, wyn);
     }
-    // ---------------- finish the gather of row t (issued one step ago), start the one of row t + 1 ----
+    // ---------------- start the gather of row t + 1 (finished at the end of this step) --------------------
     {
-      real x[3], gx[3], gy[3];
-      // the 4th components are zero by construction; consuming them keeps their registers allocated until the
-      // loads have landed (a dead component gets re-used at once, and that write-after-write then waits on the
-      // loads' scoreboard: measured 1.3 long-scoreboard stalls per issued instruction)
-      twx += (tap[0].w + tap[1].w) + (tap[2].w + tap[3].w);
-      bilerp<real>(tap[0].x, tap[1].x, tap[2].x, tap[3].x, twx, twy, x[0], gx[0], gy[0]);
-      bilerp<real>(tap[0].y, tap[1].y, tap[2].y, tap[3].y, twx, twy, x[1], gx[1], gy[1]);
-      bilerp<real>(tap[0].z, tap[1].z, tap[2].z, tap[3].z, twx, twy, x[2], gx[2], gy[2]);
-      real* rs = ring + (t & 3) * kRing * 32;
-#pragma unroll
-      for (int c = 0; c < 3; ++c) { rs[c * 32] = gx[c]; rs[(3 + c) * 32] = gy[c]; }
       start_row(t + 1, dnx);
+      const real* x = xcar;
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
         const real y = yt[c];
@@ -655,6 +666,8 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
         dpart_s[(par * C + j) * 32 + lane] = dphoto;
       }
     }
+    // ---------------- finish the gather of row t + 1: its loads had the whole step to land -----------------
+    finish_row(t + 1);
   };
 
   const int t0 = r0 - 2;
