@@ -375,7 +375,11 @@ __device__ __forceinline__ double signed_by(double mag, double x) {
 #define PSFM_SWEEP_MINB 1            // resident CTAs per SM the 2-context fp32 instantiation is compiled for
 #endif
 template <typename real, int PAD, bool RARE, int CT>
+#ifdef PSFM_SWEEP_MAXREG
+__global__ void __maxnreg__(PSFM_SWEEP_MAXREG) sweep_kernel(const SweepParams SP) {
+#else
 __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) == 4) ? PSFM_SWEEP_MINB : 1) sweep_kernel(const SweepParams SP) {
+#endif
   typedef Real4<real> vec4;
   constexpr int kRing = (PAD == PSFM_PAD_BORDER) ? 11 : 10;     // per-row values parked in shared memory
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -523,6 +527,7 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
     prev_q = -1;
   };
 
+  const int t0 = r0 - 2;
   auto step = [&](const int t, auto phc) {
     constexpr int PH = decltype(phc)::value, Q = (PH + 1) % 3, P1 = (PH + 2) % 3;
     const int p = t - 1, q = t - 2;
@@ -540,17 +545,20 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
       d3 = d2; d2 = d1; d1 = d0;
       d0 = dnx;
       dnx = dpre;
+      wxq = wxn; wyq = wyn;
+    }
+    // ---------------- prefetch of the next steps' operands, gather of row t + 1 ----------------------------
+    {
       dpre = __ldg(invd + reflect1(t + 2, H) * W + su);
       ran = ld4(ra + reflect1(t + 1, H) * W + su);
       const int orec = min(max(p + 1, 0), H - 1) * W + su;
       rbn = ld4(rb + orec);
       rcn = ld4(rcp + orec);
-      wxq = wxn; wyq = wyn;
       if (j == 0 && smooth) load_pair(wxy + (min(max(q + 1, 0), H - 1) * W + su) * 2, wxn, wyn);
-    }
-    // ---------------- start the gather of row t + 1 (finished at the end of this step) --------------------
-    {
       start_row(t + 1, dnx);
+    }
+    // ---------------- horizontal window sums of row t ------------------------------------------------------
+    {
       const real* x = xcar;
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
@@ -580,6 +588,7 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
       real best = photo * m;
       int sel = mycand;
       if (C > 1) {
+        // the contexts meet once per row (a split arrive / wait on an mbarrier measured slower than bar.sync)
         photo_s[(par * C + j) * 32 + lane] = photo;
         __syncthreads();
         best = real_inf<real>();
@@ -670,7 +679,6 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
     finish_row(t + 1);
   };
 
-  const int t0 = r0 - 2;
   for (int tb = t0; tb <= r1 + 1; tb += 3) {
     step(tb, IntC<0>());
     step(tb + 1, IntC<1>());
@@ -825,6 +833,27 @@ static int pick_chunk(int H, long warps_per_chunk_row, long want) {
   return best < kMinChunk ? (H < kMinChunk ? H : kMinChunk) : best;
 }
 
+// Rows per sweep unit.  A unit of h rows runs h + 4 steps (2 warm-up rows of the window, 2 of the adjoint),
+// rounded up to the 3-step unrolling; the grid runs in waves of (148 SMs x resident CTAs).  Pick the
+// height that minimises waves x steps (measured at config 2: 48 and 64 rows 242 us, 32 rows 259 us,
+// 96 rows 261 us, 24 rows 279 us -- the model orders them the same way).
+static int pick_sweep_chunk(int H, long ctas_per_chunk, int C, bool f64) {
+  static const int cand[] = {16, 24, 32, 48, 64, 96, 128, 192, 256, 384, 512, 1 << 30};
+  const long resident = 148L * ((f64 ? 4 : 8) / (C < 1 ? 1 : (C > 4 ? 4 : C)) > 0 ? (f64 ? 4 : 8) / (C < 1 ? 1 : (C > 4 ? 4 : C)) : 1);
+  int best = H;
+  double best_cost = 1e300;
+  for (int c : cand) {
+    const int ch = c < H ? c : H;
+    if (ch < kMinChunk && ch < H) continue;
+    const long chunks = cdiv(H, ch);
+    const long waves = (chunks * ctas_per_chunk + resident - 1) / resident;
+    const double cost = (double)waves * (double)((ch + 4 + 2) / 3 * 3);
+    if (cost < best_cost * 0.999) { best_cost = cost; best = ch; }
+    if (c >= H) break;
+  }
+  return best;
+}
+
 static void make_plan(const psfm_loss_cfg* cfg, const psfm_loss_io* io, SweepPlan& pl) {
   const size_t rs = cfg->real_dtype == PSFM_F64 ? 8 : 4;
   pl.nsets = 0;
@@ -846,7 +875,7 @@ static void make_plan(const psfm_loss_cfg* cfg, const psfm_loss_io* io, SweepPla
     S.nstrips = cdiv(S.W, kInner);
     const int forced = env_int("PSFM_SWEEP_CHUNK", 0);
     S.chunk_h = forced > 0 ? (forced < S.H ? forced : S.H)
-                           : pick_chunk(S.H, (long)S.nstrips * S.ns * cfg->B * cfg->C, 148L * 16 * 5 / 2);
+                           : pick_sweep_chunk(S.H, (long)S.nstrips * S.ns * cfg->B, cfg->C, cfg->real_dtype == PSFM_F64);
     if (S.chunk_h < kMinChunk) S.chunk_h = S.H < kMinChunk ? S.H : kMinChunk;
     S.nchunks = cdiv(S.H, S.chunk_h);
     S.pstrips = cdiv(S.W, kPrepInner);
