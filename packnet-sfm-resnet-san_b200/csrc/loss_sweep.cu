@@ -298,18 +298,19 @@ __global__ void __launch_bounds__(128) stats_kernel(const SweepParams SP) {
   const SweepSet& S = SP.set;
   const int b = blockIdx.x, s = S.scale[blockIdx.y];
   const int punits = S.pstrips * S.pchunks;
-  __shared__ double sh[3][128];
+  __shared__ double sh[3][4];
   double a[3] = {0.0, 0.0, 0.0};
   const double* base = SP.prep_part[s] + (size_t)b * punits * kPrepVals;
   for (int i = threadIdx.x; i < punits; i += blockDim.x)
     for (int k = 0; k < 3; ++k) a[k] += base[(size_t)i * kPrepVals + k];
-  for (int k = 0; k < 3; ++k) sh[k][threadIdx.x] = a[k];
-  __syncthreads();
-  for (int o = 64; o > 0; o >>= 1) {
-    if ((int)threadIdx.x < o)
-      for (int k = 0; k < 3; ++k) sh[k][threadIdx.x] += sh[k][threadIdx.x + o];
-    __syncthreads();
+  // fixed-order reduction: butterfly inside each warp, then the four warp sums in order
+  for (int k = 0; k < 3; ++k) {
+    a[k] = warp_allsum<double>(a[k]);
+    if ((threadIdx.x & 31) == 0) sh[k][threadIdx.x >> 5] = a[k];
   }
+  __syncthreads();
+  if (threadIdx.x == 0)
+    for (int k = 0; k < 3; ++k) sh[k][0] = ((sh[k][0] + sh[k][1]) + sh[k][2]) + sh[k][3];
   if (threadIdx.x == 0) {
     const double N = (double)S.H * S.W;
     const real mean = (real)(sh[0][0] / N);
@@ -741,30 +742,31 @@ __global__ void __launch_bounds__(256) final_kernel(const FinalParams F) {
   __shared__ double sh[256];
   const int tid = threadIdx.x;
   if (blockIdx.x == 0) {
+    // one pass over all scales: per-thread partial sums in a fixed order, one butterfly per warp, eight warp sums
     double photo = 0.0, smooth = 0.0;
     for (int s = 0; s < F.n; ++s) {
       double a = 0.0;
       const size_t cnt = (size_t)F.B * F.nunits[s];
       for (size_t i = tid; i < cnt; i += blockDim.x) a += F.loss_part[s][i];
-      sh[tid] = a;
-      __syncthreads();
-      for (int o = 128; o > 0; o >>= 1) {
-        if (tid < o) sh[tid] += sh[tid + o];
-        __syncthreads();
-      }
-      photo += sh[0] * F.inv_count[s];
-      __syncthreads();
-      if (F.smooth && tid == 0)
-        for (int b = 0; b < F.B; ++b) {
-          const real* st = (const real*)F.stats[s] + (size_t)b * 4;
-          smooth += (double)st[2] * F.coef_x[s] + (double)st[3] * F.coef_y[s];
-        }
+      photo += a * F.inv_count[s];
     }
+    if (F.smooth)
+      for (int i = tid; i < F.n * F.B; i += blockDim.x) {
+        const int s = i / F.B, b = i - s * F.B;
+        const real* st = (const real*)F.stats[s] + (size_t)b * 4;
+        smooth += (double)st[2] * F.coef_x[s] + (double)st[3] * F.coef_y[s];
+      }
+    photo = warp_allsum<double>(photo);
+    smooth = warp_allsum<double>(smooth);
+    if ((tid & 31) == 0) { sh[tid >> 5] = photo; sh[8 + (tid >> 5)] = smooth; }
+    __syncthreads();
     if (tid == 0) {
+      double ph = 0.0, sm = 0.0;
+      for (int w = 0; w < 8; ++w) { ph += sh[w]; sm += sh[8 + w]; }
       real* out = (real*)F.loss_out;
-      out[0] = (real)((real)photo + (real)smooth);
-      out[1] = (real)photo;
-      out[2] = (real)smooth;
+      out[0] = (real)((real)ph + (real)sm);
+      out[1] = (real)ph;
+      out[2] = (real)sm;
       *(real*)F.one = real(1);
     }
     return;
