@@ -881,7 +881,9 @@ static void make_plan(const psfm_loss_cfg* cfg, const psfm_loss_io* io, SweepPla
     if (S.chunk_h < kMinChunk) S.chunk_h = S.H < kMinChunk ? S.H : kMinChunk;
     S.nchunks = cdiv(S.H, S.chunk_h);
     S.pstrips = cdiv(S.W, kPrepInner);
-    S.pchunk_h = pick_chunk(S.H, (long)S.pstrips * cfg->B, 148L * 16);
+    const int pforced = env_int("PSFM_PREP_CHUNK", 0);
+    S.pchunk_h = pforced > 0 ? (pforced < S.H ? pforced : S.H) : pick_chunk(S.H, (long)S.pstrips * cfg->B, 148L * 16);
+    if (S.pchunk_h < kMinChunk) S.pchunk_h = S.H < kMinChunk ? S.H : kMinChunk;
     S.pchunks = cdiv(S.H, S.pchunk_h);
   }
   // workspace layout does not depend on the grouping: every scale owns worst-case sized regions
