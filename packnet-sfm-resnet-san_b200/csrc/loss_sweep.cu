@@ -444,14 +444,18 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
     cb = st[1];
   }
 
-  real h[3][9], hF[3][9], xr[3][3], yr[3][3];
+  // window state, by row phase; per-channel values live as a (channel 0, channel 1) pair + a scalar channel 2
+  // (pair_math.cuh); index m = 0: sums of x, 1: of x^2, 2: of x y (h) / their gradient coefficients (hF)
+  typedef P2<real> pr;
+  pr hA[3][3], hFA[3][3], xrA[3], yrA[3];
+  real hB[3][3], hFB[3][3], xrB[3], yrB[3];
 #pragma unroll
   for (int a = 0; a < 3; ++a) {
 #pragma unroll
-    for (int k = 0; k < 9; ++k) { h[a][k] = real(0); hF[a][k] = real(0); }
-#pragma unroll
-    for (int c = 0; c < 3; ++c) { xr[a][c] = real(0); yr[a][c] = real(0); }
+    for (int m = 0; m < 3; ++m) { hA[a][m] = pr(real(0)); hFA[a][m] = pr(real(0)); hB[a][m] = real(0); hFB[a][m] = real(0); }
+    xrA[a] = pr(real(0)); yrA[a] = pr(real(0)); xrB[a] = real(0); yrB[a] = real(0);
   }
+  const pr mu0P(mu0), mu2P(mu2);
 #pragma unroll
   for (int k = 0; k < 4 * kRing; ++k) ring[k * 32] = real(0);
   real S0a[3] = {real(0), real(0), real(0)}, Sva[3] = {real(0), real(0), real(0)}, S1a[3] = {real(0), real(0), real(0)};
@@ -487,19 +491,25 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
   // Consumes the taps in the same step that issued them (at its end): only the sample and its gradients
   // are carried into the next step.  (Carrying the tap vectors across the loop edge made ptxas copy them
   // right behind the loads in one of the three unrolled phases -- a full memory latency per three rows.)
-  real xcar[3] = {real(0), real(0), real(0)};
+  pr xcarA(real(0));
+  real xcarB = real(0);
   auto finish_row = [&](int row) {
-    real gx[3], gy[3];
-    // the 4th components are zero by construction; consuming them keeps their registers allocated until the
-    // loads have landed (a dead component gets re-used at once, and that write-after-write then waits on the
-    // loads' scoreboard: measured 1.3 long-scoreboard stalls per issued instruction)
-    twx += (tap[0].w + tap[1].w) + (tap[2].w + tap[3].w);
-    bilerp<real>(tap[0].x, tap[1].x, tap[2].x, tap[3].x, twx, twy, xcar[0], gx[0], gy[0]);
-    bilerp<real>(tap[0].y, tap[1].y, tap[2].y, tap[3].y, twx, twy, xcar[1], gx[1], gy[1]);
-    bilerp<real>(tap[0].z, tap[1].z, tap[2].z, tap[3].z, twx, twy, xcar[2], gx[2], gy[2]);
+    // channels 0, 1 as a pair; channel 2 rides with the (always zero) 4th component through the first two
+    // subtractions, which also keeps that component's register allocated until the load has landed (a dead
+    // component is re-used at once, and that write-after-write then waits on the loads' scoreboard: measured
+    // 1.3 long-scoreboard stalls per issued instruction)
+    pr gxA, gyA;
+    bilerp_v<pr>(pr(tap[0].x, tap[0].y), pr(tap[1].x, tap[1].y), pr(tap[2].x, tap[2].y), pr(tap[3].x, tap[3].y), pr(twx),
+                 pr(twy), xcarA, gxA, gyA);
+    const pr dt = pr(tap[1].z, tap[1].w) - pr(tap[0].z, tap[0].w), db = pr(tap[3].z, tap[3].w) - pr(tap[2].z, tap[2].w);
+    const real dxt = dt.lo() + dt.hi(), dxb = db.lo() + db.hi();     // the high lanes are 0 - 0: consumed on purpose
+    const real top = vfma(dxt, twx, tap[0].z), bot = vfma(dxb, twx, tap[2].z);
+    const real gyB = bot - top;
+    xcarB = vfma(gyB, twy, top);
+    const real gxB = vfma(dxb - dxt, twy, dxt);
     real* rs = ring + (row & 3) * kRing * 32;
-#pragma unroll
-    for (int c = 0; c < 3; ++c) { rs[c * 32] = gx[c]; rs[(3 + c) * 32] = gy[c]; }
+    rs[0 * 32] = gxA.lo(); rs[1 * 32] = gxA.hi(); rs[2 * 32] = gxB;
+    rs[3 * 32] = gyA.lo(); rs[4 * 32] = gyA.hi(); rs[5 * 32] = gyB;
   };
   // prefetched operands of the next steps: target pixel (+ mask) record, statistics records
   vec4 ran, rbn, rcn;
@@ -535,12 +545,10 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
     const int par = t & 1;
     // ---------------- operands prefetched one step ago; issue the prefetch of the next step -----------
     const bool p_real = (p >= 0) && (p < H) && col_real;
-    real yt[3], myv[3], qyv[3], idmin, idcand;
     real wxq = real(0), wyq = real(0), m = real(1);
+    const pr yA(ran.x, ran.y), myA(rbn.x, rbn.y), qyA(rcn.x, rcn.y);
+    const real yB = ran.z, myB = rbn.z, qyB = rcn.z, idmin = rbn.w, idcand = rcn.w;
     {
-      yt[0] = ran.x; yt[1] = ran.y; yt[2] = ran.z;
-      myv[0] = rbn.x; myv[1] = rbn.y; myv[2] = rbn.z; idmin = rbn.w;
-      qyv[0] = rcn.x; qyv[1] = rcn.y; qyv[2] = rcn.z; idcand = rcn.w;
       m = p_real ? mcur : real(0);                                 // 1 without a mask (every record component is consumed)
       mcur = ran.w;
       d3 = d2; d2 = d1; d1 = d0;
@@ -560,31 +568,31 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
     }
     // ---------------- horizontal window sums of row t ------------------------------------------------------
     {
-      const real* x = xcar;
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        const real y = yt[c];
-        const real z = x[c] * y;
-        xr[PH][c] = x[c];
-        yr[PH][c] = y;
-        const real xa = shfl_up1(x[c]), xc = shfl_dn1(x[c]);
-        const real za = shfl_up1(z), zc = shfl_dn1(z);
-        h[PH][c * 3 + 0] = xa + x[c] + xc;
-        h[PH][c * 3 + 1] = xa * xa + x[c] * x[c] + xc * xc;
-        h[PH][c * 3 + 2] = za + z + zc;
-      }
+      const pr xA = xcarA, zA = xA * yA;
+      const real xB = xcarB, zB = xB * yB;
+      xrA[PH] = xA; yrA[PH] = yA; xrB[PH] = xB; yrB[PH] = yB;
+      const pr xaA = shfl_up1(xA), xcA = shfl_dn1(xA), zaA = shfl_up1(zA), zcA = shfl_dn1(zA);
+      const real xaB = shfl_up1(xB), xcB = shfl_dn1(xB), zaB = shfl_up1(zB), zcB = shfl_dn1(zB);
+      hA[PH][0] = (xaA + xA) + xcA;
+      hA[PH][1] = vfma(xcA, xcA, vfma(xA, xA, xaA * xaA));
+      hA[PH][2] = (zaA + zA) + zcA;
+      hB[PH][0] = (xaB + xB) + xcB;
+      hB[PH][1] = vfma(xcB, xcB, vfma(xB, xB, xaB * xaB));
+      hB[PH][2] = (zaB + zB) + zcB;
     }
     // ---------------- SSIM + L1 at row p, candidate min across the contexts --------------------------
-    real F[9];
+    pr FA[3];
+    real FB[3];
     {
-      real ds = real(0), ls = real(0);
-      real st[3][8];
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        ds += ssim_fwd<real>(h[0][c * 3] + h[1][c * 3] + h[2][c * 3], h[0][c * 3 + 1] + h[1][c * 3 + 1] + h[2][c * 3 + 1],
-                             h[0][c * 3 + 2] + h[1][c * 3 + 2] + h[2][c * 3 + 2], myv[c], qyv[c], K.C1, K.C2, st[c]);
-        ls += rabs(xr[P1][c] - yr[P1][c]);
-      }
+      SsimSt<pr> stA;
+      SsimSt<real> stB;
+      const pr dA = ssim_fwd_v<real, pr>((hA[0][0] + hA[1][0]) + hA[2][0], (hA[0][1] + hA[1][1]) + hA[2][1],
+                                         (hA[0][2] + hA[1][2]) + hA[2][2], myA, qyA, K.C1, K.C2, stA);
+      const real dB = ssim_fwd_v<real, real>((hB[0][0] + hB[1][0]) + hB[2][0], (hB[0][1] + hB[1][1]) + hB[2][1],
+                                             (hB[0][2] + hB[1][2]) + hB[2][2], myB, qyB, K.C1, K.C2, stB);
+      const real ds = vclamp01_sum(dA) + vclamp01_sum(dB);
+      const pr lA = xrA[P1] - yrA[P1];
+      const real ls = (rabs(lA.lo()) + rabs(lA.hi())) + rabs(xrB[P1] - yrB[P1]);
       const real photo = K.ssim_w3 * ds + K.k1 * ls;
       real best = photo * m;
       int sel = mycand;
@@ -611,32 +619,35 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
       w_cur = (p_real && sel == mycand) ? K.inv_count * m : real(0);
       if (j == 0 && p_real && col_inner && p >= r0 && p < r1) loss_acc += best;
       const real wf = w_cur * K.ssim_w3;
-#pragma unroll
-      for (int c = 0; c < 3; ++c) ssim_grad<real>(st[c], myv[c], wf, &F[c * 3]);
+      ssim_grad_v<real, pr>(stA, myA, wf, FA);
+      ssim_grad_v<real, real>(stB, myB, wf, FB);
     }
     finalize_row(par ^ 1);
     // ---------------- adjoint at row q ----------------------------------------------------------------
     {
 #pragma unroll
-      for (int k = 0; k < 9; ++k) {
-        const real Fa = shfl_up1(F[k]), Fc = shfl_dn1(F[k]);
-        hF[P1][k] = mu0 * Fa + F[k] + mu2 * Fc;
+      for (int m = 0; m < 3; ++m) {
+        hFA[P1][m] = vfma(mu2P, shfl_dn1(FA[m]), vfma(mu0P, shfl_up1(FA[m]), FA[m]));
+        hFB[P1][m] = vfma(mu2, shfl_dn1(FB[m]), vfma(mu0, shfl_up1(FB[m]), FB[m]));
       }
       const bool q_ok = (q >= r0) && (q < r1) && col_inner;
       const real mv0 = (q == 1) ? real(2) : real(1), mv2 = (q == H - 2) ? real(2) : real(1);
+      const pr mv0P(mv0), mv2P(mv2);
       const real* rq = ring + (q & 3) * kRing * 32;
       const real wk = w_old * K.k1;
-      real gix = real(0), giy = real(0);
+      pr sA[3];
+      real sB[3];
 #pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        const real sa = mv0 * hF[PH][c * 3 + 0] + hF[Q][c * 3 + 0] + mv2 * hF[P1][c * 3 + 0];
-        const real sb = mv0 * hF[PH][c * 3 + 1] + hF[Q][c * 3 + 1] + mv2 * hF[P1][c * 3 + 1];
-        const real sc = mv0 * hF[PH][c * 3 + 2] + hF[Q][c * 3 + 2] + mv2 * hF[P1][c * 3 + 2];
-        const real xq = xr[Q][c], yq = yr[Q][c];
-        const real dl = sa + xq * sb + yq * sc + signed_by(wk, xq - yq);
-        gix += dl * rq[c * 32];
-        giy += dl * rq[(3 + c) * 32];
+      for (int m = 0; m < 3; ++m) {
+        sA[m] = vfma(mv2P, hFA[P1][m], vfma(mv0P, hFA[PH][m], hFA[Q][m]));
+        sB[m] = vfma(mv2, hFB[P1][m], vfma(mv0, hFB[PH][m], hFB[Q][m]));
       }
+      const pr xqA = xrA[Q], yqA = yrA[Q], eA = xqA - yqA;
+      const real xqB = xrB[Q], yqB = yrB[Q];
+      const pr dlA = vfma(yqA, sA[2], vfma(xqA, sA[1], sA[0])) + pr(signed_by(wk, eA.lo()), signed_by(wk, eA.hi()));
+      const real dlB = vfma(yqB, sB[2], vfma(xqB, sB[1], sB[0])) + signed_by(wk, xqB - yqB);
+      real gix = dlA.lo() * rq[0 * 32] + dlA.hi() * rq[1 * 32] + dlB * rq[2 * 32];
+      real giy = dlA.lo() * rq[3 * 32] + dlA.hi() * rq[4 * 32] + dlB * rq[5 * 32];
       gix = q_ok ? gix : real(0);
       giy = q_ok ? giy : real(0);
       const real Ds = rq[6 * 32], ixq = rq[7 * 32], iyq = rq[8 * 32];

@@ -9,6 +9,7 @@
 // function of the inputs, which the fp64 instantiation checks to 1e-10 against the oracle.
 #pragma once
 #include "psfm_device.cuh"
+#include "pair_math.cuh"
 
 namespace psfm {
 
@@ -208,6 +209,78 @@ __device__ __forceinline__ void ssim_grad(const real* st, real my, real wgt, rea
   coef[0] = act2 * (my * (v1 - a1) - (ss * mx) * (v2 - b1));
   coef[1] = -act2 * (ss * b1);
   coef[2] = act2 * a1;
+}
+
+// ------------------------------------------------------------------------------------------
+// Value-type generic forms (V = real for one channel, P2<real> for a channel pair; pair_math.cuh)
+// ------------------------------------------------------------------------------------------
+template <typename real> __device__ __forceinline__ P2<real> shfl_up1(P2<real> v) {
+  return P2<real>(shfl_up1(v.lo()), shfl_up1(v.hi()));
+}
+template <typename real> __device__ __forceinline__ P2<real> shfl_dn1(P2<real> v) {
+  return P2<real>(shfl_dn1(v.lo()), shfl_dn1(v.hi()));
+}
+__device__ __forceinline__ float vrcp_fast(float x) { return rrcp_fast(x); }
+__device__ __forceinline__ double vrcp_fast(double x) { return rrcp_fast(x); }
+template <typename real> __device__ __forceinline__ P2<real> vrcp_fast(P2<real> x) {
+  return P2<real>(rrcp_fast(x.lo()), rrcp_fast(x.hi()));
+}
+// sum over the lanes of clamp(v, 0, 1)
+__device__ __forceinline__ float vclamp01_sum(float v) { return rmin(rmax(v, 0.0f), 1.0f); }
+__device__ __forceinline__ double vclamp01_sum(double v) { return rmin(rmax(v, 0.0), 1.0); }
+template <typename real> __device__ __forceinline__ real vclamp01_sum(P2<real> v) {
+  return rmin(rmax(v.lo(), real(0)), real(1)) + rmin(rmax(v.hi(), real(0)), real(1));
+}
+// lane-wise (0 <= d <= 1) ? a : 0
+__device__ __forceinline__ float vsel_in01(float d, float a) { return (d >= 0.0f && d <= 1.0f) ? a : 0.0f; }
+__device__ __forceinline__ double vsel_in01(double d, double a) { return (d >= 0.0 && d <= 1.0) ? a : 0.0; }
+template <typename real> __device__ __forceinline__ P2<real> vsel_in01(P2<real> d, P2<real> a) {
+  return P2<real>(vsel_in01(d.lo(), a.lo()), vsel_in01(d.hi(), a.hi()));
+}
+__device__ __forceinline__ float vneg(float a) { return -a; }
+__device__ __forceinline__ double vneg(double a) { return -a; }
+template <typename real> __device__ __forceinline__ P2<real> vneg(P2<real> a) { return P2<real>(-a.lo(), -a.hi()); }
+
+template <typename V> struct SsimSt { V mx, a1, v1, b1, v2, inv, ssim, dist; };
+
+// forward half: returns the UNclamped distance (1 - ssim) / 2 per lane and keeps the factors
+template <typename real, typename V>
+__device__ __forceinline__ V ssim_fwd_v(V Sx, V Sxx, V Sxy, V my, V qy, real C1, real C2, SsimSt<V>& st) {
+  typedef Bc<V, real> B;
+  const V r9 = B::of(real(1) / real(9));
+  st.mx = Sx * r9;
+  const V mxy = st.mx * my;
+  st.a1 = vfma(mxy, B::of(real(2)), B::of(C1));
+  st.v1 = vfma(Sxy, B::of(real(2) / real(9)), B::of(C1 + C2)) - st.a1;
+  const V mx2 = st.mx * st.mx;
+  st.b1 = mx2 + vfma(my, my, B::of(C1));
+  st.v2 = vfma(Sxx, r9, qy) - mx2;
+  st.inv = vrcp_fast(st.b1 * st.v2);
+  st.ssim = (st.a1 * st.v1) * st.inv;
+  st.dist = vfma(st.ssim, B::of(real(-0.5)), B::of(real(0.5)));
+  return st.dist;
+}
+
+// gradient half: coef[0..2] = wgt * d clamp(dist) / d (sum x, sum x^2 (already x2 for d x^2/dx), sum xy)
+template <typename real, typename V>
+__device__ __forceinline__ void ssim_grad_v(const SsimSt<V>& st, V my, real wgt, V* coef) {
+  typedef Bc<V, real> B;
+  // inside the clamp range d dist = -0.5 d ssim, outside 0; every factor stays finite (see ssim_dist_sums)
+  const V act2 = vsel_in01(st.dist, B::of(wgt * (real(-1) / real(9))) * st.inv);
+  const V ssn = vsel_in01(st.dist, vneg(st.ssim));
+  const V t1 = my * (st.v1 - st.a1);
+  coef[0] = act2 * vfma(ssn * st.mx, st.v2 - st.b1, t1);
+  coef[1] = act2 * (ssn * st.b1);
+  coef[2] = act2 * st.a1;
+}
+
+template <typename V>
+__device__ __forceinline__ void bilerp_v(V v00, V v01, V v10, V v11, V wx, V wy, V& out, V& gx, V& gy) {
+  const V dxt = v01 - v00, dxb = v11 - v10;
+  const V top = vfma(dxt, wx, v00), bot = vfma(dxb, wx, v10);
+  gy = bot - top;
+  out = vfma(gy, wy, top);
+  gx = vfma(dxb - dxt, wy, dxt);
 }
 
 }  // namespace psfm
