@@ -1,9 +1,10 @@
 // loss_sweep.cu -- single-pass photometric loss: loss AND gradients in one sweep over the inputs.
 //
-//   pack_kernel    once per resolution: every context image as a channel-interleaved, zero-bordered
-//                  4-vector image in the arithmetic type, so that one bilinear tap is ONE 16-byte load
-//                  and taps outside the image need no bounds test (zeros padding reads the border).
-//   prep_kernel    once per resolution (shared by all full-resolution scales): per-pixel records with
+//   border_kernel  zero frame of the packed context images (below).
+//   prep_kernel    once per resolution (shared by all full-resolution scales): every context image as a
+//                  channel-interleaved, zero-bordered 4-vector image in the arithmetic type, so that one
+//                  bilinear tap is ONE 16-byte load and taps outside the image need no bounds test (zeros
+//                  padding reads the border); per-pixel records with
 //                  the target pixel, its window statistics (mean, variance + C2), the mask, the
 //                  automask candidate (min / arg-min of the identity photometric terms), the edge
 //                  weights of the smoothness term and the raw per-image sums its normalisation needs.
@@ -49,6 +50,8 @@ struct SweepSet {                    // scales of equal resolution sharing the s
   void* ctxp[PSFM_MAX_CTX];          // real4 [B][Hp][Wp]: context image (r, g, b, 0), zero border
 };
 
+template <int V> struct IntC { static constexpr int value = V; };
+
 // 4-vector of the arithmetic type with 16-byte vector loads / stores
 template <typename real> struct alignas(16) Real4 { real x, y, z, w; };
 __device__ __forceinline__ Real4<float> ld4(const Real4<float>* p) {
@@ -90,32 +93,37 @@ struct SweepParams {
 };
 
 // ------------------------------------------------------------------------------------------
-// pack kernel: grid (ceil(Hp * Wp / 256), C, B), 256 threads; one padded pixel per thread.
+// border kernel: zero frame of the packed context images.  grid (Hp, C, B), 128 threads; block = one
+// padded row: a frame row is cleared entirely, an image row only in its 2 + 3 frame columns.
 // ------------------------------------------------------------------------------------------
-template <typename real, typename img_t>
-__global__ void __launch_bounds__(256) pack_kernel(const SweepParams SP) {
+template <typename real>
+__global__ void __launch_bounds__(128) border_kernel(const SweepParams SP) {
   const SweepSet& S = SP.set;
-  const int i = blockIdx.x * 256 + threadIdx.x;
-  if (i >= S.Hp * S.Wp) return;
-  const int j = blockIdx.y, b = blockIdx.z;
-  const int yp = i / S.Wp, xp = i - yp * S.Wp;
-  const int y = yp - kPadLo, x = xp - kPadLo;
-  real r = real(0), g = real(0), bl = real(0);
-  if ((unsigned)y < (unsigned)S.H && (unsigned)x < (unsigned)S.W) {
-    const int plane = S.H * S.W;
-    const img_t* src = (const img_t*)SP.P.sc[S.scale[0]].ctx[j] + (size_t)b * 3 * plane + y * S.W + x;
-    r = ldimg<real>(src, 0); g = ldimg<real>(src, plane); bl = ldimg<real>(src, 2 * plane);
+  const int yp = blockIdx.x, j = blockIdx.y, b = blockIdx.z;
+  Real4<real>* row = (Real4<real>*)S.ctxp[j] + ((size_t)b * S.Hp + yp) * S.Wp;
+  const bool frame_row = (yp < kPadLo) || (yp >= kPadLo + S.H);
+  if (frame_row) {
+    for (int x = threadIdx.x; x < S.Wp; x += blockDim.x) st4(row + x, real(0), real(0), real(0), real(0));
+  } else if (threadIdx.x < kPadLo + kPadHi) {
+    const int x = threadIdx.x < kPadLo ? threadIdx.x : S.W + threadIdx.x;
+    st4(row + x, real(0), real(0), real(0), real(0));
   }
-  st4((Real4<real>*)S.ctxp[j] + (size_t)b * S.Hp * S.Wp + i, r, g, bl, real(0));
 }
 
 // ------------------------------------------------------------------------------------------
 // prep kernel: grid (ceil(punits / kPrepWarps), B), 32 * kPrepWarps threads; every warp is an
-// independent (strip, chunk) unit.  Lane l is column c0 - 1 + l; step t loads row t and finishes
-// row p = t - 1.  Pass j handles context j (pass 0 also the image-only outputs).
+// independent (strip, chunk) unit.  Lane l is column c0 - 1 + l; step t loads row t + 1 and finishes
+// row p = t - 1.  One pass over the rows handles the CT contexts [j0, j0 + CT) together (packed copy,
+// identity-reprojection term); the pass with j0 == 0 also emits the image-only outputs.
+// Per-channel arithmetic runs on (channel 0, channel 1) pairs + a scalar channel 2 (pair_math.cuh).
 // ------------------------------------------------------------------------------------------
-template <typename real, typename img_t>
-__global__ void __launch_bounds__(32 * kPrepWarps, 4) prep_kernel(const SweepParams SP) {
+__device__ __forceinline__ int value_bits(float v) { return __float_as_int(v); }
+__device__ __forceinline__ int value_bits(double v) { return __double2hiint(v); }
+
+template <typename real, typename img_t, int CT, bool AUTOMASK, bool FIRST>
+__global__ void __launch_bounds__(32 * kPrepWarps) prep_kernel(const SweepParams SP, const int j0) {
+  typedef P2<real> pr;
+  typedef Real4<real> vec4;
   const LossParams& P = SP.P;
   const SweepSet& S = SP.set;
   const int lane = threadIdx.x & 31;
@@ -128,17 +136,27 @@ __global__ void __launch_bounds__(32 * kPrepWarps, 4) prep_kernel(const SweepPar
   const int u = strip * kPrepInner - 1 + lane, su = reflect1(u, W);
   const int r0 = chunk * S.pchunk_h, r1 = min(r0 + S.pchunk_h, H);
   const bool inner = (lane >= 1) && (lane <= kPrepInner) && (u < W);
+  constexpr bool first = FIRST;
   const ScaleDesc& S0 = P.sc[S.scale[0]];
-  const img_t* image = (const img_t*)S0.image + (size_t)b * 3 * plane;
-  Real4<real>* ra = (Real4<real>*)S.ra + (size_t)b * plane;
-  Real4<real>* rb = (Real4<real>*)S.rb + (size_t)b * plane;
-  Real4<real>* rc = (Real4<real>*)S.rc + (size_t)b * plane;
+  const img_t* y0p = (const img_t*)S0.image + (size_t)b * 3 * plane;
+  const img_t *y1p = y0p + plane, *y2p = y0p + 2 * plane;
+  asm volatile("" : "+l"(y0p), "+l"(y1p), "+l"(y2p));      // opaque: one IMAD.WIDE per load off a 32-bit offset
+  const img_t* xp0[CT];
+  vec4* cpk[CT];
+#pragma unroll
+  for (int jj = 0; jj < CT; ++jj) {
+    xp0[jj] = (const img_t*)S0.ctx[j0 + jj] + (size_t)b * 3 * plane;
+    cpk[jj] = (vec4*)S.ctxp[j0 + jj] + (size_t)b * S.Hp * S.Wp + kPadLo * S.Wp + kPadLo;
+  }
+  vec4* ra = (vec4*)S.ra + (size_t)b * plane;
+  vec4* rb = (vec4*)S.rb + (size_t)b * plane;
+  vec4* rc = (vec4*)S.rc + (size_t)b * plane;
   real* wxy = (real*)S.wxy + (size_t)b * plane * 2;
   const img_t* maskp = S0.mask ? (const img_t*)S0.mask + (size_t)b * plane : nullptr;
-  const real ssim_w = (real)P.ssim_w, C1 = (real)P.C1, C2 = (real)P.C2;
+  const real C1 = (real)P.C1, C2 = (real)P.C2;
+  const real kd = (real)P.ssim_w / real(3), kl = (real(1) - (real)P.ssim_w) / real(3);
   const real r3 = real(1) / real(3), r9 = real(1) / real(9);
-  const bool smooth = P.smooth_w > 0.0;
-  const int npass = P.automask ? P.C : 1;
+  const bool smooth = first && P.smooth_w > 0.0;
 
   real sums[PSFM_MAX_SCALES][kPrepVals];
 #pragma unroll
@@ -146,132 +164,167 @@ __global__ void __launch_bounds__(32 * kPrepWarps, 4) prep_kernel(const SweepPar
 #pragma unroll
     for (int i = 0; i < kPrepVals; ++i) sums[k][i] = real(0);
 
-  for (int j = 0; j < npass; ++j) {
-    const img_t* ctx = (const img_t*)S0.ctx[j] + (size_t)b * 3 * plane;
-    real hy[2][6], hx[2][9];            // horizontal sums of the two previous rows
-    real yp[3], ycp[3], xp[3];          // previous row: y, right neighbour of y, x
-    real dp[PSFM_MAX_SCALES];           // previous row of the raw inverse depths
+  // horizontal sums of the two previous rows: y: {sum y, sum y^2}; context: {sum x, sum x^2, sum x y}
+  pr hyA[2][2], hxA[CT][2][3], ypA(real(0)), ycpA(real(0)), xpA[CT];
+  real hyB[2][2], hxB[CT][2][3], ypB = real(0), ycpB = real(0), xpB[CT];
+  real dp[PSFM_MAX_SCALES];
 #pragma unroll
-    for (int a = 0; a < 2; ++a) {
+  for (int a = 0; a < 2; ++a) {
+    hyA[a][0] = pr(real(0)); hyA[a][1] = pr(real(0)); hyB[a][0] = real(0); hyB[a][1] = real(0);
 #pragma unroll
-      for (int k = 0; k < 6; ++k) hy[a][k] = real(0);
+    for (int jj = 0; jj < CT; ++jj)
 #pragma unroll
-      for (int k = 0; k < 9; ++k) hx[a][k] = real(0);
-    }
+      for (int m = 0; m < 3; ++m) { hxA[jj][a][m] = pr(real(0)); hxB[jj][a][m] = real(0); }
+  }
 #pragma unroll
-    for (int c = 0; c < 3; ++c) { yp[c] = real(0); ycp[c] = real(0); xp[c] = real(0); }
+  for (int jj = 0; jj < CT; ++jj) { xpA[jj] = pr(real(0)); xpB[jj] = real(0); }
 #pragma unroll
-    for (int k = 0; k < PSFM_MAX_SCALES; ++k) dp[k] = real(0);
+  for (int k = 0; k < PSFM_MAX_SCALES; ++k) dp[k] = real(0);
 
-    // software pipeline: the loads of row t + 1 are issued before row t is processed
-    real yn[3], xn[3] = {real(0), real(0), real(0)}, dn[PSFM_MAX_SCALES] = {real(0), real(0), real(0), real(0)};
-    auto load_row = [&](int t) {
-      const int o = reflect1(t, H) * W + su;
+  const real* dptr[PSFM_MAX_SCALES];
 #pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        yn[c] = ldimg<real>(image + (size_t)c * plane, o);
-        if (P.automask) xn[c] = ldimg<real>(ctx + (size_t)c * plane, o);
+  for (int k = 0; k < PSFM_MAX_SCALES; ++k)
+    dptr[k] = (const real*)P.sc[S.scale[k < S.ns ? k : 0]].invd + (size_t)b * plane;
+  const int Wp = S.Wp, ns = S.ns;
+  // software pipeline: the loads of row t + 1 are issued before row t is processed
+  // All loads of a row share one scoreboard, and a wait on it waits for everything in flight: the values of
+  // row t must therefore be waited for BEFORE the loads of row t + 1 are issued, or the prefetch is void
+  // (measured: 1.2 long-scoreboard stalls per issued instruction).  `dep` (always 0, unknown to the compiler)
+  // makes the new addresses depend on a value of the previous batch.
+  real yn[3], xn[CT][3], dn[PSFM_MAX_SCALES] = {real(0), real(0), real(0), real(0)}, idn = real_inf<real>();
+  const int never = H >> 31;
+  auto load_row = [&](int t, int dep) {
+    const int o = reflect1(t, H) * W + su + dep;
+    if (AUTOMASK && !FIRST) idn = rb[min(max(t - 1, 0), H - 1) * W + su + dep].w;
+    yn[0] = ldimg<real>(y0p, o); yn[1] = ldimg<real>(y1p, o); yn[2] = ldimg<real>(y2p, o);
+#pragma unroll
+    for (int jj = 0; jj < CT; ++jj) {
+      xn[jj][0] = ldimg<real>(xp0[jj], o); xn[jj][1] = ldimg<real>(xp0[jj] + plane, o);
+      xn[jj][2] = ldimg<real>(xp0[jj] + 2 * plane, o);
+    }
+    if (smooth) {
+#pragma unroll
+      for (int k = 0; k < PSFM_MAX_SCALES; ++k)
+        if (k < ns) dn[k] = __ldg(dptr[k] + o);
+    }
+  };
+  load_row(r0 - 1, 0);
+  // two steps per trip: the 2-row rings are indexed by the step's parity, so nothing is rotated
+  auto step = [&](const int t, auto phc) {
+    constexpr int PH = decltype(phc)::value;      // slot of row t - 2 (overwritten by row t), 1 - PH: row t - 1
+    const int p = t - 1;
+    const bool row_ok = (p >= r0) && (p < r1);
+    const bool emit = inner && row_ok;
+    const int op = p * W + u;
+    const pr yA(yn[0], yn[1]);
+    const real yB = yn[2];
+    pr xA[CT];
+    real xB[CT], dcur[PSFM_MAX_SCALES];
+#pragma unroll
+    for (int jj = 0; jj < CT; ++jj) { xA[jj] = pr(xn[jj][0], xn[jj][1]); xB[jj] = xn[jj][2]; }
+#pragma unroll
+    for (int k = 0; k < PSFM_MAX_SCALES; ++k) dcur[k] = dn[k];
+    real idv = (AUTOMASK && !FIRST) ? idn : real_inf<real>(), idk = real(0);
+    load_row(t + 1, value_bits(yn[0]) & never);
+    // horizontal sums of row t
+    const pr yaA = shfl_up1(yA), ycA = shfl_dn1(yA);
+    const real yaB = shfl_up1(yB), ycB = shfl_dn1(yB);
+    const pr hynA0 = (yaA + yA) + ycA, hynA1 = vfma(ycA, ycA, vfma(yA, yA, yaA * yaA));
+    const real hynB0 = (yaB + yB) + ycB, hynB1 = vfma(ycB, ycB, vfma(yB, yB, yaB * yaB));
+    pr hxnA[CT][3];
+    real hxnB[CT][3];
+    if (AUTOMASK) {
+#pragma unroll
+      for (int jj = 0; jj < CT; ++jj) {
+        const pr zA = xA[jj] * yA;
+        const real zB = xB[jj] * yB;
+        const pr xaA = shfl_up1(xA[jj]), xcA = shfl_dn1(xA[jj]), zaA = shfl_up1(zA), zcA = shfl_dn1(zA);
+        const real xaB = shfl_up1(xB[jj]), xcB = shfl_dn1(xB[jj]), zaB = shfl_up1(zB), zcB = shfl_dn1(zB);
+        hxnA[jj][0] = (xaA + xA[jj]) + xcA;
+        hxnA[jj][1] = vfma(xcA, xcA, vfma(xA[jj], xA[jj], xaA * xaA));
+        hxnA[jj][2] = (zaA + zA) + zcA;
+        hxnB[jj][0] = (xaB + xB[jj]) + xcB;
+        hxnB[jj][1] = vfma(xcB, xcB, vfma(xB[jj], xB[jj], xaB * xaB));
+        hxnB[jj][2] = (zaB + zB) + zcB;
       }
-      if (j == 0 && smooth) {
+    }
+    real wx = real(0), wy = real(0);
+    if (row_ok) {
+      // window statistics of the target at row p (reference :15-54): mean, variance + C2
+      const pr myA = ((hyA[PH][0] + hyA[1 - PH][0]) + hynA0) * pr(r9);
+      const real myB = ((hyB[PH][0] + hyB[1 - PH][0]) + hynB0) * r9;
+      const pr qyA = vfma((hyA[PH][1] + hyA[1 - PH][1]) + hynA1, pr(r9), pr(C2)) - myA * myA;
+      const real qyB = vfma((hyB[PH][1] + hyB[1 - PH][1]) + hynB1, r9, C2) - myB * myB;
+      if (AUTOMASK) {
+        bool changed = false;
 #pragma unroll
-        for (int k = 0; k < PSFM_MAX_SCALES; ++k)
-          if (k < S.ns) dn[k] = __ldg((const real*)P.sc[S.scale[k]].invd + (size_t)b * plane + o);
-      }
-    };
-    load_row(r0 - 1);
-    for (int t = r0 - 1; t <= r1; ++t) {
-      const int p = t - 1;
-      const bool emit = inner && p >= r0 && p < r1;
-      const int op = p * W + u;
-      real y[3], ya[3], yc[3], hyn[6], x[3], dcur[PSFM_MAX_SCALES];
-#pragma unroll
-      for (int c = 0; c < 3; ++c) { y[c] = yn[c]; x[c] = xn[c]; }
-#pragma unroll
-      for (int k = 0; k < PSFM_MAX_SCALES; ++k) dcur[k] = dn[k];
-      real idprev = real(0);
-      if (j > 0 && emit) idprev = rb[op].w;
-      load_row(t + 1);
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        ya[c] = shfl_up1(y[c]);
-        yc[c] = shfl_dn1(y[c]);
-        hyn[c] = ya[c] + y[c] + yc[c];
-        hyn[3 + c] = ya[c] * ya[c] + y[c] * y[c] + yc[c] * yc[c];
-      }
-      real hxn[9];
-      if (P.automask) {
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          const real z = x[c] * y[c];
-          const real xa = shfl_up1(x[c]), xc = shfl_dn1(x[c]);
-          const real za = shfl_up1(z), zc = shfl_dn1(z);
-          hxn[c * 3 + 0] = xa + x[c] + xc;
-          hxn[c * 3 + 1] = xa * xa + x[c] * x[c] + xc * xc;
-          hxn[c * 3 + 2] = za + z + zc;
+        for (int jj = 0; jj < CT; ++jj) {
+          SsimSt<pr> stA;
+          SsimSt<real> stB;
+          const pr dA = ssim_fwd_v<real, pr>((hxA[jj][PH][0] + hxA[jj][1 - PH][0]) + hxnA[jj][0],
+                                             (hxA[jj][PH][1] + hxA[jj][1 - PH][1]) + hxnA[jj][1],
+                                             (hxA[jj][PH][2] + hxA[jj][1 - PH][2]) + hxnA[jj][2], myA, qyA, C1, C2, stA);
+          const real dB = ssim_fwd_v<real, real>((hxB[jj][PH][0] + hxB[jj][1 - PH][0]) + hxnB[jj][0],
+                                                 (hxB[jj][PH][1] + hxB[jj][1 - PH][1]) + hxnB[jj][1],
+                                                 (hxB[jj][PH][2] + hxB[jj][1 - PH][2]) + hxnB[jj][2], myB, qyB, C1, C2, stB);
+          const real ds = vclamp01_sum(dA) + vclamp01_sum(dB);
+          const pr lA = xpA[jj] - ypA;
+          const real ls = (rabs(lA.lo()) + rabs(lA.hi())) + rabs(xpB[jj] - ypB);
+          const real val = kd * ds + kl * ls;
+          // candidate order [.., id_j, ..]: the first minimum wins (reference :269-297, torch.min)
+          if ((first && jj == 0) || val < idv) { idv = val; idk = (real)(2 * (j0 + jj) + 1); changed = true; }
         }
+        if (!first && changed && emit) { rb[op].w = idv; rc[op].w = idk; }
       }
-      real wx = real(0), wy = real(0);
       if (emit) {
-        real my[3], qy[3];
 #pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          my[c] = (hy[0][c] + hy[1][c] + hyn[c]) * r9;
-          qy[c] = ((hy[0][3 + c] + hy[1][3 + c] + hyn[3 + c]) * r9 - my[c] * my[c]) + C2;
+        for (int jj = 0; jj < CT; ++jj) st4(cpk[jj] + p * Wp + u, xpA[jj].lo(), xpA[jj].hi(), xpB[jj], real(0));
+        if (first) {
+          st4(ra + op, ypA.lo(), ypA.hi(), ypB, maskp ? ldimg<real>(maskp, op) : real(1));
+          st4(rb + op, myA.lo(), myA.hi(), myB, idv);
+          st4(rc + op, qyA.lo(), qyA.hi(), qyB, idk);
         }
-        real idv = real_inf<real>(), idk = real(0);
-        if (P.automask) {
-          real ds = real(0), ls = real(0);
-#pragma unroll
-          for (int c = 0; c < 3; ++c) {
-            ds += ssim_dist_sums<real, false>(hx[0][c * 3] + hx[1][c * 3] + hxn[c * 3],
-                                              hx[0][c * 3 + 1] + hx[1][c * 3 + 1] + hxn[c * 3 + 1],
-                                              hx[0][c * 3 + 2] + hx[1][c * 3 + 2] + hxn[c * 3 + 2], my[c], qy[c], C1,
-                                              C2, nullptr);
-            ls += rabs(xp[c] - yp[c]);
-          }
-          const real val = ssim_w * (ds * r3) + (real(1) - ssim_w) * (ls * r3);
-          if (j == 0) { idv = val; idk = real(1); }
-          else if (val < idprev) { rb[op].w = val; rc[op].w = (real)(2 * j + 1); }
-        }
-        if (j == 0) {
-          st4(ra + op, yp[0], yp[1], yp[2], maskp ? ldimg<real>(maskp, op) : real(1));
-          st4(rb + op, my[0], my[1], my[2], idv);
-          st4(rc + op, qy[0], qy[1], qy[2], idk);
-        }
-        if (j == 0 && smooth) {
-          if (u + 1 < W) wx = rexp(-((rabs(yp[0] - ycp[0]) + rabs(yp[1] - ycp[1]) + rabs(yp[2] - ycp[2])) * r3));
-          if (p + 1 < H) wy = rexp(-((rabs(yp[0] - y[0]) + rabs(yp[1] - y[1]) + rabs(yp[2] - y[2])) * r3));
+        if (smooth) {
+          const pr ex = ypA - ycpA, ey = ypA - yA;
+          if (u + 1 < W) wx = rexp(-(((rabs(ex.lo()) + rabs(ex.hi())) + rabs(ypB - ycpB)) * r3));
+          if (p + 1 < H) wy = rexp(-(((rabs(ey.lo()) + rabs(ey.hi())) + rabs(ypB - yB)) * r3));
           wxy[(size_t)op * 2] = wx;
           wxy[(size_t)op * 2 + 1] = wy;
         }
       }
-      if (j == 0 && smooth) {
-        // raw smoothness sums of row p for every scale of the set (all lanes take part in the
-        // right-neighbour shuffle)
+    }
+    if (smooth) {
+      // raw smoothness sums of row p for every scale of the set (all lanes take part in the
+      // right-neighbour shuffle)
 #pragma unroll
-        for (int k = 0; k < PSFM_MAX_SCALES; ++k) {
-          if (k < S.ns) {
-            const real dt = dcur[k];
-            const real dr = shfl_dn1(dp[k]);
-            if (emit) {
-              sums[k][0] += dp[k];
-              if (u + 1 < W) sums[k][1] += rabs(dp[k] - dr) * wx;
-              if (p + 1 < H) sums[k][2] += rabs(dp[k] - dt) * wy;
-            }
-            dp[k] = dt;
+      for (int k = 0; k < PSFM_MAX_SCALES; ++k) {
+        if (k < ns) {
+          const real dt = dcur[k];
+          const real dr = shfl_dn1(dp[k]);
+          if (emit) {
+            sums[k][0] += dp[k];
+            if (u + 1 < W) sums[k][1] += rabs(dp[k] - dr) * wx;
+            if (p + 1 < H) sums[k][2] += rabs(dp[k] - dt) * wy;
           }
+          dp[k] = dt;
         }
       }
-      // rotate the rings
-#pragma unroll
-      for (int k = 0; k < 6; ++k) { hy[0][k] = hy[1][k]; hy[1][k] = hyn[k]; }
-      if (P.automask) {
-#pragma unroll
-        for (int k = 0; k < 9; ++k) { hx[0][k] = hx[1][k]; hx[1][k] = hxn[k]; }
-      }
-#pragma unroll
-      for (int c = 0; c < 3; ++c) { yp[c] = y[c]; ycp[c] = yc[c]; xp[c] = x[c]; }
     }
+    // row t replaces row t - 2 in the rings
+    hyA[PH][0] = hynA0; hyA[PH][1] = hynA1; hyB[PH][0] = hynB0; hyB[PH][1] = hynB1;
+    if (AUTOMASK) {
+#pragma unroll
+      for (int jj = 0; jj < CT; ++jj)
+#pragma unroll
+        for (int m = 0; m < 3; ++m) { hxA[jj][PH][m] = hxnA[jj][m]; hxB[jj][PH][m] = hxnB[jj][m]; }
+    }
+    ypA = yA; ypB = yB; ycpA = ycA; ycpB = ycB;
+#pragma unroll
+    for (int jj = 0; jj < CT; ++jj) { xpA[jj] = xA[jj]; xpB[jj] = xB[jj]; }
+  };
+  for (int t = r0 - 1; t <= r1; t += 2) {
+    step(t, IntC<0>());
+    step(t + 1, IntC<1>());
   }
   if (smooth) {
 #pragma unroll
@@ -348,7 +401,6 @@ __device__ __forceinline__ void sweep_cam(SweepCam<real>& c, const LossParams& P
   for (int i = 0; i < 12; ++i) c.T[i] = T[i];
 }
 
-template <int V> struct IntC { static constexpr int value = V; };
 
 template <typename real> __device__ __forceinline__ const SweepConsts<real>& sweep_consts(const SweepParams& SP);
 template <> __device__ __forceinline__ const SweepConsts<float>& sweep_consts<float>(const SweepParams& SP) { return SP.cf; }
@@ -996,9 +1048,21 @@ static cudaError_t run_sweep(const psfm_loss_cfg* cfg, const psfm_loss_io* io, v
     fill_consts(SP.cd, SP.P, s0);
     const SweepSet& S = SP.set;
     {
-      ProfScope ps(st, kTagFwd, cfg->smooth_w > 0.0 ? 3 : 2);
-      pack_kernel<real, img_t><<<dim3(cdiv(S.Hp * S.Wp, 256), cfg->C, cfg->B), 256, 0, st>>>(SP);
-      prep_kernel<real, img_t><<<dim3(cdiv(S.pstrips * S.pchunks, kPrepWarps), cfg->B), 32 * kPrepWarps, 0, st>>>(SP);
+      int npass = 0;
+      for (int j0 = 0; j0 < cfg->C; j0 += (cfg->C - j0 >= 4 ? 4 : (cfg->C - j0 >= 2 ? 2 : 1))) ++npass;
+      ProfScope ps(st, kTagFwd, 1 + npass + (cfg->smooth_w > 0.0 ? 1 : 0));
+      border_kernel<real><<<dim3(S.Hp, cfg->C, cfg->B), 128, 0, st>>>(SP);
+      const dim3 pgrid(cdiv(S.pstrips * S.pchunks, kPrepWarps), cfg->B);
+      for (int j0 = 0; j0 < cfg->C;) {
+        const int ct = cfg->C - j0 >= 4 ? 4 : (cfg->C - j0 >= 2 ? 2 : 1);
+#define PSFM_PREP(CTV, AM, FI) prep_kernel<real, img_t, CTV, AM, FI><<<pgrid, 32 * kPrepWarps, 0, st>>>(SP, j0)
+#define PSFM_PREP_CT(AM, FI) (ct == 4 ? PSFM_PREP(4, AM, FI) : ct == 2 ? PSFM_PREP(2, AM, FI) : PSFM_PREP(1, AM, FI))
+        if (cfg->automask) { if (j0 == 0) PSFM_PREP_CT(true, true); else PSFM_PREP_CT(true, false); }
+        else { if (j0 == 0) PSFM_PREP_CT(false, true); else PSFM_PREP_CT(false, false); }
+#undef PSFM_PREP_CT
+#undef PSFM_PREP
+        j0 += ct;
+      }
       if (cfg->smooth_w > 0.0) stats_kernel<real><<<dim3(cfg->B, S.ns), 128, 0, st>>>(SP);
     }
     const int ring = cfg->padding == PSFM_PAD_BORDER ? 11 : 10;
