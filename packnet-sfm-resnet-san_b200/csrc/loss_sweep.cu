@@ -886,18 +886,6 @@ static int env_int(const char* name, int dflt) {
   return (v && *v) ? atoi(v) : dflt;
 }
 
-// rows per unit: the largest chunk that still yields `want` warps (each chunk pays `extra` warm-up rows)
-static int pick_chunk(int H, long warps_per_chunk_row, long want) {
-  static const int cand[] = {1 << 30, 256, 192, 128, 96, 64, 48, 32, 24, kMinChunk};
-  int best = kMinChunk;
-  for (int c : cand) {
-    const int ch = c < H ? c : H;
-    best = ch;
-    if ((long)cdiv(H, ch) * warps_per_chunk_row >= want) break;
-  }
-  return best < kMinChunk ? (H < kMinChunk ? H : kMinChunk) : best;
-}
-
 // Rows per sweep unit.  A unit of h rows runs h + 4 steps (2 warm-up rows of the window, 2 of the adjoint),
 // rounded up to the 3-step unrolling; the grid runs in waves of (148 SMs x resident CTAs).  Pick the
 // height that minimises waves x steps (measured at config 2: 48 and 64 rows 242 us, 32 rows 259 us,
@@ -913,6 +901,24 @@ static int pick_sweep_chunk(int H, long ctas_per_chunk, int C, bool f64) {
     const long chunks = cdiv(H, ch);
     const long waves = (chunks * ctas_per_chunk + resident - 1) / resident;
     const double cost = (double)waves * (double)((ch + 4 + 2) / 3 * 3);
+    if (cost < best_cost * 0.999) { best_cost = cost; best = ch; }
+    if (c >= H) break;
+  }
+  return best;
+}
+
+// Rows per prep unit (one warp): h rows run h + 2 steps, rounded up to the 2-step unrolling; 148 SMs x 2 CTAs x
+// 4 warps are resident.  Measured at config 2: 32 rows 63 us, 16 rows 68 us, 24 / 48 rows 78-79 us.
+static int pick_prep_chunk(int H, long warps_per_chunk) {
+  static const int cand[] = {16, 24, 32, 48, 64, 96, 128, 192, 256, 384, 512, 1 << 30};
+  const long resident = 148L * 2 * kPrepWarps;
+  int best = H;
+  double best_cost = 1e300;
+  for (int c : cand) {
+    const int ch = c < H ? c : H;
+    if (ch < kMinChunk && ch < H) continue;
+    const long waves = ((long)cdiv(H, ch) * warps_per_chunk + resident - 1) / resident;
+    const double cost = (double)waves * (double)((ch + 2 + 1) / 2 * 2);
     if (cost < best_cost * 0.999) { best_cost = cost; best = ch; }
     if (c >= H) break;
   }
@@ -945,7 +951,7 @@ static void make_plan(const psfm_loss_cfg* cfg, const psfm_loss_io* io, SweepPla
     S.nchunks = cdiv(S.H, S.chunk_h);
     S.pstrips = cdiv(S.W, kPrepInner);
     const int pforced = env_int("PSFM_PREP_CHUNK", 0);
-    S.pchunk_h = pforced > 0 ? (pforced < S.H ? pforced : S.H) : pick_chunk(S.H, (long)S.pstrips * cfg->B, 148L * 16);
+    S.pchunk_h = pforced > 0 ? (pforced < S.H ? pforced : S.H) : pick_prep_chunk(S.H, (long)S.pstrips * cfg->B);
     if (S.pchunk_h < kMinChunk) S.pchunk_h = S.H < kMinChunk ? S.H : kMinChunk;
     S.pchunks = cdiv(S.H, S.pchunk_h);
   }
