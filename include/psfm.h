@@ -176,6 +176,12 @@ int psfm_transform_points(int B, size_t N, int dt, const void* mat, const void* 
 int psfm_transform_points_backward(int B, size_t N, int dt, const void* mat, const void* X, const void* grad_out,
                                    void* dX, void* d_mat, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Pose.from_vec -> pose_vec2mat -> euler2mat (geometry/pose.py:39-46, geometry/pose_utils.py:8-51):
+ * vec[B,6] = [tx, ty, tz, rx, ry, rz] -> mat[B,4,4] = [Rx(rx) Ry(ry) Rz(rz) | t; 0 0 0 1].
+ * Backward: d_vec[B,6] from grad_mat[B,4,4] (rows 0-2 are read). */
+int psfm_pose_from_vec(int B, int dt, const void* vec, void* mat, void* stream);
+int psfm_pose_from_vec_backward(int B, int dt, const void* vec, const void* grad_mat, void* d_vec, void* stream);
+
 /* SSIM / calc_photometric_loss (losses/multiview_photometric_loss.py:15-54,199-267) of x, y [B,3,H,W]:
  *   mode 0 SSIM index [B,3,H,W]; mode 1 clamp((1-SSIM)/2,0,1) [B,3,H,W];
  *   mode 2 ssim_w * mean_c(mode 1) + (1-ssim_w) * mean_c|x-y| [B,1,H,W]; mode 3 |x-y| [B,3,H,W].

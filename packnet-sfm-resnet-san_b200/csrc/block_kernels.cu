@@ -480,6 +480,61 @@ __global__ void __launch_bounds__(kBT) abs_mean_bwd_kernel(size_t n, real scale,
   if (i < n) dx[i] = rsign(x[i]) * gout[0] * scale;
 }
 
+
+// ------------------------------------------------------------------------------------------
+// Pose.from_vec / pose_vec2mat / euler2mat (geometry/pose.py:39-46, geometry/pose_utils.py:8-51):
+// vec = [tx, ty, tz, rx, ry, rz] -> [R | t; 0 0 0 1] with R = Rx(rx) Ry(ry) Rz(rz).  One thread per pose.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void sincos_full(float a, float& s, float& c) { s = sinf(a); c = cosf(a); }
+__device__ __forceinline__ void sincos_full(double a, double& s, double& c) { s = sin(a); c = cos(a); }
+
+template <typename real>
+__device__ __forceinline__ void euler_rot(const real* v, real* R, real* sc) {
+  real sx, cx, sy, cy, sz, cz;
+  sincos_full(v[3], sx, cx); sincos_full(v[4], sy, cy); sincos_full(v[5], sz, cz);
+  R[0] = cy * cz;                R[1] = -cy * sz;               R[2] = sy;
+  R[3] = sx * sy * cz + cx * sz; R[4] = cx * cz - sx * sy * sz; R[5] = -sx * cy;
+  R[6] = sx * sz - cx * sy * cz; R[7] = cx * sy * sz + sx * cz; R[8] = cx * cy;
+  sc[0] = sx; sc[1] = cx; sc[2] = sy; sc[3] = cy; sc[4] = sz; sc[5] = cz;
+}
+
+template <typename real>
+__global__ void pose_vec_kernel(int B, const real* __restrict__ vec, real* __restrict__ mat) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  real R[9], sc[6];
+  euler_rot<real>(vec + (size_t)b * 6, R, sc);
+  real* m = mat + (size_t)b * 16;
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    m[i * 4] = R[i * 3]; m[i * 4 + 1] = R[i * 3 + 1]; m[i * 4 + 2] = R[i * 3 + 2];
+    m[i * 4 + 3] = vec[(size_t)b * 6 + i];
+  }
+  m[12] = real(0); m[13] = real(0); m[14] = real(0); m[15] = real(1);
+}
+
+template <typename real>
+__global__ void pose_vec_bwd_kernel(int B, const real* __restrict__ vec, const real* __restrict__ g,
+                                    real* __restrict__ d_vec) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  real R[9], sc[6], G[9];
+  euler_rot<real>(vec + (size_t)b * 6, R, sc);
+  const real sx = sc[0], cx = sc[1], sy = sc[2], cy = sc[3], sz = sc[4], cz = sc[5];
+  const real* gm = g + (size_t)b * 16;
+#pragma unroll
+  for (int i = 0; i < 3; ++i) { G[i * 3] = gm[i * 4]; G[i * 3 + 1] = gm[i * 4 + 1]; G[i * 3 + 2] = gm[i * 4 + 2]; }
+  real* o = d_vec + (size_t)b * 6;
+  o[0] = gm[3]; o[1] = gm[7]; o[2] = gm[11];
+  // d R / d rx: row 1 -> -row 2, row 2 -> row 1
+  o[3] = (G[6] * R[3] + G[7] * R[4] + G[8] * R[5]) - (G[3] * R[6] + G[4] * R[7] + G[5] * R[8]);
+  // d R / d ry
+  o[4] = G[0] * (-sy * cz) + G[1] * (sy * sz) + G[2] * cy + G[3] * (sx * cy * cz) + G[4] * (-sx * cy * sz) +
+         G[5] * (sx * sy) + G[6] * (-cx * cy * cz) + G[7] * (cx * cy * sz) + G[8] * (-cx * sy);
+  // d R / d rz: column 0 -> column 1, column 1 -> -column 0
+  o[5] = (G[0] * R[1] + G[3] * R[4] + G[6] * R[7]) - (G[1] * R[0] + G[4] * R[3] + G[7] * R[6]);
+}
+
 }  // namespace psfm
 
 // ------------------------------------------------------------------------------------------
@@ -556,6 +611,23 @@ int psfm_project_backward(int B, int H, int W, int dt, const void* X, const void
     if (pose) mat_finish_kernel<real><<<B, 32, 0, (cudaStream_t)stream>>>((const real*)ws, (int)nb, (real*)d_Tcw);
   });
   return launch_result("psfm_project_backward");
+}
+
+int psfm_pose_from_vec(int B, int dt, const void* vec, void* mat, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(B >= 1 && vec && mat, "psfm_pose_from_vec: bad argument");
+  count_launches(1);
+  PSFM_DISPATCH(dt, (pose_vec_kernel<real><<<(B + 63) / 64, 64, 0, (cudaStream_t)stream>>>(B, (const real*)vec, (real*)mat)));
+  return launch_result("psfm_pose_from_vec");
+}
+
+int psfm_pose_from_vec_backward(int B, int dt, const void* vec, const void* grad_mat, void* d_vec, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(B >= 1 && vec && grad_mat && d_vec, "psfm_pose_from_vec_backward: bad argument");
+  count_launches(1);
+  PSFM_DISPATCH(dt, (pose_vec_bwd_kernel<real><<<(B + 63) / 64, 64, 0, (cudaStream_t)stream>>>(
+                        B, (const real*)vec, (const real*)grad_mat, (real*)d_vec)));
+  return launch_result("psfm_pose_from_vec_backward");
 }
 
 int psfm_transform_points(int B, size_t N, int dt, const void* mat, const void* X, void* out, void* stream) {

@@ -138,6 +138,37 @@ class _TransformPoints(torch.autograd.Function):
         return d_mat, dX
 
 
+class _PoseFromVec(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, vec):
+        _C.require_cuda(vec)
+        vec = vec.contiguous()
+        B = vec.shape[0]
+        mat = torch.empty(B, 4, 4, dtype=vec.dtype, device=vec.device)
+        with torch.cuda.device(vec.device):
+            _C.check(_C.lib.psfm_pose_from_vec(B, _real(vec), _C.ptr(vec), _C.ptr(mat), _C.stream_ptr(vec.device)))
+        ctx.save_for_backward(vec)
+        return mat
+
+    @staticmethod
+    def backward(ctx, g):
+        vec, = ctx.saved_tensors
+        g = g.contiguous()
+        d_vec = torch.empty_like(vec)
+        with torch.cuda.device(vec.device):
+            _C.check(_C.lib.psfm_pose_from_vec_backward(vec.shape[0], _real(vec), _C.ptr(vec), _C.ptr(g), _C.ptr(d_vec),
+                                                        _C.stream_ptr(vec.device)))
+        return d_vec
+
+
+def pose_from_vec_op(vec):
+    """Pose.from_vec(vec, 'euler'): [B,6] -> [B,4,4], one kernel each way (no batch-size dependent rounding)."""
+    _real(vec)
+    if vec.dim() != 2 or vec.shape[1] != 6:
+        raise ValueError('pose vectors must be [B,6]')
+    return _PoseFromVec.apply(vec)
+
+
 def transform_points_op(mat, points):
     """Pose.transform_points: R X + t on [B,3,H,W] (or [B,3,N]) points."""
     _real(points)

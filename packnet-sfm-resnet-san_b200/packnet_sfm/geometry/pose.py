@@ -24,6 +24,10 @@ class Pose:
     @classmethod
     def from_vec(cls, vec, mode):
         """[B,6] pose vector -> Pose (reference :39-46)."""
+        if mode == 'euler' and vec.is_cuda and vec.dim() == 2 and vec.shape[1] == 6 and \
+                vec.dtype in (torch.float32, torch.float64):
+            from packnet_sfm.block_ops import pose_from_vec_op
+            return cls(pose_from_vec_op(vec))                                 # one CUDA kernel each way
         top = pose_vec2mat(vec, mode)                                         # [B,3,4]
         mat = torch.eye(4, device=vec.device, dtype=vec.dtype).repeat([len(vec), 1, 1])
         mat[:, :3, :3] = top[:, :3, :3]

@@ -164,3 +164,25 @@ def test_cpu_tensors_are_refused():
     from packnet_sfm import ops
     with pytest.raises(RuntimeError, match='no CPU fallback'):
         ops.ssim_op(torch.rand(1, 3, 8, 8), torch.rand(1, 3, 8, 8))
+
+
+@pytest.mark.parametrize('dtype', [torch.float64, torch.float32])
+def test_pose_from_vec_kernel_matches_oracle(dtype):
+    """Pose.from_vec(vec, 'euler') (geometry/pose.py:39-46, pose_utils.py:8-51) as one kernel each way:
+    matrix and d/d vec against the oracle's torch composition Rx Ry Rz, for batch sizes 1 and 5 (the
+    kernel's rounding does not depend on the batch size, torch's batched matmul does)."""
+    from packnet_sfm.geometry.pose import Pose
+    g = torch.Generator().manual_seed(3)
+    vec = torch.randn(5, 6, generator=g, dtype=torch.float64) * torch.tensor([1., 1., 1., 0.5, 0.5, 0.5], dtype=torch.float64)
+    w = torch.randn(5, 4, 4, generator=g, dtype=torch.float64)
+    v_ref = vec.clone().requires_grad_()
+    m_ref = O.pose_vec_to_mat(v_ref)
+    (m_ref * w).sum().backward()
+    tol = 1e-12 if dtype == torch.float64 else 2e-6
+    v = vec.to(DEV).to(dtype).requires_grad_()
+    pose = Pose.from_vec(v, 'euler')
+    (pose.mat * w.to(DEV).to(dtype)).sum().backward()
+    assert (pose.mat.detach().cpu().double() - m_ref.detach()).abs().max().item() <= tol
+    assert (v.grad.cpu().double() - v_ref.grad).abs().max().item() <= 10 * tol
+    one = Pose.from_vec(vec[2:3].to(DEV).to(dtype), 'euler').mat
+    assert torch.equal(one[0], pose.mat.detach()[2])
