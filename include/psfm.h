@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define PSFM_ABI_VERSION 1
+#define PSFM_ABI_VERSION 2
 #define PSFM_MAX_SCALES 4
 #define PSFM_MAX_CTX 8
 
@@ -55,6 +55,11 @@ typedef struct psfm_loss_cfg {
   int32_t H, W;                   /* size of the full-resolution image (K/ref_K refer to it)  */
   int32_t Hs[PSFM_MAX_SCALES];    /* inv_depths[i].shape[2]                                   */
   int32_t Ws[PSFM_MAX_SCALES];    /* inv_depths[i].shape[3]                                   */
+  int32_t Hd[PSFM_MAX_SCALES];    /* 0, or: the decoder's native map is [B,1,Hd,Wd] and is     */
+  int32_t Wd[PSFM_MAX_SCALES];    /* nearest-upsampled to (Hs,Ws) INSIDE the kernels (what     */
+                                  /* SfmModel.compute_depth_net -> upsample_output does before */
+                                  /* the loss, models/SfmModel.py:86-88, model_utils.py:152-176);*/
+                                  /* inv_depth[i] / d_inv_depth[i] are then [B,1,Hd,Wd]        */
   int32_t img_dtype;              /* psfm_dtype of images / mask                              */
   int32_t real_dtype;             /* PSFM_F32 or PSFM_F64                                     */
   int32_t padding;                /* psfm_padding  (padding_mode)                             */

@@ -491,6 +491,9 @@ void build_params(const psfm_loss_cfg* cfg, const psfm_loss_io* io, void* ws, Lo
     S.d_invd = io->d_inv_depth[s];
     for (int j = 0; j < cfg->C; ++j) S.ctx[j] = io->ctx[s][j];
     S.H = cfg->Hs[s]; S.W = cfg->Ws[s];
+    S.Hd = cfg->Hd[s] > 0 ? cfg->Hd[s] : S.H; S.Wd = cfg->Wd[s] > 0 ? cfg->Wd[s] : S.W;
+    S.rs = (float)S.Hd / (float)S.H; S.cs = (float)S.Wd / (float)S.W;
+    S.d_full = S.d_invd;
     S.sf = (double)S.W / (double)cfg->W;
     const double px = (double)cfg->B * S.H * S.W;
     S.inv_count = 1.0 / ((double)cfg->n * px);

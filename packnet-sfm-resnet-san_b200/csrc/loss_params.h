@@ -19,6 +19,9 @@ struct ScaleDesc {
   uint8_t* sel;                      // [B,H,W]
   void* d_invd;                      // [B,1,H,W] real
   int H, W;
+  int Hd, Wd;                        // size of the inverse-depth map in memory (== H, W unless upsampled in-kernel)
+  float rs, cs;                      // Hd / H, Wd / W: nearest source index = min(floor(dst * scale), size - 1)
+  void* d_full;                      // where the kernels write d/d inv_depth at (H, W): d_invd, or a workspace buffer
   int tiles_x, tiles_y;
   double sf;                         // W_s / W (python float division, utils: warp_ref_image)
   double inv_count;                  // 1 / (n * B * H * W): weight of one pixel in the photometric mean

@@ -117,6 +117,11 @@ __global__ void __launch_bounds__(128) border_kernel(const SweepParams SP) {
 // identity-reprojection term); the pass with j0 == 0 also emits the image-only outputs.
 // Per-channel arithmetic runs on (channel 0, channel 1) pairs + a scalar channel 2 (pair_math.cuh).
 // ------------------------------------------------------------------------------------------
+// F.interpolate(mode='nearest') source index (utils/image.py:148-176 via models/model_utils.py:152-176)
+__device__ __forceinline__ int nearest_src(int dst, float scale, int size, bool active) {
+  return active ? min((int)floorf((float)dst * scale), size - 1) : dst;
+}
+
 __device__ __forceinline__ int value_bits(float v) { return __float_as_int(v); }
 __device__ __forceinline__ int value_bits(double v) { return __double2hiint(v); }
 
@@ -181,10 +186,17 @@ __global__ void __launch_bounds__(32 * kPrepWarps) prep_kernel(const SweepParams
 #pragma unroll
   for (int k = 0; k < PSFM_MAX_SCALES; ++k) dp[k] = real(0);
 
+  // inverse-depth maps: at (H, W), or smaller and nearest-upsampled here (ScaleDesc::Hd, Wd)
   const real* dptr[PSFM_MAX_SCALES];
+  int dcol[PSFM_MAX_SCALES];
+  bool any_ups = false;
 #pragma unroll
-  for (int k = 0; k < PSFM_MAX_SCALES; ++k)
-    dptr[k] = (const real*)P.sc[S.scale[k < S.ns ? k : 0]].invd + (size_t)b * plane;
+  for (int k = 0; k < PSFM_MAX_SCALES; ++k) {
+    const ScaleDesc& Sk = P.sc[S.scale[k < S.ns ? k : 0]];
+    dptr[k] = (const real*)Sk.invd + (size_t)b * Sk.Hd * Sk.Wd;
+    dcol[k] = nearest_src(su, Sk.cs, Sk.Wd, Sk.Wd != W);
+    any_ups = any_ups || Sk.Hd != H || Sk.Wd != W;
+  }
   const int Wp = S.Wp, ns = S.ns;
   // software pipeline: the loads of row t + 1 are issued before row t is processed
   // All loads of a row share one scoreboard, and a wait on it waits for everything in flight: the values of
@@ -205,7 +217,14 @@ __global__ void __launch_bounds__(32 * kPrepWarps) prep_kernel(const SweepParams
     if (smooth) {
 #pragma unroll
       for (int k = 0; k < PSFM_MAX_SCALES; ++k)
-        if (k < ns) dn[k] = __ldg(dptr[k] + o);
+        if (k < ns) {
+          int ok = o;
+          if (any_ups) {
+            const ScaleDesc& Sk = P.sc[S.scale[k]];
+            ok = nearest_src(reflect1(t, H), Sk.rs, Sk.Hd, Sk.Hd != H) * Sk.Wd + dcol[k] + dep;
+          }
+          dn[k] = __ldg(dptr[k] + ok);
+        }
     }
   };
   load_row(r0 - 1, 0);
@@ -460,7 +479,10 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
   const vec4* rb = (const vec4*)S.rb + (size_t)b * plane;
   const vec4* rcp = (const vec4*)S.rc + (size_t)b * plane;
   asm volatile("" : "+l"(ctxp), "+l"(ra), "+l"(rb), "+l"(rcp));   // opaque: one IMAD.WIDE per load off a 32-bit offset
-  const real* invd = (const real*)SD.invd + (size_t)b * plane;
+  const bool ups = RARE && (SD.Hd != H || SD.Wd != W);          // inverse depths nearest-upsampled on load
+  const real* invd = (const real*)SD.invd + (size_t)b * SD.Hd * SD.Wd;
+  const int Wd = SD.Wd, sud = nearest_src(su, SD.cs, SD.Wd, ups);
+  auto dofs = [&](int row) { return nearest_src(reflect1(row, H), SD.rs, SD.Hd, ups) * Wd + sud; };
   const real* wxy = (const real*)S.wxy + (size_t)b * plane * 2;
   const int Wp = S.Wp;
   const bool premap = RARE && P.premap;
@@ -516,7 +538,7 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
   real wy_prev = real(0);                                          // edge weight wy of row q - 1
   real dsum_prev = real(0);
   int prev_q = -1;
-  real* d_out = (real*)SD.d_invd + (size_t)b * plane;
+  real* d_out = (real*)SD.d_full + (size_t)b * plane;
 
   // gather pipeline: geometry of `row`, the 4 tap loads go in flight, consumed one step later
   vec4 tap[4];
@@ -568,8 +590,8 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
   real mcur = real(1);                                             // mask value of row t - 1
   real wxn = real(0), wyn = real(0);                               // edge weights of row q + 1 (context 0 only)
   if (j == 0 && smooth) load_pair(wxy + (min(max(r0 - 4, 0), H - 1) * W + su) * 2, wxn, wyn);
-  real dnx = __ldg(invd + reflect1(r0 - 2, H) * W + su);
-  real dpre = __ldg(invd + reflect1(r0 - 1, H) * W + su);
+  real dnx = __ldg(invd + dofs(r0 - 2));
+  real dpre = __ldg(invd + dofs(r0 - 1));
   {
     ran = ld4(ra + reflect1(r0 - 2, H) * W + su);
     const int orec = min(max(r0 - 3, 0), H - 1) * W + su;
@@ -610,7 +632,7 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
     }
     // ---------------- prefetch of the next steps' operands, gather of row t + 1 ----------------------------
     {
-      dpre = __ldg(invd + reflect1(t + 2, H) * W + su);
+      dpre = __ldg(invd + dofs(t + 2));
       ran = ld4(ra + reflect1(t + 1, H) * W + su);
       const int orec = min(max(p + 1, 0), H - 1) * W + su;
       rbn = ld4(rb + orec);
@@ -784,6 +806,28 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
 }
 
 // ------------------------------------------------------------------------------------------
+// pool kernel: adjoint of the in-kernel nearest upsampling.  grid (ceil(Hd Wd / 256), B), 256 threads; one
+// thread sums, in a fixed order, the full-resolution gradients of the pixels that read its map element.
+// ------------------------------------------------------------------------------------------
+template <typename real>
+__global__ void __launch_bounds__(256) pool_kernel(int H, int W, int Hd, int Wd, float rs, float cs,
+                                                   const real* __restrict__ full, real* __restrict__ out) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= Hd * Wd) return;
+  const int vs = i / Wd, us = i - vs * Wd, b = blockIdx.y;
+  const int v0 = max(0, (int)((float)vs / rs) - 1), v1 = min(H - 1, (int)((float)(vs + 1) / rs) + 1);
+  const int u0 = max(0, (int)((float)us / cs) - 1), u1 = min(W - 1, (int)((float)(us + 1) / cs) + 1);
+  const real* src = full + (size_t)b * H * W;
+  real acc = real(0);
+  for (int v = v0; v <= v1; ++v) {
+    if (nearest_src(v, rs, Hd, true) != vs) continue;
+    for (int u = u0; u <= u1; ++u)
+      if (nearest_src(u, cs, Wd, true) == us) acc += src[(size_t)v * W + u];
+  }
+  out[(size_t)b * Hd * Wd + i] = acc;
+}
+
+// ------------------------------------------------------------------------------------------
 // final kernel: block 0 -> loss triple; block 1 + b * C + j -> d pose[j].mat[b].
 // Works over all sets (called once, after every set's sweep kernel).
 // ------------------------------------------------------------------------------------------
@@ -874,7 +918,7 @@ bool stream_eligible(const psfm_loss_cfg* cfg) {
 struct SweepPlan {
   int nsets;
   SweepSet sets[PSFM_MAX_SCALES];
-  size_t off_rec[PSFM_MAX_SCALES], off_wxy[PSFM_MAX_SCALES], off_ctxp[PSFM_MAX_SCALES];                                         // per scale (a set uses its first scale's)
+  size_t off_rec[PSFM_MAX_SCALES], off_wxy[PSFM_MAX_SCALES], off_ctxp[PSFM_MAX_SCALES], off_dfull[PSFM_MAX_SCALES];                                         // per scale (a set uses its first scale's)
   size_t off_prep[PSFM_MAX_SCALES], off_stats[PSFM_MAX_SCALES], off_loss[PSFM_MAX_SCALES],
       off_pose[PSFM_MAX_SCALES];                                          // per scale
   int nunits[PSFM_MAX_SCALES];
@@ -967,6 +1011,8 @@ static void make_plan(const psfm_loss_cfg* cfg, const psfm_loss_io* io, SweepPla
     pl.off_rec[s] = off;   off = al(off + px * 12 * rs);               // three real4 planes
     pl.off_ctxp[s] = off;  off = al(off + (size_t)cfg->C * cfg->B * (Hs + kPadLo + kPadHi) * (Ws + kPadLo + kPadHi) * 4 * rs);
     pl.off_wxy[s] = off;   off = al(off + px * 2 * rs);
+    const bool ups = cfg->Hd[s] > 0 && (cfg->Hd[s] != Hs || cfg->Wd[s] != Ws);
+    pl.off_dfull[s] = off; if (ups) off = al(off + px * rs);            // full-resolution d inv_depth before pooling
     pl.off_prep[s] = off;  off = al(off + (size_t)cfg->B * pworst * kPrepVals * sizeof(double));
     pl.off_stats[s] = off; off = al(off + (size_t)cfg->B * 4 * rs);
     pl.off_loss[s] = off;  off = al(off + (size_t)cfg->B * worst * sizeof(double));
@@ -1037,7 +1083,13 @@ static cudaError_t run_sweep(const psfm_loss_cfg* cfg, const psfm_loss_io* io, v
     SP.loss_part[s] = (double*)(w + pl.off_loss[s]);
     SP.pose_part[s] = w + pl.off_pose[s];
   }
-  const bool rare = cfg->premap != 0;     // masks travel in the pixel records and cost nothing extra
+  bool rare = cfg->premap != 0;           // masks travel in the pixel records and cost nothing extra
+  for (int s = 0; s < cfg->n; ++s) {
+    if (SP.P.sc[s].Hd != SP.P.sc[s].H || SP.P.sc[s].Wd != SP.P.sc[s].W) {
+      SP.P.sc[s].d_full = (char*)ws_stream + pl.off_dfull[s];
+      rare = true;
+    }
+  }
   for (int i = 0; i < pl.nsets; ++i) {
     SP.set = pl.sets[i];
     const int s0 = SP.set.scale[0];
@@ -1084,6 +1136,13 @@ static cudaError_t run_sweep(const psfm_loss_cfg* cfg, const psfm_loss_io* io, v
       e = rare ? launch_sweep<real, PSFM_PAD_ZEROS, true>(SP, grid, threads, smem, st)
                : launch_sweep<real, PSFM_PAD_ZEROS, false>(SP, grid, threads, smem, st);
     if (e != cudaSuccess) return e;
+  }
+  for (int s = 0; s < cfg->n; ++s) {
+    const ScaleDesc& D = SP.P.sc[s];
+    if (D.d_full == D.d_invd) continue;
+    ProfScope ps(st, kTagFinish, 1);
+    pool_kernel<real><<<dim3(cdiv(D.Hd * D.Wd, 256), cfg->B), 256, 0, st>>>(D.H, D.W, D.Hd, D.Wd, D.rs, D.cs,
+                                                                          (const real*)D.d_full, (real*)D.d_invd);
   }
   FinalParams F;
   F.B = cfg->B; F.C = cfg->C; F.n = cfg->n; F.smooth = cfg->smooth_w > 0.0;

@@ -91,6 +91,16 @@ static int check_cfg(const psfm_loss_cfg* c) {
     return psfm_fail(PSFM_ERR_INVALID, "Unknown photometric_reduce_op: %d", c->reduce_op);
   if (c->automask && c->reduce_op != PSFM_REDUCE_MIN)
     return psfm_fail(PSFM_ERR_INVALID, "For automasking only the min photometric_reduce_op is supported.");
+  for (int s = 0; s < c->n; ++s) {
+    const bool ups = (c->Hd[s] > 0 || c->Wd[s] > 0) && (c->Hd[s] != c->Hs[s] || c->Wd[s] != c->Ws[s]);
+    if (!ups) continue;
+    if (c->Hd[s] < 1 || c->Wd[s] < 1 || c->Hd[s] > c->Hs[s] || c->Wd[s] > c->Ws[s])
+      return psfm_fail(PSFM_ERR_INVALID, "scale %d: in-kernel upsampling needs 1 <= Hd <= Hs and 1 <= Wd <= Ws (got %dx%d -> %dx%d)", s,
+                       c->Hd[s], c->Wd[s], c->Hs[s], c->Ws[s]);
+    if (c->reduce_op != PSFM_REDUCE_MIN || !(c->ssim_w > 0.0) || c->clip_loss > 0.0 || c->C > 8 || c->Hs[s] < 4 || c->Ws[s] < 4)
+      return psfm_fail(PSFM_ERR_INVALID, "in-kernel upsampling of the inverse depths is implemented by the sweep kernels only "
+                       "(photometric_reduce_op='min', ssim_loss_weight > 0, clip_loss = 0); upsample before the loss otherwise");
+  }
   const int groups = (c->automask ? 2 : 1) * c->C * (c->ssim_w > 0.0 ? 1 : 3);
   if (groups > 254) return psfm_fail(PSFM_ERR_INVALID, "too many candidates (%d)", groups);
   return PSFM_OK;
@@ -150,8 +160,11 @@ int psfm_loss_forward(const psfm_loss_cfg* cfg, const psfm_loss_io* io, void* wo
   int rc = check_cfg(cfg);
   if (rc) return rc;
   if ((rc = check_io(cfg, io, false))) return rc;
-  for (int s = 0; s < cfg->n; ++s)
+  for (int s = 0; s < cfg->n; ++s) {
     if (!io->sel[s]) return psfm_fail(PSFM_ERR_INVALID, "sel[%d] is NULL", s);
+    if (cfg->Hd[s] > 0 && (cfg->Hd[s] != cfg->Hs[s] || cfg->Wd[s] != cfg->Ws[s]))
+      return psfm_fail(PSFM_ERR_INVALID, "in-kernel upsampling: use psfm_loss_forward_backward");
+  }
   if (!loss_out || !workspace) return psfm_fail(PSFM_ERR_INVALID, "loss_out / workspace is NULL");
   if (workspace_bytes < psfm::loss_workspace_bytes(cfg))
     return psfm_fail(PSFM_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes, psfm::loss_workspace_bytes(cfg));
@@ -163,8 +176,11 @@ int psfm_loss_backward(const psfm_loss_cfg* cfg, const psfm_loss_io* io, void* w
   int rc = check_cfg(cfg);
   if (rc) return rc;
   if ((rc = check_io(cfg, io, true))) return rc;
-  for (int s = 0; s < cfg->n; ++s)
+  for (int s = 0; s < cfg->n; ++s) {
     if (!io->sel[s]) return psfm_fail(PSFM_ERR_INVALID, "sel[%d] is NULL", s);
+    if (cfg->Hd[s] > 0 && (cfg->Hd[s] != cfg->Hs[s] || cfg->Wd[s] != cfg->Ws[s]))
+      return psfm_fail(PSFM_ERR_INVALID, "in-kernel upsampling: use psfm_loss_forward_backward");
+  }
   if (!grad_loss || !workspace) return psfm_fail(PSFM_ERR_INVALID, "grad_loss / workspace is NULL");
   if (workspace_bytes < psfm::loss_workspace_bytes(cfg))
     return psfm_fail(PSFM_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes, psfm::loss_workspace_bytes(cfg));

@@ -32,6 +32,7 @@ EXPORTS = ('psfm_abi_version', 'psfm_last_error', 'psfm_launch_count', 'psfm_pro
 class LossCfg(C.Structure):
     _fields_ = [('B', C.c_int32), ('C', C.c_int32), ('n', C.c_int32), ('H', C.c_int32), ('W', C.c_int32),
                 ('Hs', C.c_int32 * MAX_SCALES), ('Ws', C.c_int32 * MAX_SCALES),
+                ('Hd', C.c_int32 * MAX_SCALES), ('Wd', C.c_int32 * MAX_SCALES),
                 ('img_dtype', C.c_int32), ('real_dtype', C.c_int32), ('padding', C.c_int32),
                 ('reduce_op', C.c_int32), ('automask', C.c_int32), ('premap', C.c_int32),
                 ('ssim_w', C.c_double), ('smooth_w', C.c_double), ('C1', C.c_double), ('C2', C.c_double),
@@ -107,7 +108,7 @@ def _load():
         fn = getattr(lib, name)
         fn.restype = i
         fn.argtypes = args
-    if lib.psfm_abi_version() != 1:
+    if lib.psfm_abi_version() != 2:
         raise ImportError('libpsfm_b200.so ABI version mismatch: %d' % lib.psfm_abi_version())
     return lib
 

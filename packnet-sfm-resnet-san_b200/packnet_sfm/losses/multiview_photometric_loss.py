@@ -52,6 +52,11 @@ class MultiViewPhotometricLoss(LossBase):
         # the default takes true inverse depths (upstream / north-star semantics)
         self.sigmoid_premap = bool(kwargs.get('sigmoid_premap', False))
         self.kernel_mode = kwargs.get('kernel_mode', None)      # None -> ops.DEFAULT_MODE
+        # cfg.model.loss.upsample_depth_maps (configs/default_config.py:24): in the reference the MODEL
+        # nearest-upsamples every scale to full resolution before this loss sees it
+        # (models/SfmModel.py:86-88 -> models/model_utils.py:152-176).  With this flag the loss takes the
+        # decoder's native pyramid and does that upsampling (and its adjoint) inside the kernels.
+        self.upsample_depth_maps = bool(kwargs.get('upsample_depth_maps', False))
         if self.automask_loss:
             assert self.photometric_reduce_op == 'min', \
                 'For automasking only the min photometric_reduce_op is supported.'
@@ -64,7 +69,8 @@ class MultiViewPhotometricLoss(LossBase):
         return dict(ssim_loss_weight=self.ssim_loss_weight, smooth_loss_weight=self.smooth_loss_weight,
                     C1=self.C1, C2=self.C2, photometric_reduce_op=self.photometric_reduce_op,
                     clip_loss=self.clip_loss, padding_mode=self.padding_mode, automask_loss=self.automask_loss,
-                    premap=int(self.sigmoid_premap), min_depth=self.min_depth, max_depth=self.max_depth)
+                    premap=int(self.sigmoid_premap), min_depth=self.min_depth, max_depth=self.max_depth,
+                    upsample_depth_maps=self.upsample_depth_maps)
 
     def warp_ref_image(self, inv_depths, ref_image, K, ref_K, pose):
         """Warp `ref_image` into the target view at every scale (upstream pinhole body of

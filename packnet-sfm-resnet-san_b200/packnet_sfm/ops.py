@@ -66,6 +66,7 @@ class _LossPlan:
         img_dtype = image.dtype
         dev = image.device
         self.real, self.dev, self.n, self.C, self.B = real, dev, n, Cn, B
+        self.upsampled = False
         cfg = _C.LossCfg()
         cfg.B, cfg.C, cfg.n, cfg.H, cfg.W = B, Cn, n, H, W
         cfg.img_dtype = _C.dtype_code(image)
@@ -93,6 +94,13 @@ class _LossPlan:
             if d.dim() != 4 or d.shape[0] != B or d.shape[1] != 1 or d.dtype != real:
                 raise ValueError('inv_depths[%d] must be [B,1,Hs,Ws] %s' % (s, real))
             Hs, Ws = int(d.shape[2]), int(d.shape[3])
+            if hp.get('upsample_depth_maps') and (Hs, Ws) != (H, W):
+                # the map is nearest-upsampled to the image size inside the kernels (models/model_utils.py:152-176)
+                if Hs > H or Ws > W:
+                    raise ValueError('upsample_depth_maps: inv_depths[%d] is larger than the image' % s)
+                cfg.Hd[s], cfg.Wd[s] = Hs, Ws
+                Hs, Ws = H, W
+                self.upsampled = True
             cfg.Hs[s], cfg.Ws[s] = Hs, Ws
             if (Hs, Ws) == (H, W):          # interpolate_image returns the image itself (utils/image.py:138-142)
                 img_s, ctx_s, mask_s = image, context, mask
@@ -122,7 +130,7 @@ class _LossPlan:
         if self.ws_bytes == 0:
             _C.check(-1)
         self.ws = torch.empty(self.ws_bytes, dtype=torch.uint8, device=dev)
-        self.sel = [torch.empty((B,) + tuple(d.shape[2:]), dtype=torch.uint8, device=dev) for d in self.inv_depths]
+        self.sel = [torch.empty((B, cfg.Hs[s], cfg.Ws[s]), dtype=torch.uint8, device=dev) for s in range(n)]
         for s in range(n):
             io.sel[s] = self.sel[s].data_ptr()
         self.out = torch.empty(3, dtype=real, device=dev)
@@ -155,7 +163,9 @@ class _PhotometricLossFn(torch.autograd.Function):
         need_grad = any(t.requires_grad for t in tensors[Cn:])
         st = _C.stream_ptr(plan.dev)
         with torch.cuda.device(plan.dev):
-            if need_grad and mode == 'fused':
+            if plan.upsampled and mode != 'fused':
+                raise NotImplementedError("upsample_depth_maps needs kernel_mode='fused'")
+            if (need_grad or plan.upsampled) and mode == 'fused':
                 plan.alloc_grads()
                 _C.check(_C.lib.psfm_loss_forward_backward(*plan.args(), _C.ptr(plan.out), st))
             else:

@@ -54,3 +54,46 @@ def test_fp64_kernels_match_live_oracle(name):
         assert rel_l2(a, b) <= 1e-8
     for a, b in zip(res['d_mat'], ref['d_mat']):
         assert rel_l2(a, b) <= 1e-8
+
+
+@pytest.mark.parametrize('case', [
+    dict(B=2, H=64, W=160, C=2, pm='zeros', dtype=torch.float64),
+    dict(B=2, H=24, W=40, C=2, pm='border', dtype=torch.float64, kd=5, n=3),
+    dict(B=1, H=192, W=640, C=2, pm='zeros', dtype=torch.float64),
+    dict(B=2, H=64, W=160, C=2, pm='zeros', dtype=torch.float32),
+])
+def test_in_kernel_upsampling_of_the_depth_pyramid(case):
+    """`upsample_depth_maps=True`: the loss takes the decoder's native pyramid [B,1,H>>s,W>>s] and does what the
+    reference's MODEL does before its loss -- nearest upsampling to full resolution, models/SfmModel.py:86-88 ->
+    models/model_utils.py:152-176 -> F.interpolate(mode='nearest') -- inside the kernels, adjoint included.
+    Oracle: F.interpolate + the U-mode oracle loss, gradients taken w.r.t. the pyramid."""
+    import torch.nn.functional as F
+    import photometric_oracle as O
+    from golden_cases import YAML_LOSS
+    from packnet_sfm.geometry.pose import Pose
+    from packnet_sfm.losses.multiview_photometric_loss import MultiViewPhotometricLoss
+    n = case.get('n', 4)
+    hp = dict(YAML_LOSS, padding_mode=case['pm'], num_scales=n)
+    image, context, pyr, vecs, K = O.synth_S3(case['B'], case['H'], case['W'], case['C'], torch.float64, pyramid=True,
+                                              kd=case.get('kd', 15 if case['H'] >= 128 else 7), n=n)
+    d64 = [d.clone().requires_grad_() for d in pyr]
+    v64 = [v.clone().requires_grad_() for v in vecs]
+    up = [d if s == 0 else F.interpolate(d, size=(case['H'], case['W']), mode='nearest') for s, d in enumerate(d64)]
+    ref = O.multiview_photometric_loss(image, context, up, K, K, [O.pose_vec_to_mat(v) for v in v64], **hp)
+    ref['loss'].backward()
+    dt, dev = case['dtype'], 'cuda:0'
+    dg = [d.to(dev).to(dt).requires_grad_() for d in pyr]
+    vg = [v.to(dev).to(dt).requires_grad_() for v in vecs]
+    L = MultiViewPhotometricLoss(upsample_depth_maps=True, **hp)
+    out = L(image.to(dev).to(dt), [c.to(dev).to(dt) for c in context], dg, K.to(dev).to(dt), K.to(dev).to(dt),
+            [Pose.from_vec(v, 'euler') for v in vg])
+    out['loss'].backward()
+    torch.cuda.synchronize()
+    f64 = dt == torch.float64
+    assert abs(out['loss'].item() - ref['loss'].item()) <= (1e-10 if f64 else 1e-5) * abs(ref['loss'].item())
+    for s in range(n):
+        assert dg[s].grad.shape == pyr[s].shape
+        # fp32: pooled sums average the flip-pixel noise of DESIGN.md T2/T3; bound as in T3
+        assert rel_l2(dg[s].grad.cpu(), d64[s].grad) <= (1e-8 if f64 else 1e-2), 'scale %d' % s
+    for a, b in zip(vg, v64):
+        assert rel_l2(a.grad.cpu(), b.grad) <= (1e-8 if f64 else 1e-2)
