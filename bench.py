@@ -76,7 +76,11 @@ def synth_batch(cfg, device, seed=1234):
     idt = torch.bfloat16 if cfg['img'] == 'bf16' else torch.float32
     image = tex(3, 3).to(idt)
     context = [tex(3, 3).to(idt) for _ in range(C)]
-    inv_depths = [1.0 / (2.0 + 38.0 * tex(1, 15)) for _ in range(n)]
+    if cfg.get('pyramid'):      # the decoder's native pyramid; the loss upsamples it in-kernel (upsample_depth_maps)
+        inv_depths = [1.0 / (2.0 + 38.0 * F.interpolate(tex(1, 15), size=(H >> s, W >> s), mode='bilinear',
+                                                         align_corners=False)) for s in range(n)]
+    else:
+        inv_depths = [1.0 / (2.0 + 38.0 * tex(1, 15)) for _ in range(n)]
     base = torch.tensor([0.02, -0.01, 0.8, 0.003, -0.01, 0.002])
     vecs = []
     for j in range(C):
@@ -222,9 +226,10 @@ def run_ours(args):
     from packnet_sfm.geometry.pose import Pose
     sys.path.insert(0, os.path.join(ROOT, 'oracle'))
 
-    cfg = CONFIGS[args.config]
+    cfg = dict(CONFIGS[args.config], pyramid=args.pyramid)
     B = cfg['B']
-    loss_fn = MultiViewPhotometricLoss(padding_mode=cfg['padding'], kernel_mode=args.mode, **LOSS_HP)
+    loss_fn = MultiViewPhotometricLoss(padding_mode=cfg['padding'], kernel_mode=args.mode,
+                                       upsample_depth_maps=args.pyramid, **LOSS_HP)
     real_b = 4
     e = 2 if cfg['img'] == 'bf16' else 4
     P = cfg['H'] * cfg['W']
@@ -435,7 +440,9 @@ def run_ours(args):
         line = {'metric': METRIC, 'value': frames / (t_ms * 1e-3), 'unit': 'frames/s', 'n_gpus': world,
                 'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': t_ms / args.steps,
                 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-                'config': {'workload': workload_name(args.config, cfg), 'global_batch': world * B,
+                'config': {'workload': workload_name(args.config, cfg) + (
+                               ' [inverse depths given as the decoder pyramid, upsampled in-kernel]' if args.pyramid else ''),
+                           'global_batch': world * B,
                            'l2': 'rotating %d resident input sets (%.0f MB total footprint > 3x 126 MB L2)' % (
                                R, R * foot / 2 ** 20),
                            'cuda_graph': use_graph, 'kernel_mode': args.mode or 'fused',
@@ -466,6 +473,9 @@ def main():
     ap.add_argument('--no-graph', action='store_true')
     ap.add_argument('--no-rotate', action='store_true')
     ap.add_argument('--no-cpu', action='store_true')
+    ap.add_argument('--pyramid', action='store_true',
+                    help='secondary measurement: inverse depths as the decoder pyramid [B,1,H>>s,W>>s], nearest-'
+                         'upsampled inside the kernels (upsample_depth_maps=True) instead of by the caller')
     args = ap.parse_args()
     if args.impl == 'reference':
         run_reference(args)

@@ -446,7 +446,9 @@ __device__ __forceinline__ double signed_by(double mag, double x) {
 #ifndef PSFM_SWEEP_MINB
 #define PSFM_SWEEP_MINB 1            // resident CTAs per SM the 2-context fp32 instantiation is compiled for
 #endif
-template <typename real, int PAD, bool RARE, int CT>
+// VAR: 0 = plain, 1 = inverse depths upsampled on load (all scales of the set), 2 = rare settings (fork pre-map;
+// upsampling decided per scale at run time)
+template <typename real, int PAD, int VAR, int CT>
 #ifdef PSFM_SWEEP_MAXREG
 __global__ void __maxnreg__(PSFM_SWEEP_MAXREG) sweep_kernel(const SweepParams SP) {
 #else
@@ -479,13 +481,13 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
   const vec4* rb = (const vec4*)S.rb + (size_t)b * plane;
   const vec4* rcp = (const vec4*)S.rc + (size_t)b * plane;
   asm volatile("" : "+l"(ctxp), "+l"(ra), "+l"(rb), "+l"(rcp));   // opaque: one IMAD.WIDE per load off a 32-bit offset
-  const bool ups = RARE && (SD.Hd != H || SD.Wd != W);          // inverse depths nearest-upsampled on load
+  const bool ups = VAR == 1 || (VAR == 2 && (SD.Hd != H || SD.Wd != W));   // inverse depths nearest-upsampled on load
   const real* invd = (const real*)SD.invd + (size_t)b * SD.Hd * SD.Wd;
   const int Wd = SD.Wd, sud = nearest_src(su, SD.cs, SD.Wd, ups);
   auto dofs = [&](int row) { return nearest_src(reflect1(row, H), SD.rs, SD.Hd, ups) * Wd + sud; };
   const real* wxy = (const real*)S.wxy + (size_t)b * plane * 2;
   const int Wp = S.Wp;
-  const bool premap = RARE && P.premap;
+  const bool premap = VAR == 2 && P.premap;
   const bool smooth = P.smooth_w > 0.0;
 
   // ---- per-thread geometry constants: p = (A0 + A1 v) D + m with A = ref_K R Kinv (u, v, 1) ---------
@@ -809,6 +811,28 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
 // pool kernel: adjoint of the in-kernel nearest upsampling.  grid (ceil(Hd Wd / 256), B), 256 threads; one
 // thread sums, in a fixed order, the full-resolution gradients of the pixels that read its map element.
 // ------------------------------------------------------------------------------------------
+// power-of-two factors (the decoder pyramid): block = one map row x 256 full-resolution columns; coalesced column sums
+// over the fy rows, then fx neighbours from shared memory, both in a fixed order
+template <typename real>
+__global__ void __launch_bounds__(256) pool_pow2_kernel(int H, int W, int Hd, int Wd, int fy, int fx,
+                                                        const real* __restrict__ full, real* __restrict__ out) {
+  __shared__ real col[256];
+  const int vs = blockIdx.y, b = blockIdx.z, c = blockIdx.x * 256 + threadIdx.x;
+  real acc = real(0);
+  if (c < W) {
+    const real* src = full + ((size_t)b * H + (size_t)vs * fy) * W + c;
+    for (int r = 0; r < fy; ++r) acc += src[(size_t)r * W];
+  }
+  col[threadIdx.x] = acc;
+  __syncthreads();
+  const int us = (blockIdx.x * 256) / fx + threadIdx.x;
+  if ((int)threadIdx.x < 256 / fx && us < Wd) {
+    real a = real(0);
+    for (int k = 0; k < fx; ++k) a += col[threadIdx.x * fx + k];
+    out[((size_t)b * Hd + vs) * Wd + us] = a;
+  }
+}
+
 template <typename real>
 __global__ void __launch_bounds__(256) pool_kernel(int H, int W, int Hd, int Wd, float rs, float cs,
                                                    const real* __restrict__ full, real* __restrict__ out) {
@@ -1048,9 +1072,9 @@ static void fill_consts(SweepConsts<real>& c, const LossParams& P, int s0) {
   }
 }
 
-template <typename real, int PAD, bool RARE, int CT>
+template <typename real, int PAD, int VAR, int CT>
 static cudaError_t launch_sweep_ct(const SweepParams& SP, dim3 grid, int threads, size_t smem, cudaStream_t st) {
-  auto kern = sweep_kernel<real, PAD, RARE, CT>;
+  auto kern = sweep_kernel<real, PAD, VAR, CT>;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
@@ -1060,13 +1084,13 @@ static cudaError_t launch_sweep_ct(const SweepParams& SP, dim3 grid, int threads
 }
 
 // the common context counts get their own instantiation (unrolled candidate min, tighter launch bounds)
-template <typename real, int PAD, bool RARE>
+template <typename real, int PAD, int VAR>
 static cudaError_t launch_sweep(const SweepParams& SP, dim3 grid, int threads, size_t smem, cudaStream_t st) {
-  if (!RARE) {
-    if (SP.P.C == 2) return launch_sweep_ct<real, PAD, RARE, 2>(SP, grid, threads, smem, st);
-    if (SP.P.C == 4) return launch_sweep_ct<real, PAD, RARE, 4>(SP, grid, threads, smem, st);
+  if (VAR != 2) {
+    if (SP.P.C == 2) return launch_sweep_ct<real, PAD, VAR, 2>(SP, grid, threads, smem, st);
+    if (SP.P.C == 4) return launch_sweep_ct<real, PAD, VAR, 4>(SP, grid, threads, smem, st);
   }
-  return launch_sweep_ct<real, PAD, RARE, 0>(SP, grid, threads, smem, st);
+  return launch_sweep_ct<real, PAD, VAR, 0>(SP, grid, threads, smem, st);
 }
 
 template <typename real, typename img_t>
@@ -1083,13 +1107,8 @@ static cudaError_t run_sweep(const psfm_loss_cfg* cfg, const psfm_loss_io* io, v
     SP.loss_part[s] = (double*)(w + pl.off_loss[s]);
     SP.pose_part[s] = w + pl.off_pose[s];
   }
-  bool rare = cfg->premap != 0;           // masks travel in the pixel records and cost nothing extra
-  for (int s = 0; s < cfg->n; ++s) {
-    if (SP.P.sc[s].Hd != SP.P.sc[s].H || SP.P.sc[s].Wd != SP.P.sc[s].W) {
-      SP.P.sc[s].d_full = (char*)ws_stream + pl.off_dfull[s];
-      rare = true;
-    }
-  }
+  for (int s = 0; s < cfg->n; ++s)      // upsampled scales: the sweep writes full-resolution gradients, pooled afterwards
+    if (SP.P.sc[s].Hd != SP.P.sc[s].H || SP.P.sc[s].Wd != SP.P.sc[s].W) SP.P.sc[s].d_full = (char*)ws_stream + pl.off_dfull[s];
   for (int i = 0; i < pl.nsets; ++i) {
     SP.set = pl.sets[i];
     const int s0 = SP.set.scale[0];
@@ -1129,20 +1148,28 @@ static cudaError_t run_sweep(const psfm_loss_cfg* cfg, const psfm_loss_io* io, v
     const int threads = 32 * cfg->C;
     ProfScope ps(st, kTagFused, 1);
     cudaError_t e;
-    if (cfg->padding == PSFM_PAD_BORDER)
-      e = rare ? launch_sweep<real, PSFM_PAD_BORDER, true>(SP, grid, threads, smem, st)
-               : launch_sweep<real, PSFM_PAD_BORDER, false>(SP, grid, threads, smem, st);
-    else
-      e = rare ? launch_sweep<real, PSFM_PAD_ZEROS, true>(SP, grid, threads, smem, st)
-               : launch_sweep<real, PSFM_PAD_ZEROS, false>(SP, grid, threads, smem, st);
+    int var = cfg->premap ? 2 : 0;
+    for (int k = 0; k < S.ns && var == 0; ++k)
+      if (SP.P.sc[S.scale[k]].d_full != SP.P.sc[S.scale[k]].d_invd) var = 1;
+#define PSFM_SWEEP(PADV) (var == 2 ? launch_sweep<real, PADV, 2>(SP, grid, threads, smem, st) \
+                          : var == 1 ? launch_sweep<real, PADV, 1>(SP, grid, threads, smem, st) \
+                                     : launch_sweep<real, PADV, 0>(SP, grid, threads, smem, st))
+    e = cfg->padding == PSFM_PAD_BORDER ? PSFM_SWEEP(PSFM_PAD_BORDER) : PSFM_SWEEP(PSFM_PAD_ZEROS);
+#undef PSFM_SWEEP
     if (e != cudaSuccess) return e;
   }
   for (int s = 0; s < cfg->n; ++s) {
     const ScaleDesc& D = SP.P.sc[s];
     if (D.d_full == D.d_invd) continue;
     ProfScope ps(st, kTagFinish, 1);
-    pool_kernel<real><<<dim3(cdiv(D.Hd * D.Wd, 256), cfg->B), 256, 0, st>>>(D.H, D.W, D.Hd, D.Wd, D.rs, D.cs,
-                                                                          (const real*)D.d_full, (real*)D.d_invd);
+    const int fy = D.H / D.Hd, fx = D.W / D.Wd;
+    const bool pow2 = fy * D.Hd == D.H && fx * D.Wd == D.W && (fy & (fy - 1)) == 0 && (fx & (fx - 1)) == 0 && fx <= 256;
+    if (pow2)   // floor(dst * (1 / 2^k)) == dst >> k exactly
+      pool_pow2_kernel<real><<<dim3(cdiv(D.W, 256), D.Hd, cfg->B), 256, 0, st>>>(D.H, D.W, D.Hd, D.Wd, fy, fx,
+                                                                               (const real*)D.d_full, (real*)D.d_invd);
+    else
+      pool_kernel<real><<<dim3(cdiv(D.Hd * D.Wd, 256), cfg->B), 256, 0, st>>>(D.H, D.W, D.Hd, D.Wd, D.rs, D.cs,
+                                                                            (const real*)D.d_full, (real*)D.d_invd);
   }
   FinalParams F;
   F.B = cfg->B; F.C = cfg->C; F.n = cfg->n; F.smooth = cfg->smooth_w > 0.0;

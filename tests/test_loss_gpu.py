@@ -61,6 +61,7 @@ def test_fp64_kernels_match_live_oracle(name):
     dict(B=2, H=24, W=40, C=2, pm='border', dtype=torch.float64, kd=5, n=3),
     dict(B=1, H=192, W=640, C=2, pm='zeros', dtype=torch.float64),
     dict(B=2, H=64, W=160, C=2, pm='zeros', dtype=torch.float32),
+    dict(B=2, H=30, W=50, C=2, pm='zeros', dtype=torch.float64, kd=3, n=2, sizes=[(30, 50), (10, 25)]),   # factors 3 x 2
 ])
 def test_in_kernel_upsampling_of_the_depth_pyramid(case):
     """`upsample_depth_maps=True`: the loss takes the decoder's native pyramid [B,1,H>>s,W>>s] and does what the
@@ -76,6 +77,8 @@ def test_in_kernel_upsampling_of_the_depth_pyramid(case):
     hp = dict(YAML_LOSS, padding_mode=case['pm'], num_scales=n)
     image, context, pyr, vecs, K = O.synth_S3(case['B'], case['H'], case['W'], case['C'], torch.float64, pyramid=True,
                                               kd=case.get('kd', 15 if case['H'] >= 128 else 7), n=n)
+    if 'sizes' in case:     # arbitrary (non power-of-two) map sizes: the general pooling kernel
+        pyr = [F.interpolate(pyr[0], size=sz, mode='bilinear', align_corners=False) for sz in case['sizes']]
     d64 = [d.clone().requires_grad_() for d in pyr]
     v64 = [v.clone().requires_grad_() for v in vecs]
     up = [d if s == 0 else F.interpolate(d, size=(case['H'], case['W']), mode='nearest') for s, d in enumerate(d64)]
