@@ -1,6 +1,5 @@
 // loss_sweep.cu -- single-pass photometric loss: loss AND gradients in one sweep over the inputs.
 //
-//   border_kernel  zero frame of the packed context images (below).
 //   prep_kernel    once per resolution (shared by all full-resolution scales): every context image as a
 //                  channel-interleaved, zero-bordered 4-vector image in the arithmetic type, so that one
 //                  bilinear tap is ONE 16-byte load and taps outside the image need no bounds test (zeros
@@ -93,24 +92,6 @@ struct SweepParams {
 };
 
 // ------------------------------------------------------------------------------------------
-// border kernel: zero frame of the packed context images.  grid (Hp, C, B), 128 threads; block = one
-// padded row: a frame row is cleared entirely, an image row only in its 2 + 3 frame columns.
-// ------------------------------------------------------------------------------------------
-template <typename real>
-__global__ void __launch_bounds__(128) border_kernel(const SweepParams SP) {
-  const SweepSet& S = SP.set;
-  const int yp = blockIdx.x, j = blockIdx.y, b = blockIdx.z;
-  Real4<real>* row = (Real4<real>*)S.ctxp[j] + ((size_t)b * S.Hp + yp) * S.Wp;
-  const bool frame_row = (yp < kPadLo) || (yp >= kPadLo + S.H);
-  if (frame_row) {
-    for (int x = threadIdx.x; x < S.Wp; x += blockDim.x) st4(row + x, real(0), real(0), real(0), real(0));
-  } else if (threadIdx.x < kPadLo + kPadHi) {
-    const int x = threadIdx.x < kPadLo ? threadIdx.x : S.W + threadIdx.x;
-    st4(row + x, real(0), real(0), real(0), real(0));
-  }
-}
-
-// ------------------------------------------------------------------------------------------
 // prep kernel: grid (ceil(punits / kPrepWarps), B), 32 * kPrepWarps threads; every warp is an
 // independent (strip, chunk) unit.  Lane l is column c0 - 1 + l; step t loads row t + 1 and finishes
 // row p = t - 1.  One pass over the rows handles the CT contexts [j0, j0 + CT) together (packed copy,
@@ -132,11 +113,26 @@ __global__ void __launch_bounds__(32 * kPrepWarps) prep_kernel(const SweepParams
   const LossParams& P = SP.P;
   const SweepSet& S = SP.set;
   const int lane = threadIdx.x & 31;
-  const int unit = blockIdx.x * kPrepWarps + (threadIdx.x >> 5);
   const int punits = S.pstrips * S.pchunks;
+  const int H = S.H, W = S.W, b = blockIdx.y;
+  const int nprep = (punits + kPrepWarps - 1) / kPrepWarps;
+  if ((int)blockIdx.x >= nprep) {
+    // trailing blocks: zero frame of this pass's packed context images, one warp per padded row (a frame row is
+    // cleared entirely, an image row only in its 2 + 3 frame columns)
+    const int r = ((int)blockIdx.x - nprep) * kPrepWarps + (threadIdx.x >> 5);
+    if (r >= S.Hp * CT) return;
+    const int jj = r / S.Hp, yp = r - jj * S.Hp;
+    vec4* row = (vec4*)S.ctxp[j0 + jj] + ((size_t)b * S.Hp + yp) * S.Wp;
+    if (yp < kPadLo || yp >= kPadLo + H) {
+      for (int x = lane; x < S.Wp; x += 32) st4(row + x, real(0), real(0), real(0), real(0));
+    } else if (lane < kPadLo + kPadHi) {
+      st4(row + (lane < kPadLo ? lane : W + lane), real(0), real(0), real(0), real(0));
+    }
+    return;
+  }
+  const int unit = blockIdx.x * kPrepWarps + (threadIdx.x >> 5);
   if (unit >= punits) return;
   const int strip = unit % S.pstrips, chunk = unit / S.pstrips;
-  const int H = S.H, W = S.W, b = blockIdx.y;
   const int plane = H * W;
   const int u = strip * kPrepInner - 1 + lane, su = reflect1(u, W);
   const int r0 = chunk * S.pchunk_h, r1 = min(r0 + S.pchunk_h, H);
@@ -1127,11 +1123,10 @@ static cudaError_t run_sweep(const psfm_loss_cfg* cfg, const psfm_loss_io* io, v
     {
       int npass = 0;
       for (int j0 = 0; j0 < cfg->C; j0 += (cfg->C - j0 >= 4 ? 4 : (cfg->C - j0 >= 2 ? 2 : 1))) ++npass;
-      ProfScope ps(st, kTagFwd, 1 + npass + (cfg->smooth_w > 0.0 ? 1 : 0));
-      border_kernel<real><<<dim3(S.Hp, cfg->C, cfg->B), 128, 0, st>>>(SP);
-      const dim3 pgrid(cdiv(S.pstrips * S.pchunks, kPrepWarps), cfg->B);
+      ProfScope ps(st, kTagFwd, npass + (cfg->smooth_w > 0.0 ? 1 : 0));
       for (int j0 = 0; j0 < cfg->C;) {
         const int ct = cfg->C - j0 >= 4 ? 4 : (cfg->C - j0 >= 2 ? 2 : 1);
+        const dim3 pgrid(cdiv(S.pstrips * S.pchunks, kPrepWarps) + cdiv(S.Hp * ct, kPrepWarps), cfg->B);
 #define PSFM_PREP(CTV, AM, FI) prep_kernel<real, img_t, CTV, AM, FI><<<pgrid, 32 * kPrepWarps, 0, st>>>(SP, j0)
 #define PSFM_PREP_CT(AM, FI) (ct == 4 ? PSFM_PREP(4, AM, FI) : ct == 2 ? PSFM_PREP(2, AM, FI) : PSFM_PREP(1, AM, FI))
         if (cfg->automask) { if (j0 == 0) PSFM_PREP_CT(true, true); else PSFM_PREP_CT(true, false); }
