@@ -217,9 +217,8 @@ def run_ours(args):
     dev = torch.device('cuda', local)
     torch.cuda.set_device(dev)
     if world > 1:
-        # NCCL prints its version banner on stdout at NCCL_DEBUG=VERSION; stdout carries the ONE JSON line
-        if os.environ.get('NCCL_DEBUG', '').upper() in ('', 'VERSION'):
-            os.environ['NCCL_DEBUG'] = 'WARN'
+        # NCCL writes its version banner / debug lines to stdout by default; stdout carries the ONE JSON line
+        os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')
         dist.init_process_group('nccl', device_id=dev)
     from packnet_sfm import _C
     from packnet_sfm.losses.multiview_photometric_loss import MultiViewPhotometricLoss
