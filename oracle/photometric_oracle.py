@@ -138,6 +138,83 @@ def view_synthesis(ref_image, depth, ref_K, Tcw_ref, K, padding_mode='zeros'):
 
 
 # --------------------------------------------------------------------------------------
+# fisheye (VADAS) camera  --  SURVEY.md §8(f) N1
+# Intrinsics are a dict of per-image tensors: k [B,7], s [B], div [B], ux [B], uy [B]
+# (datasets/ncdb_dataset.py:577-584; geometry/camera.py:199-220).
+# --------------------------------------------------------------------------------------
+
+FISHEYE_EPS = 2.220446049250313e-16      # sys.float_info.epsilon (geometry/camera.py:287,355,373)
+
+
+def fisheye_scaled(intr, sw, sh):
+    """Per-scale intrinsics as the fork's `warp_ref_image` builds them: only the principal point moves,
+    k / s / div are passed through unscaled (losses/multiview_photometric_loss.py:158-183)."""
+    out = dict(intr)
+    out['ux'] = (intr['ux'] + 0.5) * sw - 0.5
+    out['uy'] = (intr['uy'] + 0.5) * sh - 0.5
+    return out
+
+
+def fisheye_reconstruct(depth, intr):
+    """`FisheyeCamera.reconstruct(depth, frame='c')`: [B,1,H,W] -> [B,3,H,W]  (geometry/camera.py:242-305).
+    The inverse of the distortion polynomial is the reference's placeholder theta = r_d."""
+    B, _, H, W = depth.shape
+    g = pixel_grid(B, H, W, depth.dtype, depth.device)
+    xd = (g[:, 0] - intr['ux'].unsqueeze(1)) / intr['s'].unsqueeze(1)
+    yd = (g[:, 1] - intr['uy'].unsqueeze(1)) / intr['div'].unsqueeze(1)
+    rd = torch.sqrt(xd ** 2 + yd ** 2)
+    r = torch.tan(rd)
+    rd_safe = torch.where(rd < FISHEYE_EPS, torch.full_like(rd, FISHEYE_EPS), rd)
+    d = depth.reshape(B, -1)
+    return torch.stack([(r / rd_safe) * xd * d, (r / rd_safe) * yd * d, d], 1).view(B, 3, H, W)
+
+
+def fisheye_project(X, intr):
+    """`FisheyeCamera.project(X, frame='c')`: [B,3,H,W] -> normalised grid [B,H,W,2]  (geometry/camera.py:311-394)."""
+    B, _, H, W = X.shape
+    Xc = X.reshape(B, 3, -1)
+    Z = Xc[:, 2].clamp(min=FISHEYE_EPS)
+    xn, yn = Xc[:, 0] / Z, Xc[:, 1] / Z
+    r = torch.sqrt(xn ** 2 + yn ** 2)
+    theta = torch.atan(r)
+    k = intr['k']
+    poly = k[:, 0].unsqueeze(1)
+    for i in range(1, 7):
+        poly = poly + k[:, i].unsqueeze(1) * torch.pow(theta, i)
+    r_safe = torch.where(r < FISHEYE_EPS, torch.full_like(r, FISHEYE_EPS), r)
+    u = intr['s'].unsqueeze(1) * ((poly / r_safe) * xn) + intr['ux'].unsqueeze(1)
+    v = intr['div'].unsqueeze(1) * ((poly / r_safe) * yn) + intr['uy'].unsqueeze(1)
+    return torch.stack([2 * u / (W - 1) - 1., 2 * v / (H - 1) - 1.], -1).view(B, H, W, 2)
+
+
+def fisheye_view_synthesis(ref_image, depth, ref_intr, Tcw_ref, intr, padding_mode='zeros'):
+    """`view_synthesis` with two `FisheyeCamera`s (geometry/camera_utils.py:27-59).  As shipped the reference
+    raises inside `reconstruct(frame='w')` / `project(frame='w')` because `Pose.transform_points` takes
+    [B,3,H,W] only; this is the composition those lines spell out, with the pose
+    applied to the 4-D tensor: project_c(Tcw_ref . reconstruct_c(depth))."""
+    coords = fisheye_project(transform_points(Tcw_ref, fisheye_reconstruct(depth, intr)), ref_intr)
+    return F.grid_sample(ref_image, coords, mode='bilinear', padding_mode=padding_mode, align_corners=True)
+
+
+def fisheye_pack(intr):
+    """dict -> [B,11] rows (k0..k6, s, div, ux, uy): the layout of the C ABI (`psfm_loss_io::fisheye`)."""
+    return torch.cat([intr['k'], intr['s'].unsqueeze(1), intr['div'].unsqueeze(1), intr['ux'].unsqueeze(1),
+                      intr['uy'].unsqueeze(1)], 1)
+
+
+def synth_fisheye(B, H, W, dtype=torch.float64):
+    """Deterministic VADAS-like intrinsics for the synthetic recipe (per-image variation, principal point off
+    the pixel grid so that no pixel sits exactly on the optical axis)."""
+    t = torch.arange(B, dtype=torch.float64)
+    k = torch.tensor([0.002, 1.0, -0.01, -0.06, 0.004, 0.012, -0.002], dtype=torch.float64).repeat(B, 1)
+    k[:, 1] += 0.01 * t
+    k[:, 3] -= 0.003 * t
+    intr = dict(k=k, s=0.62 * W + 1.5 * t, div=0.60 * W - 0.8 * t, ux=0.5 * W - 0.37 + 0.9 * t,
+                uy=0.5 * H + 0.21 - 0.6 * t)
+    return {n: v.to(dtype) for n, v in intr.items()}
+
+
+# --------------------------------------------------------------------------------------
 # image pyramid helpers
 # --------------------------------------------------------------------------------------
 
@@ -254,6 +331,12 @@ def multiview_photometric_loss(image, context, inv_depths, K, ref_K, pose_mats, 
         warped = []
         for i in range(n):
             sf = inv_depths[i].shape[3] / float(W)
+            if isinstance(K, dict):      # fisheye intrinsics (the fork's forward, :331-410 with :131-195)
+                sh = inv_depths[i].shape[2] / float(image.shape[-2])
+                warped.append(fisheye_view_synthesis(ref_images[i], inv2depth(inv_depths[i]),
+                                                     fisheye_scaled(ref_K, sf, sh), T, fisheye_scaled(K, sf, sh),
+                                                     padding_mode))
+                continue
             warped.append(view_synthesis(ref_images[i], inv2depth(inv_depths[i]), scale_K(ref_K, sf), T,
                                          scale_K(K, sf), padding_mode))
         warped_all.append(warped)

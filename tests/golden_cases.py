@@ -41,6 +41,19 @@ for _B, _H, _W in ((2, 64, 160), (1, 192, 640)):
             CASES['B%d_%dx%d_C2_%s_%s' % (_B, _H, _W, 'P' if _pyr else 'U', _pm)] = (
                 dict(B=_B, H=_H, W=_W, C=2, pyramid=_pyr), dict(padding_mode=_pm), {})
 
+# the same recipe seen through fisheye (VADAS) cameras (oracle/gen_golden_fisheye.py)
+CASES.update({
+    'fisheye_tiny_U_zeros': (dict(_T, pyramid=False), {}, dict(fisheye=True)),
+    'fisheye_tiny_U_border': (dict(_T, pyramid=False), dict(padding_mode='border'), dict(fisheye=True)),
+    'fisheye_tiny_P_zeros': (dict(_T, pyramid=True), {}, dict(fisheye=True)),
+    'fisheye_tiny_U_mask': (dict(_T, pyramid=False), {}, dict(fisheye=True, with_mask=True)),
+    'fisheye_tiny_U_odd_C4': (dict(_T, H=23, W=37, C=4, pyramid=False), {}, dict(fisheye=True)),
+    'fisheye_B2_64x160_C2_U_zeros': (dict(B=2, H=64, W=160, C=2, pyramid=False), {}, dict(fisheye=True)),
+    'fisheye_B2_64x160_C2_U_border': (dict(B=2, H=64, W=160, C=2, pyramid=False), dict(padding_mode='border'),
+                                      dict(fisheye=True)),
+    'fisheye_B1_192x640_C2_U_zeros': (dict(B=1, H=192, W=640, C=2, pyramid=False), {}, dict(fisheye=True)),
+})
+
 FORK_RANGE = (0.5, 80.0)
 
 
@@ -65,5 +78,10 @@ def make_inputs(name, dtype=torch.float64, device='cpu', seed=1234):
         gm = torch.Generator('cpu').manual_seed(seed + 7)
         mask = (torch.rand(skw['B'], 1, skw['H'], skw['W'], generator=gm, dtype=torch.float64) > 0.3).to(torch.float64)
     mv = lambda t: t.to(device=device, dtype=dtype)
+    if extra.get('fisheye'):      # K becomes the intrinsics dict (k, s, div, ux, uy) of the fork's forward
+        from photometric_oracle import synth_fisheye
+        K = {n: mv(v) for n, v in synth_fisheye(skw['B'], skw['H'], skw['W']).items()}
+        return dict(image=mv(image), context=[mv(c) for c in context], inv_depths=[mv(d) for d in inv_depths],
+                    vecs=[mv(v) for v in vecs], K=K, mask=None if mask is None else mv(mask), hp=hp, fork=fork)
     return dict(image=mv(image), context=[mv(c) for c in context], inv_depths=[mv(d) for d in inv_depths],
                 vecs=[mv(v) for v in vecs], K=mv(K), mask=None if mask is None else mv(mask), hp=hp, fork=fork)

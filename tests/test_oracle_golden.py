@@ -11,6 +11,7 @@ from golden_cases import CASES, load_golden, make_inputs
 TINY = [n for n in CASES if n.startswith('tiny')]
 MID = [n for n in CASES if n.startswith('B2_')]
 BIG = [n for n in CASES if n.startswith('B1_')]
+FISHEYE = [n for n in CASES if n.startswith('fisheye_')]
 
 
 def run_oracle(name, dtype=torch.float64):
@@ -58,6 +59,28 @@ def test_oracle_matches_reference_small(name):
 @pytest.mark.parametrize('name', BIG[:2])
 def test_oracle_matches_reference_kitti(name):
     check_case(name)
+
+
+@pytest.mark.parametrize('name', FISHEYE)
+def test_oracle_matches_reference_fisheye(name):
+    """the reference's FisheyeCamera inside its loss (oracle/gen_golden_fisheye.py)."""
+    check_case(name)
+
+
+def test_fisheye_units_against_reference():
+    """FisheyeCamera.reconstruct / project (frame 'c') of the reference, incl. points behind the camera."""
+    u = load_golden('fisheye_units')
+    t = lambda k: torch.from_numpy(u[k])
+    intr = {n: t('intr_' + n) for n in ('k', 's', 'div', 'ux', 'uy')}
+    eq = lambda a, b: np.testing.assert_allclose(a.numpy(), u[b], rtol=1e-12, atol=1e-14)
+    X = O.fisheye_reconstruct(t('depth'), intr)
+    eq(X, 'reconstruct_c')
+    Xr = O.transform_points(t('pose_mat'), X)
+    eq(O.fisheye_project(Xr, intr), 'project_c')
+    eq(O.fisheye_project(t('edge_points'), intr), 'project_edge')
+    for pm in ('zeros', 'border'):
+        eq(O.fisheye_view_synthesis(t('img'), t('depth'), intr, t('pose_mat'), intr, pm), 'view_synthesis_' + pm)
+    assert O.fisheye_pack(intr).shape == (2, 11)
 
 
 def test_survey_appendix_b_values():
