@@ -88,6 +88,9 @@ def synth_batch(cfg, device, seed=1234):
         v[2] *= (-1.0 if j % 2 == 0 else 1.0)
         vecs.append(v.repeat(B, 1) + 0.01 * torch.randn(B, 6, generator=g))
     K = torch.tensor([[0.58 * W, 0, 0.5 * W], [0, 1.92 * H, 0.5 * H], [0, 0, 1.]]).repeat(B, 1, 1)
+    if cfg.get('camera') == 'fisheye':      # packed VADAS rows (k0..k6, s, div, ux, uy), include/psfm.h
+        K = torch.tensor([0.002, 1.0, -0.01, -0.06, 0.004, 0.012, -0.002, 0.62 * W, 0.60 * W, 0.5 * W - 0.37,
+                          0.5 * H + 0.21]).repeat(B, 1)
     host = dict(image=image, context=context, inv_depths=inv_depths, vecs=vecs, K=K)
     if device is None:
         return host
@@ -225,7 +228,7 @@ def run_ours(args):
     from packnet_sfm.geometry.pose import Pose
     sys.path.insert(0, os.path.join(ROOT, 'oracle'))
 
-    cfg = dict(CONFIGS[args.config], pyramid=args.pyramid)
+    cfg = dict(CONFIGS[args.config], pyramid=args.pyramid, camera=args.camera)
     B = cfg['B']
     loss_fn = MultiViewPhotometricLoss(padding_mode=cfg['padding'], kernel_mode=args.mode,
                                        upsample_depth_maps=args.pyramid, **LOSS_HP)
@@ -440,7 +443,8 @@ def run_ours(args):
                 'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': t_ms / args.steps,
                 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
                 'config': {'workload': workload_name(args.config, cfg) + (
-                               ' [inverse depths given as the decoder pyramid, upsampled in-kernel]' if args.pyramid else ''),
+                               ' [inverse depths given as the decoder pyramid, upsampled in-kernel]' if args.pyramid else '') + (
+                               ' [fisheye (VADAS) cameras instead of pinhole K]' if args.camera == 'fisheye' else ''),
                            'global_batch': world * B,
                            'l2': 'rotating %d resident input sets (%.0f MB total footprint > 3x 126 MB L2)' % (
                                R, R * foot / 2 ** 20),
@@ -472,6 +476,8 @@ def main():
     ap.add_argument('--no-graph', action='store_true')
     ap.add_argument('--no-rotate', action='store_true')
     ap.add_argument('--no-cpu', action='store_true')
+    ap.add_argument('--camera', default='pinhole', choices=['pinhole', 'fisheye'],
+                    help='fisheye: the VADAS camera model of the fork (SURVEY.md 8(f) N1) instead of pinhole K')
     ap.add_argument('--pyramid', action='store_true',
                     help='secondary measurement: inverse depths as the decoder pyramid [B,1,H>>s,W>>s], nearest-'
                          'upsampled inside the kernels (upsample_depth_maps=True) instead of by the caller')

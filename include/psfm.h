@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define PSFM_ABI_VERSION 2
+#define PSFM_ABI_VERSION 3
 #define PSFM_MAX_SCALES 4
 #define PSFM_MAX_CTX 8
 
@@ -44,6 +44,11 @@ typedef enum psfm_status {
 typedef enum psfm_dtype { PSFM_F32 = 0, PSFM_BF16 = 1, PSFM_F64 = 2 } psfm_dtype;
 typedef enum psfm_padding { PSFM_PAD_ZEROS = 0, PSFM_PAD_BORDER = 1 } psfm_padding;
 typedef enum psfm_reduce { PSFM_REDUCE_MIN = 0, PSFM_REDUCE_MEAN = 1 } psfm_reduce;
+/* Camera model of the view synthesis.  PINHOLE: geometry/camera.py:15-190 (Camera).  FISHEYE: the fork's
+ * VADAS model, geometry/camera.py:194-394 (FisheyeCamera), as its warp_ref_image builds the cameras
+ * (losses/multiview_photometric_loss.py:131-195): K / ref_K then hold [B,11] rows
+ * (k0..k6, s, div, ux, uy) -- the 'distortion_coeffs' dict of datasets/ncdb_dataset.py:577-584. */
+typedef enum psfm_camera { PSFM_CAM_PINHOLE = 0, PSFM_CAM_FISHEYE = 1 } psfm_camera;
 
 /* Hyper-parameters and shapes of one loss evaluation.
  * Mirrors MultiViewPhotometricLoss.__init__ (losses/multiview_photometric_loss.py:92-118)
@@ -67,6 +72,7 @@ typedef struct psfm_loss_cfg {
   int32_t automask;               /* automask_loss                                            */
   int32_t premap;                 /* 0: inv_depths are inverse depths (upstream / north star) */
                                   /* 1: fork's sigmoid pre-map (:362-369)                     */
+  int32_t camera_model;           /* psfm_camera; FISHEYE: psfm_loss_forward_backward only    */
   double ssim_w;                  /* ssim_loss_weight                                         */
   double smooth_w;                /* smooth_loss_weight                                       */
   double C1, C2;                  /* SSIM constants                                           */
@@ -83,7 +89,7 @@ typedef struct psfm_loss_io {
   const void* inv_depth[PSFM_MAX_SCALES];           /* [B,1,Hs,Ws] real                              */
   const void* mask[PSFM_MAX_SCALES];                /* [B,1,Hs,Ws] img_dtype or NULL                 */
   const void* K;                                    /* [B,3,3] real, full-resolution intrinsics      */
-  const void* ref_K;                                /* [B,3,3] real                                  */
+  const void* ref_K;                                /* [B,3,3] real ([B,11] each for PSFM_CAM_FISHEYE) */
   const void* pose[PSFM_MAX_CTX];                   /* [B,4,4] real, Pose.mat of context j           */
   uint8_t* sel[PSFM_MAX_SCALES];                    /* [B,Hs,Ws] u8: arg-min candidate (fwd out, bwd in) */
   void* d_inv_depth[PSFM_MAX_SCALES];               /* [B,1,Hs,Ws] real (bwd out, overwritten)       */

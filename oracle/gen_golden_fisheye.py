@@ -122,7 +122,7 @@ def main():
     tiny = dict(B=2, H=24, W=40, C=2, kd=5, full=2)
     save('fisheye_tiny_U_zeros', run_case(pyramid=False, **tiny))
     save('fisheye_tiny_U_border', run_case(pyramid=False, padding_mode='border', **tiny))
-    save('fisheye_tiny_P_zeros', run_case(pyramid=True, **tiny))
+    save('fisheye_small_P_zeros', run_case(pyramid=True, **dict(tiny, H=32, W=64, kd=3)))     # smallest scale 4 x 8
     save('fisheye_tiny_U_mask', run_case(pyramid=False, with_mask=True, **dict(tiny, full=1)))
     save('fisheye_tiny_U_odd_C4', run_case(pyramid=False, **dict(tiny, H=23, W=37, C=4, full=1)))
     for pm in ('zeros', 'border'):

@@ -474,7 +474,7 @@ size_t loss_workspace_bytes(const psfm_loss_cfg* cfg) {
 
 void build_params(const psfm_loss_cfg* cfg, const psfm_loss_io* io, void* ws, LossParams& P) {
   P.B = cfg->B; P.C = cfg->C; P.n = cfg->n; P.H = cfg->H; P.W = cfg->W;
-  P.padding = cfg->padding; P.reduce_op = cfg->reduce_op; P.automask = cfg->automask; P.premap = cfg->premap;
+  P.padding = cfg->padding; P.reduce_op = cfg->reduce_op; P.automask = cfg->automask; P.premap = cfg->premap; P.camera = cfg->camera_model;
   const int ngroups = cfg->automask ? 2 * cfg->C : cfg->C;
   P.ncand = ngroups;    // thresholds are per candidate group
   P.ssim_w = cfg->ssim_w; P.C1 = cfg->C1; P.C2 = cfg->C2; P.clip_loss = cfg->clip_loss; P.smooth_w = cfg->smooth_w;

@@ -37,6 +37,7 @@ struct LossParams {
   int B, C, n;
   int H, W;                          // full resolution
   int padding, reduce_op, automask, premap;
+  int camera;                        // psfm_camera
   int ncand;                         // candidates per pixel (C or 2C; x3 when ssim_w == 0)
   double ssim_w, C1, C2, clip_loss, smooth_w;
   double premap_lo, premap_hi;

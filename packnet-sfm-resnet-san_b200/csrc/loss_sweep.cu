@@ -444,14 +444,16 @@ __device__ __forceinline__ double signed_by(double mag, double x) {
 #endif
 // VAR: 0 = plain, 1 = inverse depths upsampled on load (all scales of the set), 2 = rare settings (fork pre-map;
 // upsampling decided per scale at run time)
-template <typename real, int PAD, int VAR, int CT>
+// CAM: 0 = pinhole cameras (K, ref_K 3x3), 1 = fisheye (VADAS) cameras (geometry/camera.py:194-394): K, ref_K are
+// rows of 11 values (k0..k6, s, div, ux, uy)
+template <typename real, int PAD, int VAR, int CT, int CAM = 0>
 #ifdef PSFM_SWEEP_MAXREG
 __global__ void __maxnreg__(PSFM_SWEEP_MAXREG) sweep_kernel(const SweepParams SP) {
 #else
 __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) == 4) ? PSFM_SWEEP_MINB : 1) sweep_kernel(const SweepParams SP) {
 #endif
   typedef Real4<real> vec4;
-  constexpr int kRing = (PAD == PSFM_PAD_BORDER) ? 11 : 10;     // per-row values parked in shared memory
+  constexpr int kRing = CAM ? 15 : ((PAD == PSFM_PAD_BORDER) ? 11 : 10);     // per-row values parked in shared memory
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const LossParams& P = SP.P;
   const SweepSet& S = SP.set;
@@ -470,6 +472,7 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
   real* ring = (real*)smem_raw + (size_t)j * 4 * kRing * 32 + lane;        // [4 slots][kRing][32]
   real* photo_s = (real*)smem_raw + (size_t)C * 4 * kRing * 32;            // [2][C][32]
   real* dpart_s = photo_s + 2 * C * 32;                                    // [2][C][32]
+  real* fc = dpart_s + 2 * C * 32 + j * 24;                                // fisheye: [C][24] per-context constants
 
   const ScaleDesc& SD = P.sc[s];
   const vec4* ctxp = (const vec4*)S.ctxp[j] + (size_t)b * S.Hp * S.Wp;
@@ -488,7 +491,25 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
 
   // ---- per-thread geometry constants: p = (A0 + A1 v) D + m with A = ref_K R Kinv (u, v, 1) ---------
   real A0[3], A1[3], mt[3];
-  {
+  real fxd = real(0), fuy = real(0), fdiv = real(1);     // fisheye: x_dist of this column, uy and div of the target camera
+  if (CAM) {
+    // per-scale intrinsics as warp_ref_image builds them: only the principal point is rescaled
+    // (losses/multiview_photometric_loss.py:158-183)
+    const real sw = K.sf[s], sh = (real)((double)H / (double)P.H);
+    const real* ti = (const real*)P.K + (size_t)b * 11;
+    const real* ri = (const real*)P.refK + (size_t)b * 11;
+    const real* T = (const real*)P.pose[j] + (size_t)b * 16;
+    if (lane < 12) fc[lane] = T[lane];
+    else if (lane < 21) fc[lane] = ri[lane - 12];                       // k0..k6, s, div of the context camera
+    else if (lane == 21) fc[21] = (ri[9] + real(0.5)) * sw - real(0.5);
+    else if (lane == 22) fc[22] = (ri[10] + real(0.5)) * sh - real(0.5);
+    __syncwarp();
+    fxd = ((real)su - ((ti[9] + real(0.5)) * sw - real(0.5))) / ti[7];
+    fuy = (ti[10] + real(0.5)) * sh - real(0.5);
+    fdiv = ti[8];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) { A0[i] = real(0); A1[i] = real(0); mt[i] = real(0); }
+  } else {
     SweepCam<real> cam;
     sweep_cam<real>(cam, P, b, j, K.sf[s]);
     real M[9];
@@ -531,6 +552,7 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
 #pragma unroll
   for (int k = 0; k < 4 * kRing; ++k) ring[k * 32] = real(0);
   real S0a[3] = {real(0), real(0), real(0)}, Sva[3] = {real(0), real(0), real(0)}, S1a[3] = {real(0), real(0), real(0)};
+  real Sua[3] = {real(0), real(0), real(0)};                       // fisheye only
   real loss_acc = real(0), w_cur = real(0), w_old = real(0);
   real d0 = real(0), d1 = real(0), d2 = real(0), d3 = real(0);   // raw inverse depths of rows t, t-1, t-2, t-3
   real wy_prev = real(0);                                          // edge weight wy of row q - 1
@@ -546,6 +568,46 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
     if (premap) { real ch; dd = premap_fork<real>(draw, K.premap_lo, K.premap_hi, ch); }
     const real D = rrcp(rmax(dd, real(1e-6)));                    // utils/depth.py:120
     const real fv = (real)reflect1(row, H);
+    real* rs = ring + (row & 3) * kRing * 32;
+    if (CAM) {
+      const real eps = (real)2.220446049250313e-16;               // sys.float_info.epsilon (camera.py:287,355,373)
+      // FisheyeCamera.reconstruct, frame 'c' (camera.py:242-305): theta = r_d placeholder, ray = (tan(r_d) / r_d) (x_d, y_d), 1
+      const real yd = (fv - fuy) / fdiv;
+      const real rd = rroot(fxd * fxd + yd * yd);
+      const real sc = rtan(rd) / (rd < eps ? eps : rd);
+      const real rx = sc * fxd, ry = sc * yd;
+      // context camera frame (pose.py:80-86)
+      const real X0 = (fc[0] * rx + fc[1] * ry + fc[2]) * D + fc[3];
+      const real X1 = (fc[4] * rx + fc[5] * ry + fc[6]) * D + fc[7];
+      const real X2 = (fc[8] * rx + fc[9] * ry + fc[10]) * D + fc[11];
+      // FisheyeCamera.project, frame 'c' (camera.py:352-383)
+      const real iz = real(1) / rmax(X2, eps);
+      const real xn = X0 * iz, yn = X1 * iz;
+      const real r2 = xn * xn + yn * yn, r = rroot(r2);
+      const real th = ratan(r);
+      real poly = fc[18], dpoly = real(6) * fc[18];
+#pragma unroll
+      for (int i = 5; i >= 1; --i) { poly = poly * th + fc[12 + i]; dpoly = dpoly * th + (real)i * fc[12 + i]; }
+      poly = poly * th + fc[12];
+      const bool tiny = r < eps;
+      const real g = poly / (tiny ? eps : r);
+      const real gp = dpoly / (real(1) + r2);
+      const real h = tiny ? real(0) : (gp - g) / r2;              // (d g / d r) / r
+      const real ix = fc[19] * (g * xn) + fc[21], iy = fc[20] * (g * yn) + fc[22];
+      real mx, my;
+      sample4_issue<real, vec4, PAD>(ctxp, H, W, Wp, kPadLo, ix, iy, twx, twy, mx, my, tap);
+      // d (ix, iy) / d X, rows scaled by the border-clamp masks
+      const real hxy = h * xn * yn;
+      real a00 = fc[19] * (g + h * xn * xn), a01 = fc[19] * hxy, a10 = fc[20] * hxy, a11 = fc[20] * (g + h * yn * yn);
+      if (PAD == PSFM_PAD_BORDER) { a00 *= mx; a01 *= mx; a10 *= my; a11 *= my; }
+      const real zk = (X2 >= eps) ? -iz : real(0);
+      rs[6 * 32] = D;
+      rs[7 * 32] = rx;
+      rs[8 * 32] = ry;
+      rs[9 * 32] = a00 * iz; rs[10 * 32] = a01 * iz; rs[11 * 32] = (a00 * xn + a01 * yn) * zk;
+      rs[12 * 32] = a10 * iz; rs[13 * 32] = a11 * iz; rs[14 * 32] = (a10 * xn + a11 * yn) * zk;
+      return;
+    }
     const real p0 = (A0[0] + A1[0] * fv) * D + mt[0];
     const real p1 = (A0[1] + A1[1] * fv) * D + mt[1];
     const real p2 = (A0[2] + A1[2] * fv) * D + mt[2];
@@ -553,7 +615,6 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
     const real ix = p0 * iz, iy = p1 * iz;
     real mx, my;
     sample4_issue<real, vec4, PAD>(ctxp, H, W, Wp, kPadLo, ix, iy, twx, twy, mx, my, tap);
-    real* rs = ring + (row & 3) * kRing * 32;
     rs[6 * 32] = (p2 >= real(1e-5)) ? D : -D;                     // sign flags the clamp of p2
     rs[7 * 32] = ix;
     rs[8 * 32] = iy;
@@ -722,16 +783,33 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
       real giy = dlA.lo() * rq[3 * 32] + dlA.hi() * rq[4 * 32] + dlB * rq[5 * 32];
       gix = q_ok ? gix : real(0);
       giy = q_ok ? giy : real(0);
-      const real Ds = rq[6 * 32], ixq = rq[7 * 32], iyq = rq[8 * 32];
-      const real D = rabs(Ds);
-      const real dp0 = gix * rq[9 * 32], dp1 = giy * rq[(PAD == PSFM_PAD_BORDER ? 10 : 9) * 32];
-      const real dp2 = (Ds > real(0)) ? -(dp0 * ixq + dp1 * iyq) : real(0);
+      real D, dD, dp0, dp1, dp2;
       const real fq = (real)q;
-      const real dD = (A0[0] + A1[0] * fq) * dp0 + (A0[1] + A1[1] * fq) * dp1 + (A0[2] + A1[2] * fq) * dp2;
+      if (CAM) {
+        D = rq[6 * 32];
+        const real rx = rq[7 * 32], ry = rq[8 * 32];
+        dp0 = gix * rq[9 * 32] + giy * rq[12 * 32];
+        dp1 = gix * rq[10 * 32] + giy * rq[13 * 32];
+        dp2 = gix * rq[11 * 32] + giy * rq[14 * 32];
+        dD = (fc[0] * rx + fc[1] * ry + fc[2]) * dp0 + (fc[4] * rx + fc[5] * ry + fc[6]) * dp1 +
+             (fc[8] * rx + fc[9] * ry + fc[10]) * dp2;
+        const real e0 = dp0 * D, e1 = dp1 * D, e2 = dp2 * D;
+        Sua[0] += e0 * rx; Sua[1] += e1 * rx; Sua[2] += e2 * rx;
+        Sva[0] += e0 * ry; Sva[1] += e1 * ry; Sva[2] += e2 * ry;
+        S0a[0] += e0; S0a[1] += e1; S0a[2] += e2;
+        S1a[0] += dp0; S1a[1] += dp1; S1a[2] += dp2;
+      } else {
+        const real Ds = rq[6 * 32], ixq = rq[7 * 32], iyq = rq[8 * 32];
+        D = rabs(Ds);
+        dp0 = gix * rq[9 * 32];
+        dp1 = giy * rq[(PAD == PSFM_PAD_BORDER ? 10 : 9) * 32];
+        dp2 = (Ds > real(0)) ? -(dp0 * ixq + dp1 * iyq) : real(0);
+        dD = (A0[0] + A1[0] * fq) * dp0 + (A0[1] + A1[1] * fq) * dp1 + (A0[2] + A1[2] * fq) * dp2;
+      }
       real chain = real(1), dd = d2;
       if (premap) dd = premap_fork<real>(d2, K.premap_lo, K.premap_hi, chain);
       const real dphoto = (q_ok && dd >= real(1e-6)) ? -(D * D) * dD * chain : real(0);
-      {
+      if (!CAM) {
         const real e0 = dp0 * D, e1 = dp1 * D, e2 = dp2 * D;
         S0a[0] += e0; S0a[1] += e1; S0a[2] += e2;
         Sva[0] += e0 * fq; Sva[1] += e1 * fq; Sva[2] += e2 * fq;
@@ -775,7 +853,20 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
   }
 
   // ---- epilogue: pose partials (converted from the (u, v, 1) basis) and the loss partial -----------
-  {
+  if (CAM) {
+    // d loss / d [R|t] directly: rows i, columns (ray x, ray y, 1 | translation)
+    real out = real(0);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const real g0 = warp_allsum<real>(Sua[i]), g1 = warp_allsum<real>(Sva[i]), g2 = warp_allsum<real>(S0a[i]),
+                 g3 = warp_allsum<real>(S1a[i]);
+      if (lane == i * 4) out = g0;
+      if (lane == i * 4 + 1) out = g1;
+      if (lane == i * 4 + 2) out = g2;
+      if (lane == i * 4 + 3) out = g3;
+    }
+    if (lane < 12) ((real*)SP.pose_part[s])[(((size_t)b * nunits + unit) * C + j) * 12 + lane] = out;
+  } else {
     SweepCam<real> cam;
     sweep_cam<real>(cam, P, b, j, K.sf[s]);
     const real fu = (real)su;
@@ -798,9 +889,9 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
       if (lane == e) out = v;
     }
     if (lane < 12) ((real*)SP.pose_part[s])[(((size_t)b * nunits + unit) * C + j) * 12 + lane] = out;
-    const real lsum = warp_allsum<real>(loss_acc);
-    if (j == 0 && lane == 0) SP.loss_part[s][(size_t)b * nunits + unit] = (double)lsum;
   }
+  const real lsum = warp_allsum<real>(loss_acc);
+  if (j == 0 && lane == 0) SP.loss_part[s][(size_t)b * nunits + unit] = (double)lsum;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1068,9 +1159,9 @@ static void fill_consts(SweepConsts<real>& c, const LossParams& P, int s0) {
   }
 }
 
-template <typename real, int PAD, int VAR, int CT>
+template <typename real, int PAD, int VAR, int CT, int CAM = 0>
 static cudaError_t launch_sweep_ct(const SweepParams& SP, dim3 grid, int threads, size_t smem, cudaStream_t st) {
-  auto kern = sweep_kernel<real, PAD, VAR, CT>;
+  auto kern = sweep_kernel<real, PAD, VAR, CT, CAM>;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
@@ -1137,8 +1228,9 @@ static cudaError_t run_sweep(const psfm_loss_cfg* cfg, const psfm_loss_io* io, v
       }
       if (cfg->smooth_w > 0.0) stats_kernel<real><<<dim3(cfg->B, S.ns), 128, 0, st>>>(SP);
     }
-    const int ring = cfg->padding == PSFM_PAD_BORDER ? 11 : 10;
-    const size_t smem = ((size_t)cfg->C * 4 * ring * 32 + (size_t)4 * cfg->C * 32) * sizeof(real);
+    const bool fisheye = cfg->camera_model == PSFM_CAM_FISHEYE;
+    const int ring = fisheye ? 15 : (cfg->padding == PSFM_PAD_BORDER ? 11 : 10);
+    const size_t smem = ((size_t)cfg->C * 4 * ring * 32 + (size_t)4 * cfg->C * 32 + (fisheye ? 24 * cfg->C : 0)) * sizeof(real);
     const dim3 grid(S.nstrips * S.nchunks, S.ns, cfg->B);
     const int threads = 32 * cfg->C;
     ProfScope ps(st, kTagFused, 1);
@@ -1149,7 +1241,11 @@ static cudaError_t run_sweep(const psfm_loss_cfg* cfg, const psfm_loss_io* io, v
 #define PSFM_SWEEP(PADV) (var == 2 ? launch_sweep<real, PADV, 2>(SP, grid, threads, smem, st) \
                           : var == 1 ? launch_sweep<real, PADV, 1>(SP, grid, threads, smem, st) \
                                      : launch_sweep<real, PADV, 0>(SP, grid, threads, smem, st))
-    e = cfg->padding == PSFM_PAD_BORDER ? PSFM_SWEEP(PSFM_PAD_BORDER) : PSFM_SWEEP(PSFM_PAD_ZEROS);
+    if (fisheye)   // one run-time-generic instantiation per padding mode (any C, pre-map, upsampled inverse depths)
+      e = cfg->padding == PSFM_PAD_BORDER ? launch_sweep_ct<real, PSFM_PAD_BORDER, 2, 0, 1>(SP, grid, threads, smem, st)
+                                          : launch_sweep_ct<real, PSFM_PAD_ZEROS, 2, 0, 1>(SP, grid, threads, smem, st);
+    else
+      e = cfg->padding == PSFM_PAD_BORDER ? PSFM_SWEEP(PSFM_PAD_BORDER) : PSFM_SWEEP(PSFM_PAD_ZEROS);
 #undef PSFM_SWEEP
     if (e != cudaSuccess) return e;
   }

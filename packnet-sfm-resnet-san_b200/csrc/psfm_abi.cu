@@ -101,6 +101,15 @@ static int check_cfg(const psfm_loss_cfg* c) {
       return psfm_fail(PSFM_ERR_INVALID, "in-kernel upsampling of the inverse depths is implemented by the sweep kernels only "
                        "(photometric_reduce_op='min', ssim_loss_weight > 0, clip_loss = 0); upsample before the loss otherwise");
   }
+  if (c->camera_model != PSFM_CAM_PINHOLE && c->camera_model != PSFM_CAM_FISHEYE)
+    return psfm_fail(PSFM_ERR_INVALID, "camera_model must be pinhole|fisheye (got %d)", c->camera_model);
+  if (c->camera_model == PSFM_CAM_FISHEYE) {
+    bool ok = c->reduce_op == PSFM_REDUCE_MIN && c->ssim_w > 0.0 && !(c->clip_loss > 0.0) && c->C <= 8;
+    for (int s = 0; s < c->n; ++s) ok = ok && c->Hs[s] >= 4 && c->Ws[s] >= 4;
+    if (!ok)
+      return psfm_fail(PSFM_ERR_INVALID, "the fisheye camera model is implemented by the sweep kernels only "
+                       "(photometric_reduce_op='min', ssim_loss_weight > 0, clip_loss = 0, scales of at least 4x4)");
+  }
   const int groups = (c->automask ? 2 : 1) * c->C * (c->ssim_w > 0.0 ? 1 : 3);
   if (groups > 254) return psfm_fail(PSFM_ERR_INVALID, "too many candidates (%d)", groups);
   return PSFM_OK;
@@ -165,6 +174,7 @@ int psfm_loss_forward(const psfm_loss_cfg* cfg, const psfm_loss_io* io, void* wo
     if (cfg->Hd[s] > 0 && (cfg->Hd[s] != cfg->Hs[s] || cfg->Wd[s] != cfg->Ws[s]))
       return psfm_fail(PSFM_ERR_INVALID, "in-kernel upsampling: use psfm_loss_forward_backward");
   }
+  if (cfg->camera_model == PSFM_CAM_FISHEYE) return psfm_fail(PSFM_ERR_INVALID, "fisheye cameras: use psfm_loss_forward_backward");
   if (!loss_out || !workspace) return psfm_fail(PSFM_ERR_INVALID, "loss_out / workspace is NULL");
   if (workspace_bytes < psfm::loss_workspace_bytes(cfg))
     return psfm_fail(PSFM_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes, psfm::loss_workspace_bytes(cfg));
@@ -181,6 +191,7 @@ int psfm_loss_backward(const psfm_loss_cfg* cfg, const psfm_loss_io* io, void* w
     if (cfg->Hd[s] > 0 && (cfg->Hd[s] != cfg->Hs[s] || cfg->Wd[s] != cfg->Ws[s]))
       return psfm_fail(PSFM_ERR_INVALID, "in-kernel upsampling: use psfm_loss_forward_backward");
   }
+  if (cfg->camera_model == PSFM_CAM_FISHEYE) return psfm_fail(PSFM_ERR_INVALID, "fisheye cameras: use psfm_loss_forward_backward");
   if (!grad_loss || !workspace) return psfm_fail(PSFM_ERR_INVALID, "grad_loss / workspace is NULL");
   if (workspace_bytes < psfm::loss_workspace_bytes(cfg))
     return psfm_fail(PSFM_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes, psfm::loss_workspace_bytes(cfg));

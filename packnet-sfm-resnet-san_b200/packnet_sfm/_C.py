@@ -16,6 +16,7 @@ MAX_CTX = 8
 F32, BF16, F64 = 0, 1, 2
 PAD = {'zeros': 0, 'border': 1}
 REDUCE = {'min': 0, 'mean': 1}
+CAM_PINHOLE, CAM_FISHEYE = 0, 1
 
 EXPORTS = ('psfm_abi_version', 'psfm_last_error', 'psfm_launch_count', 'psfm_profile_enable', 'psfm_profile_read',
            'psfm_loss_workspace_bytes', 'psfm_loss_forward',
@@ -34,7 +35,7 @@ class LossCfg(C.Structure):
                 ('Hs', C.c_int32 * MAX_SCALES), ('Ws', C.c_int32 * MAX_SCALES),
                 ('Hd', C.c_int32 * MAX_SCALES), ('Wd', C.c_int32 * MAX_SCALES),
                 ('img_dtype', C.c_int32), ('real_dtype', C.c_int32), ('padding', C.c_int32),
-                ('reduce_op', C.c_int32), ('automask', C.c_int32), ('premap', C.c_int32),
+                ('reduce_op', C.c_int32), ('automask', C.c_int32), ('premap', C.c_int32), ('camera_model', C.c_int32),
                 ('ssim_w', C.c_double), ('smooth_w', C.c_double), ('C1', C.c_double), ('C2', C.c_double),
                 ('clip_loss', C.c_double), ('min_depth', C.c_double), ('max_depth', C.c_double)]
 
@@ -108,7 +109,7 @@ def _load():
         fn = getattr(lib, name)
         fn.restype = i
         fn.argtypes = args
-    if lib.psfm_abi_version() != 2:
+    if lib.psfm_abi_version() != 3:
         raise ImportError('libpsfm_b200.so ABI version mismatch: %d' % lib.psfm_abi_version())
     return lib
 

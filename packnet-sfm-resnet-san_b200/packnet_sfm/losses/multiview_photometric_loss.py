@@ -121,13 +121,14 @@ class MultiViewPhotometricLoss(LossBase):
         """Photometric + smoothness loss (reference :331-410).
 
         image [B,3,H,W]; context: list of [B,3,H,W]; inv_depths: list of [B,1,Hs,Ws]; K, ref_K
-        [B,3,3] (the fork's keyword names `intrinsics` / `ref_intrinsics` are accepted);
+        [B,3,3] (the fork's keyword names `intrinsics` / `ref_intrinsics` are accepted), or the fork's fisheye
+        intrinsics dicts {'k': [B,7], 's', 'div', 'ux', 'uy': [B]} (reference :131-195 with
+        geometry/camera.py:194-394; the pose is applied to the [B,3,H,W] points, which the reference's
+        `frame='w'` branches fail to do);
         poses: list of Pose (target -> context).  Returns {'loss': [1], 'metrics': {...}}.
         """
         K = intrinsics if K is None else K
         ref_K = ref_intrinsics if ref_K is None else ref_K
-        if isinstance(K, dict) or isinstance(ref_K, dict):
-            raise NotImplementedError('fisheye (dict) intrinsics are not implemented; pass [B,3,3] pinhole K')
         self.n = self.progressive_scaling(progress)
         mats = [p.mat if isinstance(p, Pose) else p for p in poses]
         out = ops.photometric_loss(self._hyper(), image, list(context), list(inv_depths[:self.n]), K, ref_K, mats,

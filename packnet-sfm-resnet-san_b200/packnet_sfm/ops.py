@@ -21,7 +21,35 @@ from .block_ops import (abs_mean_op, normalize_op, photometric_map_op, project_o
 DEFAULT_MODE = os.environ.get('PSFM_LOSS_MODE', 'fused')
 
 
+FISHEYE_KEYS = ('k', 's', 'div', 'ux', 'uy')
+
+
+def pack_fisheye(intr, B, dtype, device=None):
+    """The fork's fisheye intrinsics dict (k [B,7], s, div, ux, uy [B]; datasets/ncdb_dataset.py:577-584) ->
+    [B,11] rows (k0..k6, s, div, ux, uy), the layout of PSFM_CAM_FISHEYE in include/psfm.h."""
+    missing = [n for n in FISHEYE_KEYS if n not in intr]
+    if missing:
+        raise KeyError('fisheye intrinsics need the keys %s (missing %s)' % (FISHEYE_KEYS, missing))
+    k = torch.as_tensor(intr['k'])
+    device = k.device if device is None else device
+    k = k.to(device=device, dtype=dtype).reshape(-1, 7)
+    cols = [k.expand(B, 7)] + [torch.as_tensor(intr[n]).to(device=device, dtype=dtype).reshape(-1, 1).expand(B, 1)
+                                for n in FISHEYE_KEYS[1:]]
+    return torch.cat(cols, 1).contiguous()
+
+
+def _is_fisheye(K):
+    """Fisheye intrinsics: the fork's dict, or its packed [B,11] form (pack_fisheye)."""
+    return isinstance(K, dict) or (torch.is_tensor(K) and K.dim() == 2 and K.shape[1] == 11)
+
+
 def _as_batched_K(K, B, dtype):
+    if isinstance(K, dict):
+        return pack_fisheye(K, B, dtype)
+    if _is_fisheye(K):
+        if K.shape[0] != B:
+            raise ValueError('packed fisheye intrinsics must be [B,11], got %s' % (tuple(K.shape),))
+        return K.to(dtype).contiguous()
     if K.dim() == 2:
         K = K.unsqueeze(0).expand(B, 3, 3)
     if tuple(K.shape) != (B, 3, 3):
@@ -59,7 +87,9 @@ class _LossPlan:
             raise ValueError('between 1 and %d context frames are supported, got %d' % (_C.MAX_CTX, Cn))
         if len(pose_mats) != Cn:
             raise ValueError('need one pose per context frame')
-        _C.require_cuda(image, K, ref_K, mask, *context, *inv_depths, *pose_mats)
+        _C.require_cuda(image, mask, *context, *inv_depths, *pose_mats)
+        for Kx in (K, ref_K):
+            _C.require_cuda(*(list(Kx.values()) if isinstance(Kx, dict) else [Kx]))
         real = inv_depths[0].dtype
         if real not in (torch.float32, torch.float64):
             raise ValueError('inverse depths must be float32 (or float64 for the math-parity build)')
@@ -114,9 +144,13 @@ class _LossPlan:
             io.mask[s] = 0 if mask_s is None else mask_s.data_ptr()
             for j in range(Cn):
                 io.ctx[s][j] = ctx_s[j].data_ptr()
+        if _is_fisheye(K) != _is_fisheye(ref_K):
+            raise ValueError('K and ref_K must both be pinhole matrices or both be fisheye intrinsics')
+        cfg.camera_model = _C.CAM_FISHEYE if _is_fisheye(K) else _C.CAM_PINHOLE
         self.K = _as_batched_K(K, B, real)
         self.ref_K = _as_batched_K(ref_K, B, real)
         io.K, io.ref_K = self.K.data_ptr(), self.ref_K.data_ptr()
+        self.fisheye = _is_fisheye(K)
         self.pose = []
         for j, m in enumerate(pose_mats):
             if tuple(m.shape) != (B, 4, 4):
@@ -163,9 +197,9 @@ class _PhotometricLossFn(torch.autograd.Function):
         need_grad = any(t.requires_grad for t in tensors[Cn:])
         st = _C.stream_ptr(plan.dev)
         with torch.cuda.device(plan.dev):
-            if plan.upsampled and mode != 'fused':
-                raise NotImplementedError("upsample_depth_maps needs kernel_mode='fused'")
-            if (need_grad or plan.upsampled) and mode == 'fused':
+            if (plan.upsampled or plan.fisheye) and mode != 'fused':
+                raise NotImplementedError("upsample_depth_maps / fisheye cameras need kernel_mode='fused'")
+            if (need_grad or plan.upsampled or plan.fisheye) and mode == 'fused':
                 plan.alloc_grads()
                 _C.check(_C.lib.psfm_loss_forward_backward(*plan.args(), _C.ptr(plan.out), st))
             else:

@@ -45,7 +45,7 @@ for _B, _H, _W in ((2, 64, 160), (1, 192, 640)):
 CASES.update({
     'fisheye_tiny_U_zeros': (dict(_T, pyramid=False), {}, dict(fisheye=True)),
     'fisheye_tiny_U_border': (dict(_T, pyramid=False), dict(padding_mode='border'), dict(fisheye=True)),
-    'fisheye_tiny_P_zeros': (dict(_T, pyramid=True), {}, dict(fisheye=True)),
+    'fisheye_small_P_zeros': (dict(_T, H=32, W=64, kd=3, pyramid=True), {}, dict(fisheye=True)),
     'fisheye_tiny_U_mask': (dict(_T, pyramid=False), {}, dict(fisheye=True, with_mask=True)),
     'fisheye_tiny_U_odd_C4': (dict(_T, H=23, W=37, C=4, pyramid=False), {}, dict(fisheye=True)),
     'fisheye_B2_64x160_C2_U_zeros': (dict(B=2, H=64, W=160, C=2, pyramid=False), {}, dict(fisheye=True)),

@@ -39,8 +39,8 @@ def cuda_run(name, dtype=torch.float64, mode='split', img_dtype=None, inputs=Non
         hp.update(sigmoid_premap=True, min_depth=inp['fork'][0], max_depth=inp['fork'][1])
     L = MultiViewPhotometricLoss(kernel_mode=mode, **hp)
     mask = None if inp['mask'] is None else inp['mask'].to(dev).to(idt)
-    out = L(inp['image'].to(dev).to(idt), [c.to(dev).to(idt) for c in inp['context']], invd, inp['K'].to(dev),
-            inp['K'].to(dev), poses, mask=mask)
+    K = {k: v.to(dev) for k, v in inp['K'].items()} if isinstance(inp['K'], dict) else inp['K'].to(dev)
+    out = L(inp['image'].to(dev).to(idt), [c.to(dev).to(idt) for c in inp['context']], invd, K, K, poses, mask=mask)
     out['loss'].backward()
     torch.cuda.synchronize()
     n = L.n

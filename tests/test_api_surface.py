@@ -85,7 +85,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), 'libpsfm_b200.so does not export %s' % n
     assert sorted(_C.EXPORTS) == names, 'ctypes table and include/psfm.h disagree'
-    assert lib.psfm_abi_version() == 2
+    assert lib.psfm_abi_version() == 3
 
 
 def test_abi_argument_validation_without_gpu():
@@ -121,8 +121,17 @@ def test_python_surface_refuses_cpu_tensors_and_bad_settings():
     img = torch.rand(1, 3, 8, 8)
     with pytest.raises(RuntimeError, match='no CPU fallback'):
         L(img, [img], [torch.rand(1, 1, 8, 8)], torch.eye(3)[None], torch.eye(3)[None], [Pose.identity(1)])
-    with pytest.raises(NotImplementedError, match='fisheye'):
-        L(img, [img], [torch.rand(1, 1, 8, 8)], {'k': None}, {'k': None}, [Pose.identity(1)])
+    # the fork's fisheye intrinsics dicts take the same CUDA-only path
+    fe = {'k': torch.zeros(1, 7), 's': torch.ones(1), 'div': torch.ones(1), 'ux': torch.ones(1), 'uy': torch.ones(1)}
+    with pytest.raises(RuntimeError, match='no CPU fallback'):
+        L(img, [img], [torch.rand(1, 1, 8, 8)], fe, fe, [Pose.identity(1)])
+    from packnet_sfm.ops import pack_fisheye
+    packed = pack_fisheye({'k': torch.arange(7.)[None], 's': torch.tensor([7.]), 'div': torch.tensor([8.]),
+                           'ux': torch.tensor([9.]), 'uy': torch.tensor([10.])}, 2, torch.float64)
+    assert packed.shape == (2, 11) and packed.dtype == torch.float64
+    assert packed[1].tolist() == [float(i) for i in range(11)]       # k0..k6, s, div, ux, uy (include/psfm.h)
+    with pytest.raises(KeyError, match='fisheye'):
+        pack_fisheye({'k': torch.zeros(1, 7)}, 1, torch.float32)
     with pytest.raises(NotImplementedError, match='Unknown photometric_reduce_op'):
         MultiViewPhotometricLoss(photometric_reduce_op='median').reduce_photometric_loss([[img]])
     with pytest.raises(AssertionError):
