@@ -46,6 +46,7 @@ struct SweepSet {                    // scales of equal resolution sharing the s
   void* rb;                          // real4 [B][H][W]: mean(y) x3, min identity photometric value (automask)
   void* rc;                          // real4 [B][H][W]: E[y^2]-mean(y)^2+C2 x3, candidate index of that min
   void* wxy;                         // real [B][H][W][2]: exp(-mean|dx I|), exp(-mean|dy I|)
+  void* ray;                         // real [B][H][W][2]: fisheye only, x and y of the pixel's viewing ray (z = 1)
   void* ctxp[PSFM_MAX_CTX];          // real4 [B][Hp][Wp]: context image (r, g, b, 0), zero border
 };
 
@@ -393,6 +394,34 @@ __global__ void __launch_bounds__(128) stats_kernel(const SweepParams SP) {
 }
 
 // ------------------------------------------------------------------------------------------
+// fisheye ray kernel: grid (ceil(H W / 256), B).  FisheyeCamera.reconstruct, frame 'c' (geometry/camera.py:242-305) up
+// to the depth factor: x_d = (u - ux) / s, y_d = (v - uy) / div, theta = r_d (the reference's placeholder inverse of the
+// distortion polynomial), ray = (tan(r_d) / r_d) (x_d, y_d), 1.  Depth-independent, shared by the scales of a set and
+// by all contexts, so it is evaluated once per pixel here instead of per (scale, context) in the sweep.
+// ------------------------------------------------------------------------------------------
+template <typename real>
+__global__ void __launch_bounds__(256) fisheye_ray_kernel(const SweepParams SP) {
+  const LossParams& P = SP.P;
+  const SweepSet& S = SP.set;
+  const int b = blockIdx.y, H = S.H, W = S.W;
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= H * W) return;
+  const int v = i / W, u = i - v * W;
+  const real eps = (real)2.220446049250313e-16;                 // sys.float_info.epsilon (camera.py:287)
+  // per-scale intrinsics as warp_ref_image builds them: only the principal point is rescaled
+  // (losses/multiview_photometric_loss.py:158-183)
+  const real sw = (real)P.sc[S.scale[0]].sf, sh = (real)((double)H / (double)P.H);
+  const real* ti = (const real*)P.K + (size_t)b * 11;
+  const real xd = ((real)u - ((ti[9] + real(0.5)) * sw - real(0.5))) / ti[7];
+  const real yd = ((real)v - ((ti[10] + real(0.5)) * sh - real(0.5))) / ti[8];
+  const real rd = rroot(xd * xd + yd * yd);
+  const real sc = rtan(rd) / (rd < eps ? eps : rd);
+  real* out = (real*)S.ray + ((size_t)b * H * W + i) * 2;
+  out[0] = sc * xd;
+  out[1] = sc * yd;
+}
+
+// ------------------------------------------------------------------------------------------
 // sweep kernel: grid (nstrips * nchunks, ns, B), 32 * C threads (warp j = context j).
 // Lane l is column c0 - 2 + l (2 halo columns per side: SSIM needs +-1, its adjoint +-1 more).
 // Step t finishes the gather of row t (issued one step earlier), starts the gather of row t + 1,
@@ -491,12 +520,12 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
 
   // ---- per-thread geometry constants: p = (A0 + A1 v) D + m with A = ref_K R Kinv (u, v, 1) ---------
   real A0[3], A1[3], mt[3];
-  real fxd = real(0), fuy = real(0), fdiv = real(1);     // fisheye: x_dist of this column, uy and div of the target camera
+  const real* rayp = (const real*)S.ray + (size_t)b * plane * 2;   // fisheye: rays of the target camera (fisheye_ray_kernel)
+  real rxc = real(0), ryc = real(0), rxn = real(0), ryn = real(0);  // ray of the row being started / prefetched
   if (CAM) {
-    // per-scale intrinsics as warp_ref_image builds them: only the principal point is rescaled
+    // per-scale intrinsics of the context camera as warp_ref_image builds them: only the principal point is rescaled
     // (losses/multiview_photometric_loss.py:158-183)
     const real sw = K.sf[s], sh = (real)((double)H / (double)P.H);
-    const real* ti = (const real*)P.K + (size_t)b * 11;
     const real* ri = (const real*)P.refK + (size_t)b * 11;
     const real* T = (const real*)P.pose[j] + (size_t)b * 16;
     if (lane < 12) fc[lane] = T[lane];
@@ -504,9 +533,6 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
     else if (lane == 21) fc[21] = (ri[9] + real(0.5)) * sw - real(0.5);
     else if (lane == 22) fc[22] = (ri[10] + real(0.5)) * sh - real(0.5);
     __syncwarp();
-    fxd = ((real)su - ((ti[9] + real(0.5)) * sw - real(0.5))) / ti[7];
-    fuy = (ti[10] + real(0.5)) * sh - real(0.5);
-    fdiv = ti[8];
 #pragma unroll
     for (int i = 0; i < 3; ++i) { A0[i] = real(0); A1[i] = real(0); mt[i] = real(0); }
   } else {
@@ -571,17 +597,13 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
     real* rs = ring + (row & 3) * kRing * 32;
     if (CAM) {
       const real eps = (real)2.220446049250313e-16;               // sys.float_info.epsilon (camera.py:287,355,373)
-      // FisheyeCamera.reconstruct, frame 'c' (camera.py:242-305): theta = r_d placeholder, ray = (tan(r_d) / r_d) (x_d, y_d), 1
-      const real yd = (fv - fuy) / fdiv;
-      const real rd = rroot(fxd * fxd + yd * yd);
-      const real sc = rtan(rd) / (rd < eps ? eps : rd);
-      const real rx = sc * fxd, ry = sc * yd;
+      const real rx = rxc, ry = ryc;                               // FisheyeCamera.reconstruct: fisheye_ray_kernel
       // context camera frame (pose.py:80-86)
       const real X0 = (fc[0] * rx + fc[1] * ry + fc[2]) * D + fc[3];
       const real X1 = (fc[4] * rx + fc[5] * ry + fc[6]) * D + fc[7];
       const real X2 = (fc[8] * rx + fc[9] * ry + fc[10]) * D + fc[11];
       // FisheyeCamera.project, frame 'c' (camera.py:352-383)
-      const real iz = real(1) / rmax(X2, eps);
+      const real iz = rrcp(rmax(X2, eps));
       const real xn = X0 * iz, yn = X1 * iz;
       const real r2 = xn * xn + yn * yn, r = rroot(r2);
       const real th = ratan(r);
@@ -590,9 +612,10 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
       for (int i = 5; i >= 1; --i) { poly = poly * th + fc[12 + i]; dpoly = dpoly * th + (real)i * fc[12 + i]; }
       poly = poly * th + fc[12];
       const bool tiny = r < eps;
-      const real g = poly / (tiny ? eps : r);
-      const real gp = dpoly / (real(1) + r2);
-      const real h = tiny ? real(0) : (gp - g) / r2;              // (d g / d r) / r
+      const real ir = rrcp(tiny ? eps : r);
+      const real g = poly * ir;
+      const real gp = dpoly * rrcp(real(1) + r2);
+      const real h = tiny ? real(0) : (gp - g) * ir * ir;         // (d g / d r) / r
       const real ix = fc[19] * (g * xn) + fc[21], iy = fc[20] * (g * yn) + fc[22];
       real mx, my;
       sample4_issue<real, vec4, PAD>(ctxp, H, W, Wp, kPadLo, ix, iy, twx, twy, mx, my, tap);
@@ -651,6 +674,10 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
   if (j == 0 && smooth) load_pair(wxy + (min(max(r0 - 4, 0), H - 1) * W + su) * 2, wxn, wyn);
   real dnx = __ldg(invd + dofs(r0 - 2));
   real dpre = __ldg(invd + dofs(r0 - 1));
+  if (CAM) {
+    load_pair(rayp + (reflect1(r0 - 2, H) * W + su) * 2, rxc, ryc);
+    load_pair(rayp + (reflect1(r0 - 1, H) * W + su) * 2, rxn, ryn);
+  }
   {
     ran = ld4(ra + reflect1(r0 - 2, H) * W + su);
     const int orec = min(max(r0 - 3, 0), H - 1) * W + su;
@@ -688,6 +715,7 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
       d0 = dnx;
       dnx = dpre;
       wxq = wxn; wyq = wyn;
+      if (CAM) { rxc = rxn; ryc = ryn; }
     }
     // ---------------- prefetch of the next steps' operands, gather of row t + 1 ----------------------------
     {
@@ -697,6 +725,7 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
       rbn = ld4(rb + orec);
       rcn = ld4(rcp + orec);
       if (j == 0 && smooth) load_pair(wxy + (min(max(q + 1, 0), H - 1) * W + su) * 2, wxn, wyn);
+      if (CAM) load_pair(rayp + (reflect1(t + 2, H) * W + su) * 2, rxn, ryn);
       start_row(t + 1, dnx);
     }
     // ---------------- horizontal window sums of row t ------------------------------------------------------
@@ -1029,7 +1058,7 @@ bool stream_eligible(const psfm_loss_cfg* cfg) {
 struct SweepPlan {
   int nsets;
   SweepSet sets[PSFM_MAX_SCALES];
-  size_t off_rec[PSFM_MAX_SCALES], off_wxy[PSFM_MAX_SCALES], off_ctxp[PSFM_MAX_SCALES], off_dfull[PSFM_MAX_SCALES];                                         // per scale (a set uses its first scale's)
+  size_t off_rec[PSFM_MAX_SCALES], off_wxy[PSFM_MAX_SCALES], off_ctxp[PSFM_MAX_SCALES], off_dfull[PSFM_MAX_SCALES], off_ray[PSFM_MAX_SCALES];                                         // per scale (a set uses its first scale's)
   size_t off_prep[PSFM_MAX_SCALES], off_stats[PSFM_MAX_SCALES], off_loss[PSFM_MAX_SCALES],
       off_pose[PSFM_MAX_SCALES];                                          // per scale
   int nunits[PSFM_MAX_SCALES];
@@ -1122,6 +1151,7 @@ static void make_plan(const psfm_loss_cfg* cfg, const psfm_loss_io* io, SweepPla
     pl.off_rec[s] = off;   off = al(off + px * 12 * rs);               // three real4 planes
     pl.off_ctxp[s] = off;  off = al(off + (size_t)cfg->C * cfg->B * (Hs + kPadLo + kPadHi) * (Ws + kPadLo + kPadHi) * 4 * rs);
     pl.off_wxy[s] = off;   off = al(off + px * 2 * rs);
+    pl.off_ray[s] = off;   if (cfg->camera_model == PSFM_CAM_FISHEYE) off = al(off + px * 2 * rs);
     const bool ups = cfg->Hd[s] > 0 && (cfg->Hd[s] != Hs || cfg->Wd[s] != Ws);
     pl.off_dfull[s] = off; if (ups) off = al(off + px * rs);            // full-resolution d inv_depth before pooling
     pl.off_prep[s] = off;  off = al(off + (size_t)cfg->B * pworst * kPrepVals * sizeof(double));
@@ -1208,13 +1238,14 @@ static cudaError_t run_sweep(const psfm_loss_cfg* cfg, const psfm_loss_io* io, v
       for (int j = 0; j < PSFM_MAX_CTX; ++j) SP.set.ctxp[j] = j < cfg->C ? w + pl.off_ctxp[s0] + j * cpx : nullptr;
     }
     SP.set.wxy = w + pl.off_wxy[s0];
+    SP.set.ray = w + pl.off_ray[s0];
     fill_consts(SP.cf, SP.P, s0);
     fill_consts(SP.cd, SP.P, s0);
     const SweepSet& S = SP.set;
     {
       int npass = 0;
       for (int j0 = 0; j0 < cfg->C; j0 += (cfg->C - j0 >= 4 ? 4 : (cfg->C - j0 >= 2 ? 2 : 1))) ++npass;
-      ProfScope ps(st, kTagFwd, npass + (cfg->smooth_w > 0.0 ? 1 : 0));
+      ProfScope ps(st, kTagFwd, npass + (cfg->smooth_w > 0.0 ? 1 : 0) + (cfg->camera_model == PSFM_CAM_FISHEYE ? 1 : 0));
       for (int j0 = 0; j0 < cfg->C;) {
         const int ct = cfg->C - j0 >= 4 ? 4 : (cfg->C - j0 >= 2 ? 2 : 1);
         const dim3 pgrid(cdiv(S.pstrips * S.pchunks, kPrepWarps) + cdiv(S.Hp * ct, kPrepWarps), cfg->B);
@@ -1227,6 +1258,8 @@ static cudaError_t run_sweep(const psfm_loss_cfg* cfg, const psfm_loss_io* io, v
         j0 += ct;
       }
       if (cfg->smooth_w > 0.0) stats_kernel<real><<<dim3(cfg->B, S.ns), 128, 0, st>>>(SP);
+      if (cfg->camera_model == PSFM_CAM_FISHEYE)
+        fisheye_ray_kernel<real><<<dim3(cdiv(S.H * S.W, 256), cfg->B), 256, 0, st>>>(SP);
     }
     const bool fisheye = cfg->camera_model == PSFM_CAM_FISHEYE;
     const int ring = fisheye ? 15 : (cfg->padding == PSFM_PAD_BORDER ? 11 : 10);
@@ -1241,9 +1274,21 @@ static cudaError_t run_sweep(const psfm_loss_cfg* cfg, const psfm_loss_io* io, v
 #define PSFM_SWEEP(PADV) (var == 2 ? launch_sweep<real, PADV, 2>(SP, grid, threads, smem, st) \
                           : var == 1 ? launch_sweep<real, PADV, 1>(SP, grid, threads, smem, st) \
                                      : launch_sweep<real, PADV, 0>(SP, grid, threads, smem, st))
-    if (fisheye)   // one run-time-generic instantiation per padding mode (any C, pre-map, upsampled inverse depths)
-      e = cfg->padding == PSFM_PAD_BORDER ? launch_sweep_ct<real, PSFM_PAD_BORDER, 2, 0, 1>(SP, grid, threads, smem, st)
-                                          : launch_sweep_ct<real, PSFM_PAD_ZEROS, 2, 0, 1>(SP, grid, threads, smem, st);
+    if (fisheye) {
+      // fp32, two contexts, plain inputs: own instantiation; everything else (any C, pre-map, upsampled inverse
+      // depths, fp64) runs the run-time-generic one
+      bool done = false;
+      if constexpr (sizeof(real) == 4) {
+        if (var == 0 && cfg->C == 2) {
+          e = cfg->padding == PSFM_PAD_BORDER ? launch_sweep_ct<real, PSFM_PAD_BORDER, 0, 2, 1>(SP, grid, threads, smem, st)
+                                              : launch_sweep_ct<real, PSFM_PAD_ZEROS, 0, 2, 1>(SP, grid, threads, smem, st);
+          done = true;
+        }
+      }
+      if (!done)
+        e = cfg->padding == PSFM_PAD_BORDER ? launch_sweep_ct<real, PSFM_PAD_BORDER, 2, 0, 1>(SP, grid, threads, smem, st)
+                                            : launch_sweep_ct<real, PSFM_PAD_ZEROS, 2, 0, 1>(SP, grid, threads, smem, st);
+    }
     else
       e = cfg->padding == PSFM_PAD_BORDER ? PSFM_SWEEP(PSFM_PAD_BORDER) : PSFM_SWEEP(PSFM_PAD_ZEROS);
 #undef PSFM_SWEEP

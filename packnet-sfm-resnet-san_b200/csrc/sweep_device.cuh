@@ -15,7 +15,6 @@ namespace psfm {
 
 constexpr unsigned kFull = 0xffffffffu;
 
-// reciprocal: exact for double; MUFU.RCP + one Newton step (< 1 ulp) for float
 // elementary functions of the fisheye camera model (geometry/camera.py:194-394)
 __device__ __forceinline__ double rroot(double x) { return sqrt(x); }
 __device__ __forceinline__ float rroot(float x) { return sqrtf(x); }
@@ -23,6 +22,7 @@ __device__ __forceinline__ double rtan(double x) { return tan(x); }
 __device__ __forceinline__ float rtan(float x) { return tanf(x); }
 __device__ __forceinline__ double ratan(double x) { return atan(x); }
 __device__ __forceinline__ float ratan(float x) { return atanf(x); }
+// reciprocal: exact for double; MUFU.RCP + one Newton step (< 1 ulp) for float
 __device__ __forceinline__ double rrcp(double x) { return 1.0 / x; }
 __device__ __forceinline__ float rrcp(float x) {
   float r;
