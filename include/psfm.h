@@ -182,6 +182,27 @@ int psfm_project_backward(int B, int H, int W, int dt, const void* X, const void
                           const void* grad_out, void* dX, void* d_Tcw, void* workspace, size_t workspace_bytes,
                           void* stream);
 
+/* FisheyeCamera.reconstruct / FisheyeCamera.project in the camera frame (geometry/camera.py:242-305, :311-394; VADAS
+ * model; intr = [B,11] rows k0..k6, s, div, ux, uy).  The world-frame variants of the reference are these composed
+ * with psfm_transform_points (as shipped they raise).
+ * reconstruct: out[B,3,H,W] = (tan(r_d)/r_d x_d, tan(r_d)/r_d y_d, 1) * depth; backward: d_depth[B,1,H,W].
+ * project: X[B,3,N] -> out[B,N,2] normalised with (Hn, Wn) (N = H*W, Hn = H, Wn = W for maps; image_size for clouds);
+ * Z clamped at sys.float_info.epsilon; backward: dX[B,3,N]. */
+int psfm_fisheye_reconstruct(int B, int H, int W, int dt, const void* depth, const void* intr, void* out, void* stream);
+int psfm_fisheye_reconstruct_backward(int B, int H, int W, int dt, const void* intr, const void* grad_out, void* d_depth,
+                                      void* stream);
+int psfm_fisheye_project(int B, size_t N, int Hn, int Wn, int dt, const void* X, const void* intr, void* out, void* stream);
+int psfm_fisheye_project_backward(int B, size_t N, int Hn, int Wn, int dt, const void* X, const void* intr,
+                                  const void* grad_out, void* dX, void* stream);
+
+/* funct.grid_sample(image, grid, mode='bilinear', padding_mode, align_corners=True) as view_synthesis calls it
+ * (geometry/camera_utils.py:58-59): image[B,3,Hi,Wi], grid[B,Ho,Wo,2] -> out[B,3,Ho,Wo], all of type dt.
+ * Backward: d_grid[B,Ho,Wo,2] (the image is an input frame; its gradient is not produced). */
+int psfm_grid_sample(int B, int Hi, int Wi, int Ho, int Wo, int dt, int padding, const void* image, const void* grid,
+                     void* out, void* stream);
+int psfm_grid_sample_backward(int B, int Hi, int Wi, int Ho, int Wo, int dt, int padding, const void* image,
+                              const void* grid, const void* grad_out, void* d_grid, void* stream);
+
 /* Pose.transform_points (geometry/pose.py:80-86): out[B,3,N] = R X + t.  Backward: dX, d_mat[B,4,4]. */
 int psfm_transform_points(int B, size_t N, int dt, const void* mat, const void* X, void* out, void* stream);
 int psfm_transform_points_backward(int B, size_t N, int dt, const void* mat, const void* X, const void* grad_out,

@@ -34,7 +34,9 @@ API = {
         'MultiViewPhotometricLoss.calc_photometric_loss', 'MultiViewPhotometricLoss.reduce_photometric_loss',
         'MultiViewPhotometricLoss.calc_smoothness_loss'],
     'packnet_sfm.losses.loss_base': ['LossBase.add_metric', 'ProgressiveScaling.__init__', 'ProgressiveScaling.__call__'],
-    'packnet_sfm.geometry.camera': ['Camera.__init__', 'Camera.scaled', 'Camera.reconstruct', 'Camera.project', 'Camera.to'],
+    'packnet_sfm.geometry.camera': ['Camera.__init__', 'Camera.scaled', 'Camera.reconstruct', 'Camera.project', 'Camera.to',
+                                    'FisheyeCamera.__init__', 'FisheyeCamera.reconstruct', 'FisheyeCamera.project',
+                                    'FisheyeCamera.to'],
     'packnet_sfm.geometry.camera_utils': ['construct_K', 'scale_intrinsics', 'view_synthesis'],
     'packnet_sfm.geometry.pose': ['Pose.__init__', 'Pose.identity', 'Pose.from_vec', 'Pose.inverse', 'Pose.repeat',
                                   'Pose.transform_pose', 'Pose.transform_points', 'Pose.__matmul__', 'Pose.item'],

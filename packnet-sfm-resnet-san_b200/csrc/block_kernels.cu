@@ -167,6 +167,140 @@ __global__ void __launch_bounds__(kBT) project_bwd_kernel(int H, int W, const re
 }
 
 // ------------------------------------------------------------------------------------------
+// FisheyeCamera (VADAS), frame 'c' (reference geometry/camera.py:194-394).  intr: [B,11] rows
+// (k0..k6, s, div, ux, uy).  reconstruct: theta = r_d is the reference's placeholder inverse of the
+// distortion polynomial (:278-283); project: r_d = sum k_i atan(r)^i (:352-383).
+// ------------------------------------------------------------------------------------------
+template <typename real> __device__ __forceinline__ real fe_eps() { return (real)2.220446049250313e-16; }   // sys.float_info.epsilon
+
+template <typename real>
+__device__ __forceinline__ void fisheye_ray(const real* fi, real u, real v, real& rx, real& ry) {
+  const real xd = (u - fi[9]) / fi[7], yd = (v - fi[10]) / fi[8];
+  const real rd = sqrt(xd * xd + yd * yd);
+  const real sc = tan(rd) / (rd < fe_eps<real>() ? fe_eps<real>() : rd);
+  rx = sc * xd; ry = sc * yd;
+}
+
+template <typename real>
+__global__ void __launch_bounds__(kBT) fisheye_reconstruct_kernel(int H, int W, const real* depth, const real* intr, real* out) {
+  const int b = blockIdx.y;
+  const size_t plane = (size_t)H * W, i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  if (i >= plane) return;
+  real rx, ry;
+  fisheye_ray<real>(intr + (size_t)b * 11, (real)(int)(i % W), (real)(int)(i / W), rx, ry);
+  const real d = depth[b * plane + i];
+  out[((size_t)b * 3) * plane + i] = rx * d;
+  out[((size_t)b * 3 + 1) * plane + i] = ry * d;
+  out[((size_t)b * 3 + 2) * plane + i] = d;
+}
+
+template <typename real>
+__global__ void __launch_bounds__(kBT) fisheye_reconstruct_bwd_kernel(int H, int W, const real* intr, const real* gout,
+                                                                      real* d_depth) {
+  const int b = blockIdx.y;
+  const size_t plane = (size_t)H * W, i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  if (i >= plane) return;
+  real rx, ry;
+  fisheye_ray<real>(intr + (size_t)b * 11, (real)(int)(i % W), (real)(int)(i / W), rx, ry);
+  d_depth[b * plane + i] = rx * gout[((size_t)b * 3) * plane + i] + ry * gout[((size_t)b * 3 + 1) * plane + i] +
+                           gout[((size_t)b * 3 + 2) * plane + i];
+}
+
+// pixel coordinates (px, py) of the camera-frame point X; when J: J[0..2] = d px / d X, J[3..5] = d py / d X.
+// torch's gradient of sqrt at r = 0 is undefined (inf * 0); here it is 0.
+template <typename real>
+__device__ __forceinline__ void fisheye_pixel(const real* fi, const real* X, real& px, real& py, real* J) {
+  const real eps = fe_eps<real>();
+  const real Z = rmax(X[2], eps);
+  const real xn = X[0] / Z, yn = X[1] / Z;
+  const real r2 = xn * xn + yn * yn, r = sqrt(r2);
+  const real th = atan(r);
+  real poly = fi[6], dpoly = real(6) * fi[6];
+#pragma unroll
+  for (int i = 5; i >= 1; --i) { poly = poly * th + fi[i]; dpoly = dpoly * th + (real)i * fi[i]; }
+  poly = poly * th + fi[0];
+  const bool tiny = r < eps;
+  const real g = poly / (tiny ? eps : r);
+  px = fi[7] * (g * xn) + fi[9];
+  py = fi[8] * (g * yn) + fi[10];
+  if (J) {
+    const real h = tiny ? real(0) : (dpoly / (real(1) + r2) - g) / r2;      // (d g / d r) / r
+    const real a00 = fi[7] * (g + h * xn * xn), a01 = fi[7] * h * xn * yn, a10 = fi[8] * h * xn * yn,
+               a11 = fi[8] * (g + h * yn * yn);
+    const real zk = (X[2] >= eps) ? real(-1) / Z : real(0);
+    J[0] = a00 / Z; J[1] = a01 / Z; J[2] = (a00 * xn + a01 * yn) * zk;
+    J[3] = a10 / Z; J[4] = a11 / Z; J[5] = (a10 * xn + a11 * yn) * zk;
+  }
+}
+
+// Hn, Wn: the size the coordinates are normalised with (the map itself, or FisheyeCamera.image_size for [B,3,N] clouds)
+template <typename real>
+__global__ void __launch_bounds__(kBT) fisheye_project_kernel(size_t N, int Hn, int Wn, const real* X, const real* intr, real* out) {
+  const int b = blockIdx.y;
+  const size_t i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  if (i >= N) return;
+  real x[3], px, py;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) x[k] = X[((size_t)b * 3 + k) * N + i];
+  fisheye_pixel<real>(intr + (size_t)b * 11, x, px, py, nullptr);
+  out[(b * N + i) * 2] = real(2) * px / real(Wn - 1) - real(1);
+  out[(b * N + i) * 2 + 1] = real(2) * py / real(Hn - 1) - real(1);
+}
+
+template <typename real>
+__global__ void __launch_bounds__(kBT) fisheye_project_bwd_kernel(size_t N, int Hn, int Wn, const real* X, const real* intr,
+                                                                  const real* gout, real* dX) {
+  const int b = blockIdx.y;
+  const size_t i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  if (i >= N) return;
+  real x[3], px, py, J[6];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) x[k] = X[((size_t)b * 3 + k) * N + i];
+  fisheye_pixel<real>(intr + (size_t)b * 11, x, px, py, J);
+  const real gx = gout[(b * N + i) * 2] * real(2) / real(Wn - 1), gy = gout[(b * N + i) * 2 + 1] * real(2) / real(Hn - 1);
+#pragma unroll
+  for (int k = 0; k < 3; ++k) dX[((size_t)b * 3 + k) * N + i] = gx * J[k] + gy * J[3 + k];
+}
+
+// ------------------------------------------------------------------------------------------
+// grid_sample(image [B,3,Hi,Wi], grid [B,Ho,Wo,2], bilinear, align_corners=True, zeros | border)
+// (the reference's call: geometry/camera_utils.py:58-59).  Backward: d grid.
+// ------------------------------------------------------------------------------------------
+template <typename real>
+__global__ void __launch_bounds__(kBT) grid_sample_kernel(int Hi, int Wi, size_t No, int pad, const real* img, const real* grid,
+                                                          real* out) {
+  const int b = blockIdx.y;
+  const size_t i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  if (i >= No) return;
+  const real ix = (grid[(b * No + i) * 2] + real(1)) * real(0.5) * real(Wi - 1);
+  const real iy = (grid[(b * No + i) * 2 + 1] + real(1)) * real(0.5) * real(Hi - 1);
+  real v[3];
+  bilinear3<real, real, false>(img + (size_t)b * 3 * Hi * Wi, (size_t)Hi * Wi, Hi, Wi, pad, ix, iy, v, nullptr, nullptr);
+#pragma unroll
+  for (int c = 0; c < 3; ++c) out[((size_t)b * 3 + c) * No + i] = v[c];
+}
+
+template <typename real>
+__global__ void __launch_bounds__(kBT) grid_sample_bwd_kernel(int Hi, int Wi, size_t No, int pad, const real* img,
+                                                              const real* grid, const real* gout, real* d_grid) {
+  const int b = blockIdx.y;
+  const size_t i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  if (i >= No) return;
+  const real ix = (grid[(b * No + i) * 2] + real(1)) * real(0.5) * real(Wi - 1);
+  const real iy = (grid[(b * No + i) * 2 + 1] + real(1)) * real(0.5) * real(Hi - 1);
+  real v[3], gx[3], gy[3];
+  bilinear3<real, real, true>(img + (size_t)b * 3 * Hi * Wi, (size_t)Hi * Wi, Hi, Wi, pad, ix, iy, v, gx, gy);
+  real ax = real(0), ay = real(0);
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    const real g = gout[((size_t)b * 3 + c) * No + i];
+    ax += g * gx[c]; ay += g * gy[c];
+  }
+  d_grid[(b * No + i) * 2] = ax * real(0.5) * real(Wi - 1);
+  d_grid[(b * No + i) * 2 + 1] = ay * real(0.5) * real(Hi - 1);
+}
+
+// ------------------------------------------------------------------------------------------
 // Pose.transform_points: out = R X + t on [B,3,N]
 // ------------------------------------------------------------------------------------------
 template <typename real>
@@ -611,6 +745,69 @@ int psfm_project_backward(int B, int H, int W, int dt, const void* X, const void
     if (pose) mat_finish_kernel<real><<<B, 32, 0, (cudaStream_t)stream>>>((const real*)ws, (int)nb, (real*)d_Tcw);
   });
   return launch_result("psfm_project_backward");
+}
+
+int psfm_fisheye_reconstruct(int B, int H, int W, int dt, const void* depth, const void* intr, void* out, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(B >= 1 && H >= 1 && W >= 1 && depth && intr && out, "psfm_fisheye_reconstruct: bad argument");
+  count_launches(1);
+  PSFM_DISPATCH(dt, (fisheye_reconstruct_kernel<real><<<dim3(nblk_for((size_t)H * W), B), kBT, 0, (cudaStream_t)stream>>>(
+                        H, W, (const real*)depth, (const real*)intr, (real*)out)));
+  return launch_result("psfm_fisheye_reconstruct");
+}
+
+int psfm_fisheye_reconstruct_backward(int B, int H, int W, int dt, const void* intr, const void* grad_out, void* d_depth,
+                                      void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(B >= 1 && H >= 1 && W >= 1 && intr && grad_out && d_depth, "psfm_fisheye_reconstruct_backward: bad argument");
+  count_launches(1);
+  PSFM_DISPATCH(dt, (fisheye_reconstruct_bwd_kernel<real><<<dim3(nblk_for((size_t)H * W), B), kBT, 0, (cudaStream_t)stream>>>(
+                        H, W, (const real*)intr, (const real*)grad_out, (real*)d_depth)));
+  return launch_result("psfm_fisheye_reconstruct_backward");
+}
+
+int psfm_fisheye_project(int B, size_t N, int Hn, int Wn, int dt, const void* X, const void* intr, void* out, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(B >= 1 && N >= 1 && Hn >= 2 && Wn >= 2 && X && intr && out, "psfm_fisheye_project: bad argument");
+  count_launches(1);
+  PSFM_DISPATCH(dt, (fisheye_project_kernel<real><<<dim3(nblk_for(N), B), kBT, 0, (cudaStream_t)stream>>>(
+                        N, Hn, Wn, (const real*)X, (const real*)intr, (real*)out)));
+  return launch_result("psfm_fisheye_project");
+}
+
+int psfm_fisheye_project_backward(int B, size_t N, int Hn, int Wn, int dt, const void* X, const void* intr,
+                                  const void* grad_out, void* dX, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(B >= 1 && N >= 1 && Hn >= 2 && Wn >= 2 && X && intr && grad_out && dX,
+                   "psfm_fisheye_project_backward: bad argument");
+  count_launches(1);
+  PSFM_DISPATCH(dt, (fisheye_project_bwd_kernel<real><<<dim3(nblk_for(N), B), kBT, 0, (cudaStream_t)stream>>>(
+                        N, Hn, Wn, (const real*)X, (const real*)intr, (const real*)grad_out, (real*)dX)));
+  return launch_result("psfm_fisheye_project_backward");
+}
+
+int psfm_grid_sample(int B, int Hi, int Wi, int Ho, int Wo, int dt, int padding, const void* image, const void* grid,
+                     void* out, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(B >= 1 && Hi >= 1 && Wi >= 1 && Ho >= 1 && Wo >= 1 && image && grid && out &&
+                       (padding == PSFM_PAD_ZEROS || padding == PSFM_PAD_BORDER), "psfm_grid_sample: bad argument");
+  count_launches(1);
+  const size_t No = (size_t)Ho * Wo;
+  PSFM_DISPATCH(dt, (grid_sample_kernel<real><<<dim3(nblk_for(No), B), kBT, 0, (cudaStream_t)stream>>>(
+                        Hi, Wi, No, padding, (const real*)image, (const real*)grid, (real*)out)));
+  return launch_result("psfm_grid_sample");
+}
+
+int psfm_grid_sample_backward(int B, int Hi, int Wi, int Ho, int Wo, int dt, int padding, const void* image,
+                              const void* grid, const void* grad_out, void* d_grid, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(B >= 1 && Hi >= 1 && Wi >= 1 && Ho >= 1 && Wo >= 1 && image && grid && grad_out && d_grid &&
+                       (padding == PSFM_PAD_ZEROS || padding == PSFM_PAD_BORDER), "psfm_grid_sample_backward: bad argument");
+  count_launches(1);
+  const size_t No = (size_t)Ho * Wo;
+  PSFM_DISPATCH(dt, (grid_sample_bwd_kernel<real><<<dim3(nblk_for(No), B), kBT, 0, (cudaStream_t)stream>>>(
+                        Hi, Wi, No, padding, (const real*)image, (const real*)grid, (const real*)grad_out, (real*)d_grid)));
+  return launch_result("psfm_grid_sample_backward");
 }
 
 int psfm_pose_from_vec(int B, int dt, const void* vec, void* mat, void* stream) {

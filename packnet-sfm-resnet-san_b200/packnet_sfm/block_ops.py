@@ -107,6 +107,126 @@ def project_op(X, K, Tcw=None):
     return _Project.apply(X, K, Tcw)
 
 
+class _FisheyeReconstruct(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, depth, intr):
+        _C.require_cuda(depth, intr)
+        B, _, H, W = depth.shape
+        depth = depth.contiguous()
+        out = torch.empty((B, 3, H, W), dtype=depth.dtype, device=depth.device)
+        with torch.cuda.device(depth.device):
+            _C.check(_C.lib.psfm_fisheye_reconstruct(B, H, W, _real(depth), _C.ptr(depth), _C.ptr(intr), _C.ptr(out),
+                                                     _C.stream_ptr(depth.device)))
+        ctx.save_for_backward(intr)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        intr, = ctx.saved_tensors
+        g = g.contiguous()
+        B, _, H, W = g.shape
+        d_depth = torch.empty((B, 1, H, W), dtype=g.dtype, device=g.device)
+        with torch.cuda.device(g.device):
+            _C.check(_C.lib.psfm_fisheye_reconstruct_backward(B, H, W, _real(g), _C.ptr(intr), _C.ptr(g), _C.ptr(d_depth),
+                                                              _C.stream_ptr(g.device)))
+        return d_depth, None
+
+
+def fisheye_reconstruct_op(depth, intr):
+    """FisheyeCamera.reconstruct(frame='c'): depth [B,1,H,W], packed intrinsics [B,11] -> points [B,3,H,W]."""
+    _real(depth)
+    _no_grad_supported(intr, 'the fisheye intrinsics')
+    return _FisheyeReconstruct.apply(depth, intr.to(depth.dtype).contiguous())
+
+
+class _FisheyeProject(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, X, intr, Hn, Wn):
+        _C.require_cuda(X, intr)
+        B = X.shape[0]
+        X = X.contiguous()
+        N = X.numel() // (B * 3)
+        out = torch.empty(((B,) + tuple(X.shape[2:]) + (2,)), dtype=X.dtype, device=X.device)
+        with torch.cuda.device(X.device):
+            _C.check(_C.lib.psfm_fisheye_project(B, N, Hn, Wn, _real(X), _C.ptr(X), _C.ptr(intr), _C.ptr(out),
+                                                 _C.stream_ptr(X.device)))
+        ctx.save_for_backward(X, intr)
+        ctx.size = (Hn, Wn)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        X, intr = ctx.saved_tensors
+        g = g.contiguous()
+        B = X.shape[0]
+        N = X.numel() // (B * 3)
+        dX = torch.empty_like(X)
+        with torch.cuda.device(X.device):
+            _C.check(_C.lib.psfm_fisheye_project_backward(B, N, ctx.size[0], ctx.size[1], _real(X), _C.ptr(X), _C.ptr(intr),
+                                                          _C.ptr(g), _C.ptr(dX), _C.stream_ptr(X.device)))
+        return dX, None, None, None
+
+
+def fisheye_project_op(X, intr, image_size=None):
+    """FisheyeCamera.project(frame='c'): points [B,3,H,W] (or [B,3,N] with image_size=(H, W)) and packed
+    intrinsics [B,11] -> normalised coordinates [B,H,W,2] ([B,N,2])."""
+    _real(X)
+    _no_grad_supported(intr, 'the fisheye intrinsics')
+    if X.dim() == 4:
+        Hn, Wn = int(X.shape[2]), int(X.shape[3])
+    elif X.dim() == 3:
+        if image_size is None or image_size[0] is None or image_size[1] is None:
+            raise ValueError('image_size must be provided for 3D point cloud projection.')
+        Hn, Wn = int(image_size[0]), int(image_size[1])
+    else:
+        raise ValueError('Input X must be of shape [B,3,H,W] or [B,3,N]')
+    assert X.shape[1] == 3
+    return _FisheyeProject.apply(X, intr.to(X.dtype).contiguous(), Hn, Wn)
+
+
+class _GridSample(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, image, grid, padding):
+        _C.require_cuda(image, grid)
+        B, ch, Hi, Wi = image.shape
+        if ch != 3:
+            raise ValueError('image must be [B,3,H,W]')
+        if grid.dim() != 4 or grid.shape[0] != B or grid.shape[3] != 2:
+            raise ValueError('grid must be [B,Ho,Wo,2]')
+        grid = grid.contiguous()
+        image = image.to(grid.dtype).contiguous()
+        Ho, Wo = int(grid.shape[1]), int(grid.shape[2])
+        out = torch.empty((B, 3, Ho, Wo), dtype=grid.dtype, device=grid.device)
+        with torch.cuda.device(grid.device):
+            _C.check(_C.lib.psfm_grid_sample(B, Hi, Wi, Ho, Wo, _real(grid), padding, _C.ptr(image), _C.ptr(grid),
+                                             _C.ptr(out), _C.stream_ptr(grid.device)))
+        ctx.save_for_backward(image, grid)
+        ctx.padding = padding
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        image, grid = ctx.saved_tensors
+        g = g.to(grid.dtype).contiguous()
+        B, _, Hi, Wi = image.shape
+        Ho, Wo = int(grid.shape[1]), int(grid.shape[2])
+        d_grid = torch.empty_like(grid)
+        with torch.cuda.device(grid.device):
+            _C.check(_C.lib.psfm_grid_sample_backward(B, Hi, Wi, Ho, Wo, _real(grid), ctx.padding, _C.ptr(image),
+                                                      _C.ptr(grid), _C.ptr(g), _C.ptr(d_grid), _C.stream_ptr(grid.device)))
+        return None, d_grid, None
+
+
+def grid_sample_op(image, grid, padding_mode='zeros'):
+    """funct.grid_sample(image, grid, mode='bilinear', padding_mode, align_corners=True) as view_synthesis calls
+    it (reference geometry/camera_utils.py:58-59); differentiable w.r.t. the grid."""
+    if padding_mode not in _C.PAD:
+        raise ValueError('padding_mode must be zeros or border (got %s)' % padding_mode)
+    _real(grid)
+    _no_grad_supported(image, 'the sampled image')
+    return _GridSample.apply(image, grid, _C.PAD[padding_mode])
+
+
 class _TransformPoints(torch.autograd.Function):
     @staticmethod
     def forward(ctx, mat, X):

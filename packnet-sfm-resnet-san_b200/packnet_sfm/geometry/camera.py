@@ -1,8 +1,8 @@
-"""Pinhole camera (reference: geometry/camera.py:15-190).
+"""Pinhole camera (reference: geometry/camera.py:15-190) and the fork's fisheye (VADAS) camera
+(reference :194-394).
 
 `reconstruct` and `project` keep the reference signatures and run as CUDA kernels through
-the C ABI.  The fisheye (VADAS) camera of the fork (reference :194-394) is a "next" row
- and is not provided."""
+the C ABI."""
 import torch
 import torch.nn as nn
 
@@ -99,3 +99,76 @@ class Camera(nn.Module):
             return project_op(X, self.K, None if self._identity_pose else self.Tcw.mat)
         else:
             raise ValueError('Unknown reference frame {}'.format(frame))
+
+
+class FisheyeCamera(nn.Module):
+    """Differentiable fisheye camera (VADAS model), reference :194-394.
+
+    intrinsics: dict with 'k' [B,7] (distortion polynomial), 's', 'div', 'ux', 'uy' [B]
+    (datasets/ncdb_dataset.py:577-584).  `reconstruct` keeps the reference's placeholder inverse of the
+    polynomial (theta = r_d, :278-283).  The world-frame branches, which raise in the reference because
+    `Pose.transform_points` is handed a [B,3,HW] tensor (:305, :344), apply the pose to the point tensor here."""
+
+    def __init__(self, intrinsics, Tcw=None, image_size=None):
+        super().__init__()
+        self.k = intrinsics['k']
+        self.s = intrinsics['s']
+        self.div = intrinsics['div']
+        self.ux = intrinsics['ux']
+        self.uy = intrinsics['uy']
+        self._identity_pose = Tcw is None
+        self.Tcw = Pose.identity(len(self.k), device=self.k.device, dtype=self.k.dtype) if Tcw is None else Tcw
+        self.image_size = image_size
+        self._Twc = None
+
+    def __len__(self):
+        return len(self.k)
+
+    def to(self, *args, **kwargs):
+        for name in ('k', 's', 'div', 'ux', 'uy'):
+            setattr(self, name, getattr(self, name).to(*args, **kwargs))
+        self.Tcw = self.Tcw.to(*args, **kwargs)
+        self._Twc = None
+        return self
+
+    @property
+    def intrinsics(self):
+        return {'k': self.k, 's': self.s, 'div': self.div, 'ux': self.ux, 'uy': self.uy}
+
+    @property
+    def Twc(self):
+        """World -> camera pose (inverse of Tcw)."""
+        if self._Twc is None:
+            self._Twc = self.Tcw.inverse()
+        return self._Twc
+
+    def _packed(self, like):
+        from packnet_sfm.ops import pack_fisheye
+        return pack_fisheye(self.intrinsics, like.shape[0], like.dtype, like.device)
+
+    def reconstruct(self, depth, frame='w'):
+        """Depth map [B,1,H,W] -> 3D points [B,3,H,W] in the camera ('c') or world ('w') frame (:242-309)."""
+        B, C, H, W = depth.shape
+        assert C == 1
+        from packnet_sfm.block_ops import fisheye_reconstruct_op
+        Xc = fisheye_reconstruct_op(depth, self._packed(depth))
+        if frame == 'c':
+            return Xc
+        elif frame == 'w':
+            return Xc if self._identity_pose else self.Twc @ Xc
+        else:
+            raise ValueError('Unknown reference frame {}'.format(frame))
+
+    def project(self, X, frame='w'):
+        """3D points [B,3,H,W] (or [B,3,N] with `image_size`) -> normalised coordinates [B,H,W,2] ([B,N,2]) (:311-394)."""
+        if X.dim() not in (3, 4):
+            raise ValueError('Input X must be of shape [B,3,H,W] or [B,3,N]')
+        assert X.shape[1] == 3
+        from packnet_sfm.block_ops import fisheye_project_op
+        if frame == 'w':
+            Xc = X if self._identity_pose else self.Tcw @ X
+        elif frame == 'c':
+            Xc = X
+        else:
+            raise ValueError('Unknown reference frame {}'.format(frame))
+        return fisheye_project_op(Xc, self._packed(X), self.image_size)

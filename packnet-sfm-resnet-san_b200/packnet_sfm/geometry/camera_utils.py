@@ -26,6 +26,13 @@ def view_synthesis(ref_image, depth, ref_cam, cam, mode='bilinear', padding_mode
     assert depth.size(1) == 1
     if mode != 'bilinear':
         raise NotImplementedError('only bilinear view synthesis is implemented')
+    from packnet_sfm.geometry.camera import FisheyeCamera
+    if isinstance(cam, FisheyeCamera) or isinstance(ref_cam, FisheyeCamera):
+        # the reference's own chain (:50-59), every link a CUDA kernel of this library
+        from packnet_sfm.block_ops import grid_sample_op
+        world_points = cam.reconstruct(depth, frame='w')
+        ref_coords = ref_cam.project(world_points, frame='w')
+        return grid_sample_op(ref_image, ref_coords, padding_mode)
     from packnet_sfm.ops import view_synthesis_op
     # world = Twc_cam @ Xc, then Tcw_ref @ world  ==  (Tcw_ref @ Twc_cam) @ Xc
     T = ref_cam.Tcw.mat

@@ -9,7 +9,7 @@ signatures and are kernel-backed individually for callers that use them directly
 """
 import torch
 
-from packnet_sfm.geometry.camera import Camera
+from packnet_sfm.geometry.camera import Camera, FisheyeCamera
 from packnet_sfm.geometry.camera_utils import view_synthesis
 from packnet_sfm.geometry.pose import Pose
 from packnet_sfm.losses.loss_base import LossBase, ProgressiveScaling
@@ -72,12 +72,24 @@ class MultiViewPhotometricLoss(LossBase):
                     premap=int(self.sigmoid_premap), min_depth=self.min_depth, max_depth=self.max_depth,
                     upsample_depth_maps=self.upsample_depth_maps)
 
-    def warp_ref_image(self, inv_depths, ref_image, K, ref_K, pose):
-        """Warp `ref_image` into the target view at every scale (upstream pinhole body of
-        reference :131-195).  Returns a list of [B,3,Hs,Ws]."""
+    def warp_ref_image(self, inv_depths, ref_image, K, ref_K, pose, image_size=None):
+        """Warp `ref_image` into the target view at every scale (reference :131-195).  Returns a list of
+        [B,3,Hs,Ws].  K / ref_K: [B,3,3] pinhole matrices (upstream body), or the fork's fisheye intrinsics
+        dicts (the fork's body: FisheyeCamera per scale, principal point rescaled, k / s / div passed through)."""
         B, _, H, W = ref_image.shape
         ref_images = match_scales(ref_image, inv_depths, self.n)
         out = []
+        if isinstance(K, dict):
+            for i in range(self.n):
+                _, _, DH, DW = inv_depths[i].shape
+                sw, sh = DW / float(W), DH / float(H)
+                scaled = lambda d: {'k': d['k'], 's': d['s'], 'div': d['div'],
+                                    'ux': (d['ux'] + 0.5) * sw - 0.5, 'uy': (d['uy'] + 0.5) * sh - 0.5}
+                cam = FisheyeCamera(intrinsics=scaled(K), image_size=(DH, DW))
+                ref_cam = FisheyeCamera(intrinsics=scaled(ref_K), Tcw=pose, image_size=(DH, DW))
+                out.append(view_synthesis(ref_images[i], inv2depth(inv_depths[i]), ref_cam, cam,
+                                          padding_mode=self.padding_mode))
+            return out
         for i in range(self.n):
             sf = inv_depths[i].shape[3] / float(W)
             cam = Camera(K=K).scaled(sf)

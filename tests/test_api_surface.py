@@ -30,9 +30,7 @@ RENAMED = {'packnet_sfm.losses.multiview_photometric_loss:MultiViewPhotometricLo
            {'intrinsics': 'K', 'ref_intrinsics': 'ref_K'},
            'packnet_sfm.losses.multiview_photometric_loss:MultiViewPhotometricLoss.warp_ref_image':
            {'intrinsics': 'K', 'ref_intrinsics': 'ref_K', 'poses': 'pose'}}
-# the fork's warp_ref_image takes fisheye dicts plus a trailing `image_size` argument and cannot run
-# (SURVEY.md §0 fact 1); the drop-in keeps the upstream pinhole form, so only the leading parameters are compared
-LEADING_ONLY = {'packnet_sfm.losses.multiview_photometric_loss:MultiViewPhotometricLoss.warp_ref_image': 6}
+LEADING_ONLY = {}
 
 
 def test_signatures_match_reference():

@@ -97,3 +97,90 @@ def test_fisheye_rejections():
         MultiViewPhotometricLoss(kernel_mode='split', **inp['hp'])(*args, K, K, poses)
     with pytest.raises(ValueError):
         MultiViewPhotometricLoss(**inp['hp'])(*args, K, torch.eye(3, device=dev, dtype=torch.float64), poses)
+
+
+# ---- building blocks: FisheyeCamera / grid_sample / view_synthesis (geometry/camera.py:194-394) ----------------
+
+def _units():
+    from golden_cases import load_golden
+    u = load_golden('fisheye_units')
+    t = lambda k: torch.from_numpy(u[k]).to('cuda:0')
+    return u, t, {n: t('intr_' + n) for n in ('k', 's', 'div', 'ux', 'uy')}
+
+
+def test_fisheye_camera_methods_match_reference():
+    """FisheyeCamera.reconstruct / project (both frames) and view_synthesis against outputs of the reference's
+    own class (fisheye_units.npz), fp64."""
+    import numpy as np
+    from packnet_sfm.geometry.camera import FisheyeCamera
+    from packnet_sfm.geometry.camera_utils import view_synthesis
+    from packnet_sfm.geometry.pose import Pose
+    u, t, intr = _units()
+    eq = lambda a, key: np.testing.assert_allclose(a.cpu().numpy(), u[key], rtol=1e-12, atol=1e-13)
+    B, _, H, W = u['depth'].shape
+    pose = Pose(t('pose_mat'))
+    cam = FisheyeCamera(intrinsics=intr, image_size=(H, W))
+    X = cam.reconstruct(t('depth'), frame='c')
+    eq(X, 'reconstruct_c')
+    eq(cam.project(pose @ X, frame='c'), 'project_c')
+    eq(cam.project(t('edge_points'), frame='c'), 'project_edge')              # Z <= 0, far off-axis points
+    # world frame: what the reference's frame='w' branches spell out (they raise there)
+    ref_cam = FisheyeCamera(intrinsics=intr, Tcw=pose, image_size=(H, W))
+    eq(ref_cam.project(cam.reconstruct(t('depth'), frame='w'), frame='w'), 'project_c')
+    # [B,3,N] point clouds are normalised with image_size (:325-333)
+    eq(cam.project((pose @ X).reshape(B, 3, -1), frame='c').view(B, H, W, 2), 'project_c')
+    with pytest.raises(ValueError, match='image_size'):
+        FisheyeCamera(intrinsics=intr).project(X.reshape(B, 3, -1), frame='c')
+    for pm in ('zeros', 'border'):
+        eq(view_synthesis(t('img'), t('depth'), ref_cam, cam, padding_mode=pm), 'view_synthesis_' + pm)
+    assert len(cam) == B and cam.to('cuda:0') is cam
+
+
+@pytest.mark.parametrize('pm', ['zeros', 'border'])
+def test_fisheye_view_synthesis_gradients(pm):
+    """d/d depth and d/d pose of the kernel chain reconstruct -> transform -> project -> grid_sample against
+    autograd through the oracle (fp64)."""
+    from packnet_sfm.geometry.camera import FisheyeCamera
+    from packnet_sfm.geometry.camera_utils import view_synthesis
+    from packnet_sfm.geometry.pose import Pose
+    B, H, W = 2, 20, 36
+    image, context, invd, vecs, _ = O.synth_S3(B, H, W, 1, torch.float64, kd=5)
+    intr = O.synth_fisheye(B, H, W)
+    gen = torch.Generator('cpu').manual_seed(5)
+    wgt = torch.rand(B, 3, H, W, generator=gen, dtype=torch.float64)
+    d64 = O.inv2depth(invd[0]).clone().requires_grad_()
+    v64 = vecs[0].clone().requires_grad_()
+    ref = O.fisheye_view_synthesis(context[0], d64, intr, O.pose_vec_to_mat(v64), intr, pm)
+    (ref * wgt).sum().backward()
+    dev = 'cuda:0'
+    dg = O.inv2depth(invd[0]).to(dev).requires_grad_()
+    vg = vecs[0].to(dev).requires_grad_()
+    K = {k: v.to(dev) for k, v in intr.items()}
+    out = view_synthesis(context[0].to(dev), dg, FisheyeCamera(K, Tcw=Pose.from_vec(vg, 'euler'), image_size=(H, W)),
+                         FisheyeCamera(K, image_size=(H, W)), padding_mode=pm)
+    (out * wgt.to(dev)).sum().backward()
+    torch.cuda.synchronize()
+    assert (out.detach().cpu() - ref.detach()).abs().max().item() <= 1e-12
+    assert rel_l2(dg.grad.cpu(), d64.grad) <= 1e-10
+    assert rel_l2(vg.grad.cpu(), v64.grad) <= 1e-10
+
+
+@pytest.mark.parametrize('name', ['fisheye_tiny_U_zeros', 'fisheye_tiny_U_border', 'fisheye_small_P_zeros'])
+def test_warp_ref_image_with_fisheye_intrinsics(name):
+    """MultiViewPhotometricLoss.warp_ref_image with the fork's dict intrinsics (:131-195) against the warped
+    images the reference produced."""
+    import numpy as np
+    from golden_cases import load_golden
+    from packnet_sfm.geometry.pose import Pose
+    from packnet_sfm.losses.multiview_photometric_loss import MultiViewPhotometricLoss
+    gold = load_golden(name)
+    inp = make_inputs(name, torch.float64)
+    dev = 'cuda:0'
+    L = MultiViewPhotometricLoss(**inp['hp'])
+    K = {k: v.to(dev) for k, v in inp['K'].items()}
+    H, W = inp['image'].shape[2:]
+    for j, (c, v) in enumerate(zip(inp['context'], inp['vecs'])):
+        warped = L.warp_ref_image([d.to(dev) for d in inp['inv_depths']], c.to(dev), K, K,
+                                  Pose.from_vec(v.to(dev), 'euler'), (H, W))
+        for i, w in enumerate(warped):
+            np.testing.assert_allclose(w.cpu().numpy(), gold['warp%d_s%d' % (j, i)], rtol=1e-10, atol=1e-12)
