@@ -11,7 +11,10 @@ Parity pin: the reference ships no tests for this path, so the o
 pinned against outputs of the reference's own classes run in the build container:
 `oracle/gen_golden.py` imports `/root/reference` (pinhole `warp_ref_image`, SURVEY
 Appendix C), and `tests/golden/*.npz` hold what it produced; `tests/test_oracle_golden.py`
-checks this restatement against those fixtures on every run.
+checks this restatement against those fixtures on every run.  The fisheye (VADAS) camera functions
+ are pinned the same way: `oracle/gen_golden_fisheye.py` runs the reference's own
+`FisheyeCamera.reconstruct` / `.project` (frame 'c', which execute as shipped) inside its loss class and
+writes `tests/golden/fisheye_*.npz`.
 
 Third-party arithmetic: `F.grid_sample`, `F.avg_pool2d`, reflection `F.pad` and
 `F.interpolate` are PyTorch primitives (reference pins torch==1.9.0+cu111 in
