@@ -74,8 +74,12 @@ def synth_batch(cfg, device, seed=1234):
         return (x - lo) / (hi - lo)
 
     idt = torch.bfloat16 if cfg['img'] == 'bf16' else torch.float32
-    image = tex(3, 3).to(idt)
-    context = [tex(3, 3).to(idt) for _ in range(C)]
+    if cfg.get('host_images') == 'u8':     # what an image file holds; value = byte / 255 (torchvision to_tensor)
+        quant = lambda t: (t * 255.0).round().clamp(0, 255).to(torch.uint8)
+    else:
+        quant = lambda t: t.to(idt)
+    image = quant(tex(3, 3))
+    context = [quant(tex(3, 3)) for _ in range(C)]
     if cfg.get('pyramid'):      # the decoder's native pyramid; the loss upsamples it in-kernel (upsample_depth_maps)
         inv_depths = [1.0 / (2.0 + 38.0 * F.interpolate(tex(1, 15), size=(H >> s, W >> s), mode='bilinear',
                                                          align_corners=False)) for s in range(n)]
@@ -210,7 +214,27 @@ def run_reference(args):
                              'sample': '%d frame(s) of the %d-frame batch per step, %d steps, fp32, PyTorch CPU' % (
                                  sample, cfg['B'], steps)},
             'e2e': {'value': val, 'unit': 'frames/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+def bind_to_gpu_numa_node(index):
+    """Pin this process (and the pinned host buffers it allocates afterwards, first touch) to the CPU cores next to
+    its GPU.  With N ranks per node the host side of the end-to-end path is the H2D copy from pinned memory; a rank
+    scheduled on the far socket pulls every byte across the inter-socket link.  Returns the core count or None."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        cpus = {w * 64 + b for w, m in enumerate(words) for b in range(64) if (m >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception as ex:      # affinity is an optimisation; say why it was skipped
+        print('[bench] NUMA binding skipped: %s' % ex, file=sys.stderr)
+    return None
 
 
 def run_ours(args):
@@ -219,21 +243,20 @@ def run_ours(args):
     local = int(os.environ.get('LOCAL_RANK', 0))
     dev = torch.device('cuda', local)
     torch.cuda.set_device(dev)
+    numa = bind_to_gpu_numa_node(local) if (world > 1 and not args.no_numa) else None
     if world > 1:
-        # NCCL writes its version banner / debug lines to stdout by default; stdout carries the ONE JSON line
-        os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')
         dist.init_process_group('nccl', device_id=dev)
     from packnet_sfm import _C
     from packnet_sfm.losses.multiview_photometric_loss import MultiViewPhotometricLoss
     from packnet_sfm.geometry.pose import Pose
     sys.path.insert(0, os.path.join(ROOT, 'oracle'))
 
-    cfg = dict(CONFIGS[args.config], pyramid=args.pyramid, camera=args.camera)
+    cfg = dict(CONFIGS[args.config], pyramid=args.pyramid, camera=args.camera, host_images=args.host_images)
     B = cfg['B']
     loss_fn = MultiViewPhotometricLoss(padding_mode=cfg['padding'], kernel_mode=args.mode,
                                        upsample_depth_maps=args.pyramid, **LOSS_HP)
     real_b = 4
-    e = 2 if cfg['img'] == 'bf16' else 4
+    e = 1 if args.host_images == 'u8' else (2 if cfg['img'] == 'bf16' else 4)
     P = cfg['H'] * cfg['W']
     in_bytes = B * P * (3 * e * (1 + cfg['C']) + real_b * cfg['n'])          # inputs of one step
     foot = in_bytes + B * P * (real_b + 1) * cfg['n']                        # + grads + arg-min maps
@@ -444,11 +467,12 @@ def run_ours(args):
                 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
                 'config': {'workload': workload_name(args.config, cfg) + (
                                ' [inverse depths given as the decoder pyramid, upsampled in-kernel]' if args.pyramid else '') + (
-                               ' [fisheye (VADAS) cameras instead of pinhole K]' if args.camera == 'fisheye' else ''),
+                               ' [fisheye (VADAS) cameras instead of pinhole K]' if args.camera == 'fisheye' else '') + (
+                               ' [frames as image bytes, to_tensor (byte / 255) applied in-kernel]' if args.host_images == 'u8' else ''),
                            'global_batch': world * B,
                            'l2': 'rotating %d resident input sets (%.0f MB total footprint > 3x 126 MB L2)' % (
                                R, R * foot / 2 ** 20),
-                           'cuda_graph': use_graph, 'kernel_mode': args.mode or 'fused',
+                           'numa_bound_cores': numa, 'cuda_graph': use_graph, 'kernel_mode': args.mode or 'fused',
                            'loss': dict(LOSS_HP, padding_mode=cfg['padding']),
                            'parallelism': 'dp%d (batch-sharded, one NCCL all-reduce of the loss per step)' % world},
                 'e2e': {'value': frames / (t_e2e_ms * 1e-3), 'unit': 'frames/s', 'h2d_bytes_per_step': h2d,
@@ -459,13 +483,35 @@ def run_ours(args):
                     'value': cpu_val, 'unit': 'frames/s', 'cores': cpu_threads, 'kind': 'port',
                     'sample': 'configs[0] (B=1 192x640 C=2 n=4 fp32), median of %d fwd+bwd iterations of the '
                               'PyTorch-CPU oracle' % cpu_iters}}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
+_RESULT_FD = None
+
+
+def claim_stdout():
+    """stdout carries exactly ONE JSON line.  Native libraries write there too (NCCL prints its version banner with
+    printf, whatever NCCL_DEBUG_FILE says), so file descriptor 1 is pointed at stderr for the whole run and the result
+    goes to a private duplicate of the original stdout."""
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + '\n').encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
+
+
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=200)
@@ -476,6 +522,9 @@ def main():
     ap.add_argument('--no-graph', action='store_true')
     ap.add_argument('--no-rotate', action='store_true')
     ap.add_argument('--no-cpu', action='store_true')
+    ap.add_argument('--no-numa', action='store_true', help='do not bind ranks to the cores next to their GPU')
+    ap.add_argument('--host-images', default='native', choices=['native', 'u8'],
+                    help='u8: frames stay image bytes on the host and in HBM; the kernels apply to_tensor (byte / 255)')
     ap.add_argument('--camera', default='pinhole', choices=['pinhole', 'fisheye'],
                     help='fisheye: the VADAS camera model of the fork (SURVEY.md 8(f) N1) instead of pinhole K')
     ap.add_argument('--pyramid', action='store_true',

@@ -41,7 +41,11 @@ typedef enum psfm_status {
   PSFM_ERR_WORKSPACE = -3     /* workspace too small */
 } psfm_status;
 
-typedef enum psfm_dtype { PSFM_F32 = 0, PSFM_BF16 = 1, PSFM_F64 = 2 } psfm_dtype;
+/* PSFM_U8: image bytes as decoded from the file; the kernels use byte / 255 in fp32 -- bit-identical to
+ * torchvision's to_tensor, which the reference's data pipeline applies on the CPU (datasets/transforms.py) -- so the
+ * host->device copy moves 1 byte per sample instead of 4.  A mask of this type holds 0 / 1 bytes.  Accepted by
+ * psfm_loss_forward_backward when every scale is at image resolution (sweep kernels, fp32 arithmetic). */
+typedef enum psfm_dtype { PSFM_F32 = 0, PSFM_BF16 = 1, PSFM_F64 = 2, PSFM_U8 = 3 } psfm_dtype;
 typedef enum psfm_padding { PSFM_PAD_ZEROS = 0, PSFM_PAD_BORDER = 1 } psfm_padding;
 typedef enum psfm_reduce { PSFM_REDUCE_MIN = 0, PSFM_REDUCE_MEAN = 1 } psfm_reduce;
 /* Camera model of the view synthesis.  PINHOLE: geometry/camera.py:15-190 (Camera).  FISHEYE: the fork's

@@ -296,7 +296,7 @@ __global__ void __launch_bounds__(32 * kPrepWarps) prep_kernel(const SweepParams
 #pragma unroll
         for (int jj = 0; jj < CT; ++jj) st4(cpk[jj] + p * Wp + u, xpA[jj].lo(), xpA[jj].hi(), xpB[jj], real(0));
         if (first) {
-          st4(ra + op, ypA.lo(), ypA.hi(), ypB, maskp ? ldimg<real>(maskp, op) : real(1));
+          st4(ra + op, ypA.lo(), ypA.hi(), ypB, maskp ? ldmask<real>(maskp, op) : real(1));
           st4(rb + op, myA.lo(), myA.hi(), myB, idv);
           st4(rc + op, qyA.lo(), qyA.hi(), qyB, idk);
         }
@@ -991,12 +991,16 @@ __global__ void __launch_bounds__(256) final_kernel(const FinalParams F) {
   if (blockIdx.x == 0) {
     // one pass over all scales: per-thread partial sums in a fixed order, one butterfly per warp, eight warp sums
     double photo = 0.0, smooth = 0.0;
-    for (int s = 0; s < F.n; ++s) {
-      double a = 0.0;
-      const size_t cnt = (size_t)F.B * F.nunits[s];
-      for (size_t i = tid; i < cnt; i += blockDim.x) a += F.loss_part[s][i];
-      photo += a * F.inv_count[s];
+    // the scales' partial lists are read side by side (independent loads in flight; the order of every sum is fixed)
+    double a4[PSFM_MAX_SCALES] = {0.0, 0.0, 0.0, 0.0};
+    size_t cmax = 0;
+    for (int s = 0; s < F.n; ++s) cmax = max(cmax, (size_t)F.B * F.nunits[s]);
+    for (size_t i = tid; i < cmax; i += blockDim.x) {
+#pragma unroll
+      for (int s = 0; s < PSFM_MAX_SCALES; ++s)
+        if (s < F.n && i < (size_t)F.B * F.nunits[s]) a4[s] += F.loss_part[s][i];
     }
+    for (int s = 0; s < F.n; ++s) photo += a4[s] * F.inv_count[s];
     if (F.smooth)
       for (int i = tid; i < F.n * F.B; i += blockDim.x) {
         const int s = i / F.B, b = i - s * F.B;
@@ -1023,10 +1027,16 @@ __global__ void __launch_bounds__(256) final_kernel(const FinalParams F) {
   const int e = tid % 12, k = tid / 12;      // 252 active threads
   double a = 0.0;
   if (tid < 252) {
-    for (int s = 0; s < F.n; ++s) {
-      const real* base = (const real*)F.pose_part[s] + (((size_t)b * F.nunits[s]) * F.C + j) * 12 + e;
-      for (int i = k; i < F.nunits[s]; i += 21) a += (double)base[(size_t)i * F.C * 12];
+    double a4[PSFM_MAX_SCALES] = {0.0, 0.0, 0.0, 0.0};
+    int umax = 0;
+    for (int s = 0; s < F.n; ++s) umax = max(umax, F.nunits[s]);
+    for (int i = k; i < umax; i += 21) {
+#pragma unroll
+      for (int s = 0; s < PSFM_MAX_SCALES; ++s)
+        if (s < F.n && i < F.nunits[s])
+          a4[s] += (double)((const real*)F.pose_part[s])[(((size_t)b * F.nunits[s] + i) * F.C + j) * 12 + e];
     }
+    for (int s = 0; s < F.n; ++s) a += a4[s];
   }
   sh[tid] = a;
   __syncthreads();
@@ -1328,6 +1338,7 @@ cudaError_t loss_stream_dispatch(const psfm_loss_cfg* cfg, const psfm_loss_io* i
                                  void* loss_out, cudaStream_t st) {
   if (cfg->real_dtype == PSFM_F64) return run_sweep<double, double>(cfg, io, ws_split, ws_stream, loss_out, st);
   if (cfg->img_dtype == PSFM_BF16) return run_sweep<float, __nv_bfloat16>(cfg, io, ws_split, ws_stream, loss_out, st);
+  if (cfg->img_dtype == PSFM_U8) return run_sweep<float, uint8_t>(cfg, io, ws_split, ws_stream, loss_out, st);
   return run_sweep<float, float>(cfg, io, ws_split, ws_stream, loss_out, st);
 }
 

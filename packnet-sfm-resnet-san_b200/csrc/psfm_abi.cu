@@ -83,8 +83,16 @@ static int check_cfg(const psfm_loss_cfg* c) {
   if (c->real_dtype != PSFM_F32 && c->real_dtype != PSFM_F64) return psfm_fail(PSFM_ERR_INVALID, "real_dtype must be f32|f64");
   if (c->real_dtype == PSFM_F64 && c->img_dtype != PSFM_F64)
     return psfm_fail(PSFM_ERR_INVALID, "f64 arithmetic requires f64 images");
-  if (c->real_dtype == PSFM_F32 && c->img_dtype != PSFM_F32 && c->img_dtype != PSFM_BF16)
-    return psfm_fail(PSFM_ERR_INVALID, "f32 arithmetic requires f32 or bf16 images");
+  if (c->real_dtype == PSFM_F32 && c->img_dtype != PSFM_F32 && c->img_dtype != PSFM_BF16 && c->img_dtype != PSFM_U8)
+    return psfm_fail(PSFM_ERR_INVALID, "f32 arithmetic requires f32, bf16 or u8 images");
+  if (c->img_dtype == PSFM_U8) {
+    bool ok = c->reduce_op == PSFM_REDUCE_MIN && c->ssim_w > 0.0 && !(c->clip_loss > 0.0) && c->C <= 8 && c->H >= 4 && c->W >= 4;
+    for (int s = 0; s < c->n; ++s) ok = ok && c->Hs[s] == c->H && c->Ws[s] == c->W;
+    if (!ok)
+      return psfm_fail(PSFM_ERR_INVALID, "u8 images are read by the sweep kernels only, with every scale at image resolution "
+                       "(photometric_reduce_op='min', ssim_loss_weight > 0, clip_loss = 0; inverse depths full-size or "
+                       "upsampled in-kernel); convert to float before the loss otherwise");
+  }
   if (c->padding != PSFM_PAD_ZEROS && c->padding != PSFM_PAD_BORDER)
     return psfm_fail(PSFM_ERR_INVALID, "padding must be zeros|border");
   if (c->reduce_op != PSFM_REDUCE_MIN && c->reduce_op != PSFM_REDUCE_MEAN)
@@ -175,6 +183,7 @@ int psfm_loss_forward(const psfm_loss_cfg* cfg, const psfm_loss_io* io, void* wo
       return psfm_fail(PSFM_ERR_INVALID, "in-kernel upsampling: use psfm_loss_forward_backward");
   }
   if (cfg->camera_model == PSFM_CAM_FISHEYE) return psfm_fail(PSFM_ERR_INVALID, "fisheye cameras: use psfm_loss_forward_backward");
+  if (cfg->img_dtype == PSFM_U8) return psfm_fail(PSFM_ERR_INVALID, "u8 images: use psfm_loss_forward_backward");
   if (!loss_out || !workspace) return psfm_fail(PSFM_ERR_INVALID, "loss_out / workspace is NULL");
   if (workspace_bytes < psfm::loss_workspace_bytes(cfg))
     return psfm_fail(PSFM_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes, psfm::loss_workspace_bytes(cfg));
@@ -192,6 +201,7 @@ int psfm_loss_backward(const psfm_loss_cfg* cfg, const psfm_loss_io* io, void* w
       return psfm_fail(PSFM_ERR_INVALID, "in-kernel upsampling: use psfm_loss_forward_backward");
   }
   if (cfg->camera_model == PSFM_CAM_FISHEYE) return psfm_fail(PSFM_ERR_INVALID, "fisheye cameras: use psfm_loss_forward_backward");
+  if (cfg->img_dtype == PSFM_U8) return psfm_fail(PSFM_ERR_INVALID, "u8 images: use psfm_loss_forward_backward");
   if (!grad_loss || !workspace) return psfm_fail(PSFM_ERR_INVALID, "grad_loss / workspace is NULL");
   if (workspace_bytes < psfm::loss_workspace_bytes(cfg))
     return psfm_fail(PSFM_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes, psfm::loss_workspace_bytes(cfg));

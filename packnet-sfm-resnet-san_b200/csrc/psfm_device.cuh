@@ -34,6 +34,17 @@ template <typename real, typename I> __device__ __forceinline__ real ldimg(const
   return (real)__bfloat162float(__ldg(p + i));
 }
 
+// bytes: value = byte / 255, correctly rounded (= torchvision to_tensor).  q = x * fl(1/255) is off by an ulp for
+// 126 of the 256 bytes; one residual correction makes all 256 exact (checked exhaustively).
+template <typename real, typename I> __device__ __forceinline__ real ldimg(const uint8_t* p, I i) {
+  const float x = (float)__ldg(p + i), c = 1.0f / 255.0f;
+  const float q = x * c;
+  return (real)fmaf(fmaf(-q, 255.0f, x), c, q);
+}
+// mask element: the value itself (a byte mask holds 0 / 1)
+template <typename real, typename T, typename I> __device__ __forceinline__ real ldmask(const T* p, I i) { return ldimg<real>(p, i); }
+template <typename real, typename I> __device__ __forceinline__ real ldmask(const uint8_t* p, I i) { return (real)__ldg(p + i); }
+
 // ReflectionPad2d(1) source index: -1 -> 1, n -> n-2 (losses/multiview_photometric_loss.py:34).
 // Positions further out (only touched by windows that are never evaluated) are clamped.
 __device__ __forceinline__ int reflect1(int i, int n) {

@@ -13,7 +13,7 @@ LIB_PATH = os.environ.get('PSFM_B200_LIB', os.path.join(os.path.dirname(_HERE), 
 
 MAX_SCALES = 4
 MAX_CTX = 8
-F32, BF16, F64 = 0, 1, 2
+F32, BF16, F64, U8 = 0, 1, 2, 3
 PAD = {'zeros': 0, 'border': 1}
 REDUCE = {'min': 0, 'mean': 1}
 CAM_PINHOLE, CAM_FISHEYE = 0, 1
@@ -147,7 +147,9 @@ def dtype_code(t):
         return BF16
     if t.dtype == torch.float64:
         return F64
-    raise ValueError('unsupported dtype %s (float32, bfloat16 or float64)' % t.dtype)
+    if t.dtype == torch.uint8:
+        return U8
+    raise ValueError('unsupported dtype %s (float32, bfloat16, float64 or uint8 image bytes)' % t.dtype)
 
 
 def require_cuda(*tensors):

@@ -113,6 +113,9 @@ class _LossPlan:
         io = _C.LossIO()
         keep = []
         image = image.contiguous()
+        self.u8 = img_dtype == torch.uint8
+        if self.u8 and any(c.dtype != torch.uint8 for c in context):
+            raise ValueError('uint8 images (bytes, value = byte / 255) need uint8 context frames')
         context = [c.to(img_dtype).contiguous() for c in context]
         for c in context:
             if tuple(c.shape) != (B, 3, H, W):
@@ -197,9 +200,9 @@ class _PhotometricLossFn(torch.autograd.Function):
         need_grad = any(t.requires_grad for t in tensors[Cn:])
         st = _C.stream_ptr(plan.dev)
         with torch.cuda.device(plan.dev):
-            if (plan.upsampled or plan.fisheye) and mode != 'fused':
-                raise NotImplementedError("upsample_depth_maps / fisheye cameras need kernel_mode='fused'")
-            if (need_grad or plan.upsampled or plan.fisheye) and mode == 'fused':
+            if (plan.upsampled or plan.fisheye or plan.u8) and mode != 'fused':
+                raise NotImplementedError("upsample_depth_maps / fisheye cameras / uint8 images need kernel_mode='fused'")
+            if (need_grad or plan.upsampled or plan.fisheye or plan.u8) and mode == 'fused':
                 plan.alloc_grads()
                 _C.check(_C.lib.psfm_loss_forward_backward(*plan.args(), _C.ptr(plan.out), st))
             else:

@@ -100,3 +100,49 @@ def test_in_kernel_upsampling_of_the_depth_pyramid(case):
         assert rel_l2(dg[s].grad.cpu(), d64[s].grad) <= (1e-8 if f64 else 1e-2), 'scale %d' % s
     for a, b in zip(vg, v64):
         assert rel_l2(a.grad.cpu(), b.grad) <= (1e-8 if f64 else 1e-2)
+
+
+@pytest.mark.parametrize('case', [dict(pm='zeros', mask=False, pyramid=False), dict(pm='border', mask=True, pyramid=False),
+                                  dict(pm='zeros', mask=False, pyramid=True)])
+def test_uint8_frames_are_bit_identical_to_to_tensor_floats(case):
+    """img_dtype PSFM_U8: the kernels read image bytes and apply torchvision's to_tensor (byte / 255) themselves.
+    The result must be bit-identical to feeding the float frames that to_tensor would have produced, for the loss
+    and every gradient (byte masks hold 0 / 1)."""
+    import torch.nn.functional as F
+    import photometric_oracle as O
+    from golden_cases import YAML_LOSS
+    from packnet_sfm.geometry.pose import Pose
+    from packnet_sfm.losses.multiview_photometric_loss import MultiViewPhotometricLoss
+    B, H, W, C = 2, 64, 160, 2
+    image, context, invd, vecs, K = O.synth_S3(B, H, W, C, torch.float32, pyramid=case['pyramid'], kd=7)
+    dev = 'cuda:0'
+    q = lambda t: (t * 255.0).round().clamp(0, 255).to(torch.uint8).to(dev)
+    img8, ctx8 = q(image), [q(c) for c in context]
+    # torchvision.transforms.functional.to_tensor, on the CPU like the reference's data pipeline: a true division
+    # (on a CUDA tensor torch turns div-by-scalar into a multiplication by 1/255, which is off by an ulp for 126 bytes)
+    to_tensor = lambda b: b.cpu().float().div(255).to(dev)
+    gm = torch.Generator('cpu').manual_seed(11)
+    mask = (torch.rand(B, 1, H, W, generator=gm) > 0.3) if case['mask'] else None
+    hp = dict(YAML_LOSS, padding_mode=case['pm'])
+    res = []
+    for as_bytes in (True, False):
+        d = [x.to(dev).clone().requires_grad_() for x in invd]
+        v = [x.to(dev).clone().requires_grad_() for x in vecs]
+        L = MultiViewPhotometricLoss(upsample_depth_maps=case['pyramid'], **hp)
+        m = None if mask is None else (mask.to(torch.uint8) if as_bytes else mask.float()).to(dev)
+        out = L(img8 if as_bytes else to_tensor(img8), ctx8 if as_bytes else [to_tensor(c) for c in ctx8], d,
+                K.to(dev), K.to(dev), [Pose.from_vec(x, 'euler') for x in v], mask=m)
+        out['loss'].backward()
+        torch.cuda.synchronize()
+        res.append((out['loss'].detach().clone(), [x.grad for x in d], [x.grad for x in v]))
+    assert torch.equal(res[0][0], res[1][0])
+    for a, b in zip(res[0][1] + res[0][2], res[1][1] + res[1][2]):
+        assert torch.equal(a, b)
+    # settings outside the sweep kernels are refused, not converted behind the caller's back
+    with pytest.raises(ValueError, match='u8 images'):
+        MultiViewPhotometricLoss(**dict(hp, photometric_reduce_op='mean', automask_loss=False))(
+            img8, ctx8, [x.to(dev) for x in invd][:1] * 4 if case['pyramid'] else [x.to(dev) for x in invd], K.to(dev), K.to(dev),
+            [Pose.from_vec(x.to(dev), 'euler') for x in vecs])
+    with pytest.raises(ValueError, match='uint8 context'):
+        MultiViewPhotometricLoss(**hp)(img8, [to_tensor(c) for c in ctx8], [x.to(dev) for x in invd][:1] * 4, K.to(dev),
+                                       K.to(dev), [Pose.from_vec(x.to(dev), 'euler') for x in vecs])
