@@ -1,0 +1,47 @@
+"""Generate tests/golden/supervised.npz from the REAL reference  --  TEST INFRASTRUCTURE, build container only.
+
+Runs the reference's own `SupervisedLoss` (losses/supervised_loss.py) in fp64 on the deterministic recipe
+`synth_supervised` (oracle/supervised_oracle.py) for the methods this library provides.
+
+    python oracle/gen_golden_supervised.py
+"""
+import contextlib
+import io
+import os
+
+import numpy as np
+import torch
+
+import gen_golden as G          # stubs yacs / matplotlib and puts /root/reference first on sys.path
+from packnet_sfm.losses.supervised_loss import SupervisedLoss  # noqa: E402
+from supervised_oracle import synth_supervised  # noqa: E402
+
+CASES = [(m, n, pyr, use_mask) for m in ('sparse-l1', 'sparse-mse', 'sparse-silog', 'l1', 'mse', 'silog')
+         for (n, pyr, use_mask) in ((1, False, False), (4, True, False), (2, False, True))
+         if not (use_mask and not m.startswith('sparse'))]
+
+
+def main():
+    out = {}
+    for method, n, pyr, use_mask in CASES:
+        preds, gt, masks = synth_supervised(2, 24, 40, n, pyramid=pyr)
+        if not method.startswith('sparse'):
+            gt = gt.clamp(min=0.02)                       # dense methods take the log of every pixel
+        preds = [p.requires_grad_() for p in preds]
+        with contextlib.redirect_stdout(io.StringIO()):  # the reference prints banners
+            L = SupervisedLoss(supervised_method=method, supervised_num_scales=n)
+            res = L(preds, gt, masks=[m.clone() for m in masks] if use_mask else None)
+        res['loss'].backward()
+        key = '%s_n%d_%s%s' % (method, n, 'P' if pyr else 'U', '_mask' if use_mask else '')
+        out[key + '/loss'] = res['loss'].detach().numpy()
+        for i, p in enumerate(preds):
+            out[key + '/d_pred%d' % i] = p.grad.numpy()
+        if method.startswith('sparse'):
+            out[key + '/valid_px'] = np.array([float(res['metrics']['s%d/valid_px' % i]) for i in range(n)])
+            out[key + '/scale_loss'] = np.array([float(res['metrics']['s%d/loss' % i]) for i in range(n)])
+    np.savez_compressed(os.path.join(G.ROOT, 'tests', 'golden', 'supervised.npz'), **out)
+    print('wrote supervised.npz with', len(out), 'arrays')
+
+
+if __name__ == '__main__':
+    main()

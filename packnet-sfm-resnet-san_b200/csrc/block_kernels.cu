@@ -301,6 +301,101 @@ __global__ void __launch_bounds__(kBT) grid_sample_bwd_kernel(int Hi, int Wi, si
 }
 
 // ------------------------------------------------------------------------------------------
+// SupervisedLoss.calculate_loss, one scale (reference losses/supervised_loss.py:292-417) with the loss functions
+// nn.L1Loss / nn.MSELoss / SilogLoss (:67-82, :84-92).
+//   sparse methods: valid = (gt > 0) [& mask]; pred and gt are masked_fill'ed with 1e-6 where not valid, and the
+//   loss function then averages over ALL N elements (:323-345); dense methods use every element as it is.
+//   l1: mean |p - g|;  mse: mean (p - g)^2;  silog: sqrt(mean(l^2) - ratio2 * mean(l)^2), l = log p - log g.
+// state (double[8], caller-owned, forward -> backward): {sum |d|, sum d^2, sum l, sum l^2, valid count, N, loss, 0}.
+// ------------------------------------------------------------------------------------------
+constexpr int kSupVals = 5;
+
+template <typename real>
+__device__ __forceinline__ bool sup_load(size_t i, int sparse, const real* pred, const real* gt, const uint8_t* mask,
+                                         real& p, real& g) {
+  p = pred[i]; g = gt[i];
+  const bool valid = !sparse || (g > real(0) && (!mask || mask[i] != 0));
+  if (!valid) { p = real(1e-6); g = real(1e-6); }
+  return valid;
+}
+
+template <typename real>
+__global__ void __launch_bounds__(kBT) sup_sums_kernel(size_t N, int method, int sparse, const real* pred, const real* gt,
+                                                       const uint8_t* mask, double* part) {
+  const size_t i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  __shared__ real scratch[kSupVals * (kBT / 32)];
+  real v[kSupVals];
+#pragma unroll
+  for (int k = 0; k < kSupVals; ++k) v[k] = real(0);
+  if (i < N) {
+    real p, g;
+    const bool valid = sup_load<real>(i, sparse, pred, gt, mask, p, g);
+    const real d = p - g;
+    v[0] = rabs(d);
+    v[1] = d * d;
+    if (method == PSFM_SUP_SILOG) {
+      const real l = log(p) - log(g);
+      v[2] = l; v[3] = l * l;
+    }
+    v[4] = valid ? real(1) : real(0);
+  }
+  block_reduce<real, kSupVals>(v, scratch);
+  if (threadIdx.x < kSupVals) part[(size_t)blockIdx.x * kSupVals + threadIdx.x] = (double)v[threadIdx.x];
+}
+
+template <typename real>
+__global__ void __launch_bounds__(256) sup_finish_kernel(const double* part, int nblk, size_t N, int method, double ratio2,
+                                                         double* state, real* loss_out) {
+  __shared__ double sh[kSupVals][256];
+  double a[kSupVals] = {0.0, 0.0, 0.0, 0.0, 0.0};
+  for (int i = threadIdx.x; i < nblk; i += 256)
+#pragma unroll
+    for (int k = 0; k < kSupVals; ++k) a[k] += part[(size_t)i * kSupVals + k];
+#pragma unroll
+  for (int k = 0; k < kSupVals; ++k) sh[k][threadIdx.x] = a[k];
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o)
+#pragma unroll
+      for (int k = 0; k < kSupVals; ++k) sh[k][threadIdx.x] += sh[k][threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const double n = (double)N;
+    double loss;
+    if (method == PSFM_SUP_L1) loss = sh[0][0] / n;
+    else if (method == PSFM_SUP_MSE) loss = sh[1][0] / n;
+    else { const double m = sh[2][0] / n; loss = sqrt(sh[3][0] / n - ratio2 * m * m); }
+#pragma unroll
+    for (int k = 0; k < kSupVals; ++k) state[k] = sh[k][0];
+    state[5] = n; state[6] = loss; state[7] = 0.0;
+    loss_out[0] = (real)loss;
+  }
+}
+
+template <typename real>
+__global__ void __launch_bounds__(kBT) sup_grad_kernel(size_t N, int method, int sparse, const real* pred, const real* gt,
+                                                       const uint8_t* mask, double ratio2, const double* state,
+                                                       const real* grad_loss, real* d_pred) {
+  const size_t i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  if (i >= N) return;
+  real p, g;
+  const bool valid = sup_load<real>(i, sparse, pred, gt, mask, p, g);
+  real out = real(0);
+  if (valid) {                                   // masked_fill: no gradient reaches a filled element
+    const real up = grad_loss[0], n = (real)state[5];
+    const real d = p - g;
+    if (method == PSFM_SUP_L1) out = up * rsign(d) / n;
+    else if (method == PSFM_SUP_MSE) out = up * real(2) * d / n;
+    else {
+      const real l = log(p) - log(g), m = (real)(state[2] / state[5]), loss = (real)state[6];
+      out = up * (l - (real)ratio2 * m) / (n * loss * p);
+    }
+  }
+  d_pred[i] = out;
+}
+
+// ------------------------------------------------------------------------------------------
 // Pose.transform_points: out = R X + t on [B,3,N]
 // ------------------------------------------------------------------------------------------
 template <typename real>
@@ -808,6 +903,34 @@ int psfm_grid_sample_backward(int B, int Hi, int Wi, int Ho, int Wo, int dt, int
   PSFM_DISPATCH(dt, (grid_sample_bwd_kernel<real><<<dim3(nblk_for(No), B), kBT, 0, (cudaStream_t)stream>>>(
                         Hi, Wi, No, padding, (const real*)image, (const real*)grid, (const real*)grad_out, (real*)d_grid)));
   return launch_result("psfm_grid_sample_backward");
+}
+
+int psfm_supervised_loss(int method, int sparse, size_t N, int dt, const void* pred, const void* gt, const void* mask,
+                         double ratio2, void* loss_out, void* state, void* ws, size_t ws_bytes, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(N >= 1 && pred && gt && loss_out && state && method >= PSFM_SUP_L1 && method <= PSFM_SUP_SILOG,
+                   "psfm_supervised_loss: bad argument");
+  if (!ws || ws_bytes < psfm_block_workspace_bytes(1, N)) return psfm_fail(PSFM_ERR_WORKSPACE, "psfm_supervised_loss: workspace too small");
+  const unsigned nb = nblk_for(N);
+  cudaStream_t st = (cudaStream_t)stream;
+  count_launches(2);
+  PSFM_DISPATCH(dt, {
+    sup_sums_kernel<real><<<nb, kBT, 0, st>>>(N, method, sparse, (const real*)pred, (const real*)gt, (const uint8_t*)mask, (double*)ws);
+    sup_finish_kernel<real><<<1, 256, 0, st>>>((const double*)ws, (int)nb, N, method, ratio2, (double*)state, (real*)loss_out);
+  });
+  return launch_result("psfm_supervised_loss");
+}
+
+int psfm_supervised_loss_backward(int method, int sparse, size_t N, int dt, const void* pred, const void* gt, const void* mask,
+                                  double ratio2, const void* state, const void* grad_loss, void* d_pred, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(N >= 1 && pred && gt && state && grad_loss && d_pred && method >= PSFM_SUP_L1 && method <= PSFM_SUP_SILOG,
+                   "psfm_supervised_loss_backward: bad argument");
+  count_launches(1);
+  PSFM_DISPATCH(dt, (sup_grad_kernel<real><<<nblk_for(N), kBT, 0, (cudaStream_t)stream>>>(
+                        N, method, sparse, (const real*)pred, (const real*)gt, (const uint8_t*)mask, ratio2,
+                        (const double*)state, (const real*)grad_loss, (real*)d_pred)));
+  return launch_result("psfm_supervised_loss_backward");
 }
 
 int psfm_pose_from_vec(int B, int dt, const void* vec, void* mat, void* stream) {

@@ -498,3 +498,56 @@ def smoothness_op(inv_depth, image):
     mean-normalised inverse depth, weighted by exp(-mean_c |image gradient|)."""
     _no_grad_supported(image, 'the image of calc_smoothness')
     return _SmoothMaps.apply(normalize_op(inv_depth), image)
+
+
+SUP_METHODS = {'l1': 0, 'mse': 1, 'silog': 2}
+
+
+class _SupervisedLoss(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, pred, gt, mask, method, sparse, ratio2):
+        _C.require_cuda(pred, gt, mask)
+        if pred.shape != gt.shape:
+            raise ValueError('prediction and ground truth must have the same shape')
+        pred = pred.contiguous()
+        gt = gt.to(pred.dtype).contiguous()
+        if mask is not None:
+            if mask.numel() != pred.numel():
+                raise ValueError('the mask must have one element per pixel')
+            mask = (mask if mask.dtype == torch.uint8 else (mask > 0).to(torch.uint8)).contiguous()
+        N = pred.numel()
+        out = torch.empty(1, dtype=pred.dtype, device=pred.device)
+        state = torch.empty(8, dtype=torch.float64, device=pred.device)
+        ws, n = _ws(1, N, pred.device)
+        with torch.cuda.device(pred.device):
+            _C.check(_C.lib.psfm_supervised_loss(method, int(sparse), N, _real(pred), _C.ptr(pred), _C.ptr(gt), _C.ptr(mask),
+                                                 float(ratio2), _C.ptr(out), _C.ptr(state), _C.ptr(ws), n,
+                                                 _C.stream_ptr(pred.device)))
+        ctx.save_for_backward(pred, gt, mask, state)
+        ctx.cfg = (method, int(sparse), float(ratio2))
+        ctx.mark_non_differentiable(state)
+        return out, state
+
+    @staticmethod
+    def backward(ctx, g, _gs=None):
+        pred, gt, mask, state = ctx.saved_tensors
+        method, sparse, ratio2 = ctx.cfg
+        g = g.to(pred.dtype).contiguous()
+        d_pred = torch.empty_like(pred)
+        with torch.cuda.device(pred.device):
+            _C.check(_C.lib.psfm_supervised_loss_backward(method, sparse, pred.numel(), _real(pred), _C.ptr(pred), _C.ptr(gt),
+                                                          _C.ptr(mask), ratio2, _C.ptr(state), _C.ptr(g), _C.ptr(d_pred),
+                                                          _C.stream_ptr(pred.device)))
+        return d_pred, None, None, None, None, None
+
+
+def supervised_loss_op(pred, gt, method, sparse=False, mask=None, ratio2=0.85):
+    """One scale of SupervisedLoss.calculate_loss (reference losses/supervised_loss.py:292-417) with the l1 / mse /
+    silog loss functions.  Returns (loss [], state [8] float64 = {sum|d|, sum d^2, sum l, sum l^2, valid count, N,
+    loss, 0}); differentiable w.r.t. `pred`."""
+    if method not in SUP_METHODS:
+        raise NotImplementedError('supervised loss function %r is not provided (l1, mse, silog)' % (method,))
+    _real(pred)
+    _no_grad_supported(gt, 'the ground truth')
+    out, state = _SupervisedLoss.apply(pred, gt, mask, SUP_METHODS[method], bool(sparse), ratio2)
+    return out[0], state

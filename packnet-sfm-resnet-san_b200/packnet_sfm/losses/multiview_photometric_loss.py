@@ -148,4 +148,4 @@ class MultiViewPhotometricLoss(LossBase):
         self.add_metric('photometric_loss', out[1])
         if self.smooth_loss_weight > 0.0:
             self.add_metric('smoothness_loss', out[2])
-        return {'loss': out[0:1], 'metrics': self.metrics}
+        return {'loss': out[0], 'metrics': self.metrics}

@@ -210,10 +210,14 @@ class _PhotometricLossFn(torch.autograd.Function):
         ctx.plan, ctx.mode, ctx.consumed = plan, mode, False
         ctx.counts = (n, Cn)
         out, plan.out = plan.out, None      # the node must not reference its own output (reference cycle)
-        return out
+        # loss [1] (differentiable) and the two logged parts as separate outputs: autograd hands backward the
+        # gradient of the loss itself, with no zeros + copy for a slice of a 3-vector
+        loss, photo, smooth = out[0:1], out[1], out[2]
+        ctx.mark_non_differentiable(photo, smooth)
+        return loss, photo, smooth
 
     @staticmethod
-    def backward(ctx, grad_out):
+    def backward(ctx, grad_out, _gp=None, _gs=None):
         plan, (n, Cn) = ctx.plan, ctx.counts
         g = grad_out.to(plan.real).contiguous()
         st = _C.stream_ptr(plan.dev)
@@ -232,8 +236,8 @@ class _PhotometricLossFn(torch.autograd.Function):
 
 
 def photometric_loss(hp, image, context, inv_depths, K, ref_K, pose_mats, mask=None, mode=None):
-    """Returns a [3] tensor {loss, photometric_loss, smoothness_loss}; element 0 carries the
-    gradient w.r.t. `inv_depths` and `pose_mats`."""
+    """Returns (loss [1], photometric_loss [], smoothness_loss []); the loss carries the gradient w.r.t.
+    `inv_depths` and `pose_mats`, the two parts are logged values."""
     mode = DEFAULT_MODE if mode is None else mode
     if mode not in ('fused', 'split'):
         raise ValueError('mode must be "fused" or "split"')

@@ -1,0 +1,20 @@
+"""Catalogue of tests/golden/supervised.npz (mirrors oracle/gen_golden_supervised.py)."""
+import torch
+
+CASES = [(m, n, pyr, use_mask) for m in ('sparse-l1', 'sparse-mse', 'sparse-silog', 'l1', 'mse', 'silog')
+         for (n, pyr, use_mask) in ((1, False, False), (4, True, False), (2, False, True))
+         if not (use_mask and not m.startswith('sparse'))]
+
+
+def key_of(case):
+    method, n, pyr, use_mask = case
+    return '%s_n%d_%s%s' % (method, n, 'P' if pyr else 'U', '_mask' if use_mask else '')
+
+
+def make_inputs(case, dtype=torch.float64):
+    from supervised_oracle import synth_supervised
+    method, n, pyr, use_mask = case
+    preds, gt, masks = synth_supervised(2, 24, 40, n, dtype, pyramid=pyr)
+    if not method.startswith('sparse'):
+        gt = gt.clamp(min=0.02)
+    return preds, gt, (masks if use_mask else None)

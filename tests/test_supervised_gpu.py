@@ -1,0 +1,72 @@
+"""SupervisedLoss with the l1 / mse / silog loss functions
+(reference losses/supervised_loss.py:67-92, :241-437) through psfm_supervised_loss[_backward].
+fp64 kernels against fixtures produced by the reference's own class; fp32 kernels against the fp64 oracle."""
+import numpy as np
+import pytest
+import torch
+
+import supervised_oracle as S
+from golden_cases import load_golden
+from supervised_cases import CASES, key_of, make_inputs
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(case, dtype):
+    from packnet_sfm.losses.supervised_loss import SupervisedLoss
+    preds, gt, masks = make_inputs(case, dtype)
+    dev = 'cuda:0'
+    preds = [p.to(dev).requires_grad_() for p in preds]
+    L = SupervisedLoss(supervised_method=case[0], supervised_num_scales=case[1])
+    out = L(preds, gt.to(dev), masks=None if masks is None else [m.to(dev) for m in masks])
+    out['loss'].backward()
+    torch.cuda.synchronize()
+    return out, preds
+
+
+@pytest.mark.parametrize('case', CASES, ids=[key_of(c) for c in CASES])
+def test_fp64_kernels_match_reference_fixtures(case):
+    gold = load_golden('supervised')
+    out, preds = _run(case, torch.float64)
+    k = key_of(case)
+    assert out['loss'].shape == (1,)
+    np.testing.assert_allclose(out['loss'].item(), gold[k + '/loss'][0], rtol=1e-12)
+    for i, p in enumerate(preds):
+        np.testing.assert_allclose(p.grad.cpu().numpy(), gold[k + '/d_pred%d' % i], rtol=1e-10, atol=1e-16)
+    if case[0].startswith('sparse'):
+        m = out['metrics']
+        np.testing.assert_allclose([m['s%d/valid_px' % i].item() for i in range(case[1])], gold[k + '/valid_px'])
+        np.testing.assert_allclose([m['s%d/loss' % i].item() for i in range(case[1])], gold[k + '/scale_loss'], rtol=1e-12)
+        assert abs(m['supervised_loss'].item() - out['loss'].item()) == 0
+
+
+@pytest.mark.parametrize('method', ['sparse-l1', 'sparse-mse', 'sparse-silog'])
+def test_fp32_kernels_at_full_size(method):
+    """640x192, batch 8, one scale (what the shipped yaml runs): fp32 kernels vs the fp64 oracle."""
+    preds, gt, _ = S.synth_supervised(8, 192, 640, 1, torch.float64, seed=5)
+    p64 = [p.clone().requires_grad_() for p in preds]
+    ref = S.supervised_loss(p64, gt, method, 1)
+    ref.backward()
+    from packnet_sfm.losses.supervised_loss import SupervisedLoss
+    dev = 'cuda:0'
+    p32 = [p.float().to(dev).requires_grad_() for p in preds]
+    out = SupervisedLoss(supervised_method=method, supervised_num_scales=1)(p32, gt.float().to(dev))
+    out['loss'].backward()
+    torch.cuda.synchronize()
+    assert abs(out['loss'].item() - ref.item()) <= 1e-5 * abs(ref.item())
+    g, g64 = p32[0].grad.double().cpu(), p64[0].grad
+    assert ((g - g64).norm() / g64.norm()).item() <= 1e-5
+    # deterministic: fixed-order partial sums
+    out2 = SupervisedLoss(supervised_method=method, supervised_num_scales=1)([p32[0].detach()], gt.float().to(dev))
+    assert torch.equal(out2['loss'], out['loss'].detach())
+
+
+def test_unsupported_methods_are_refused():
+    from packnet_sfm.losses.supervised_loss import SupervisedLoss, get_loss_func
+    for m in ('sparse-berhu', 'sparse-ssi-silog', 'sparse-ssi'):
+        with pytest.raises(NotImplementedError):
+            get_loss_func(m)
+    with pytest.raises(ValueError):
+        SupervisedLoss(supervised_method='sparse-huber')
+    with pytest.raises(RuntimeError, match='no CPU fallback'):
+        SupervisedLoss(supervised_method='l1', supervised_num_scales=1)([torch.rand(1, 1, 4, 4)], torch.rand(1, 1, 4, 4))
