@@ -208,17 +208,21 @@ int psfm_grid_sample_backward(int B, int Hi, int Wi, int Ho, int Wo, int dt, int
                               const void* grid, const void* grad_out, void* d_grid, void* stream);
 
 /* SupervisedLoss.calculate_loss for one scale (losses/supervised_loss.py:292-417) with the loss
- * functions get_loss_func returns for '...l1' / '...mse' / '...silog' (:84-92, SilogLoss :67-82).  sparse != 0: the
- * 'sparse-*' methods -- valid = gt > 0 (and mask != 0 when a [N] byte mask is given); pred and gt are filled with 1e-6
- * elsewhere and the mean still runs over all N elements, as the reference does.  pred, gt: [N] of type dt.
- * loss_out: real[1].  state: double[8], written by the forward call and read by the backward call
- * {sum|d|, sum d^2, sum l, sum l^2, valid count, N, loss, 0}.  Backward: d_pred[N] = grad_loss[0] * d loss / d pred.
+ * functions get_loss_func returns for '...l1' / '...mse' / '...silog' (:84-92, SilogLoss :67-82) and '...ssi-silog'
+ * (SSISilogLoss, losses/ssi_silog_loss.py:53-429, without its multi-scale gradient term, gradient_weight = 0).
+ * sparse != 0: the 'sparse-*' methods -- valid = gt > 0 (and mask != 0 when a [N] byte mask is given); pred and gt are
+ * filled with 1e-6 elsewhere and the mean still runs over all N elements, as the reference does; ssi-silog averages
+ * over the valid elements only.  pred, gt: [N] of type dt.  hp: HOST double[6] = {silog ratio2, ssi alpha, ssi weight,
+ * silog weight, depth clamp min, depth clamp max} (the last four: ssi-silog only).  loss_out: real[1].
+ * state: DEVICE double[16], written by the forward call, read by the backward call and by callers that log parts:
+ * {sum|d|, sum d^2, sum l, sum l^2, valid count, sum d, N, loss, ssi, silog, mean d, var d, silog1, silog2, sign, const}.
+ * Backward: d_pred[N] = grad_loss[0] * d loss / d pred.
  * ('...berhu' raises inside the reference itself, torch.cat of a 4-D and a 1-D tensor at :65, and is not provided.) */
-typedef enum psfm_sup_method { PSFM_SUP_L1 = 0, PSFM_SUP_MSE = 1, PSFM_SUP_SILOG = 2 } psfm_sup_method;
+typedef enum psfm_sup_method { PSFM_SUP_L1 = 0, PSFM_SUP_MSE = 1, PSFM_SUP_SILOG = 2, PSFM_SUP_SSI_SILOG = 3 } psfm_sup_method;
 int psfm_supervised_loss(int method, int sparse, size_t N, int dt, const void* pred, const void* gt, const void* mask,
-                         double ratio2, void* loss_out, void* state, void* workspace, size_t workspace_bytes, void* stream);
+                         const double* hp, void* loss_out, void* state, void* workspace, size_t workspace_bytes, void* stream);
 int psfm_supervised_loss_backward(int method, int sparse, size_t N, int dt, const void* pred, const void* gt, const void* mask,
-                                  double ratio2, const void* state, const void* grad_loss, void* d_pred, void* stream);
+                                  const double* hp, const void* state, const void* grad_loss, void* d_pred, void* stream);
 
 /* Pose.transform_points (geometry/pose.py:80-86): out[B,3,N] = R X + t.  Backward: dX, d_mat[B,4,4]. */
 int psfm_transform_points(int B, size_t N, int dt, const void* mat, const void* X, void* out, void* stream);

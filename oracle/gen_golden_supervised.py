@@ -16,9 +16,12 @@ import gen_golden as G          # stubs yacs / matplotlib and puts /root/referen
 from packnet_sfm.losses.supervised_loss import SupervisedLoss  # noqa: E402
 from supervised_oracle import synth_supervised  # noqa: E402
 
-CASES = [(m, n, pyr, use_mask) for m in ('sparse-l1', 'sparse-mse', 'sparse-silog', 'l1', 'mse', 'silog')
+CASES = [(m, n, pyr, use_mask) for m in ('sparse-l1', 'sparse-mse', 'sparse-silog', 'sparse-ssi-silog', 'l1', 'mse', 'silog')
          for (n, pyr, use_mask) in ((1, False, False), (4, True, False), (2, False, True))
          if not (use_mask and not m.startswith('sparse'))]
+
+
+EXTRA = {'sparse-ssi-silog': dict(min_depth=0.5, max_depth=30.0)}     # clamps some of the 2..40 m depths
 
 
 def main():
@@ -29,16 +32,20 @@ def main():
             gt = gt.clamp(min=0.02)                       # dense methods take the log of every pixel
         preds = [p.requires_grad_() for p in preds]
         with contextlib.redirect_stdout(io.StringIO()):  # the reference prints banners
-            L = SupervisedLoss(supervised_method=method, supervised_num_scales=n)
+            L = SupervisedLoss(supervised_method=method, supervised_num_scales=n, **EXTRA.get(method, {}))
             res = L(preds, gt, masks=[m.clone() for m in masks] if use_mask else None)
         res['loss'].backward()
         key = '%s_n%d_%s%s' % (method, n, 'P' if pyr else 'U', '_mask' if use_mask else '')
         out[key + '/loss'] = res['loss'].detach().numpy()
         for i, p in enumerate(preds):
-            out[key + '/d_pred%d' % i] = p.grad.numpy()
+            # a scale with fewer than 100 valid pixels returns a constant in SSISilogLoss: no gradient
+            out[key + '/d_pred%d' % i] = (torch.zeros_like(p) if p.grad is None else p.grad).numpy()
         if method.startswith('sparse'):
             out[key + '/valid_px'] = np.array([float(res['metrics']['s%d/valid_px' % i]) for i in range(n)])
             out[key + '/scale_loss'] = np.array([float(res['metrics']['s%d/loss' % i]) for i in range(n)])
+        if method.endswith('ssi-silog'):
+            for name in ('ssi_component', 'silog_component', 'ssi_mean', 'ssi_var', 'silog1', 'silog2'):
+                out[key + '/' + name] = np.array([float(res['metrics']['s%d/%s' % (i, name)]) for i in range(n)])
     np.savez_compressed(os.path.join(G.ROOT, 'tests', 'golden', 'supervised.npz'), **out)
     print('wrote supervised.npz with', len(out), 'arrays')
 

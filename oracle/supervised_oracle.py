@@ -20,10 +20,26 @@ def loss_function(pred, gt, method, ratio2=0.85):
     raise NotImplementedError(method)
 
 
-def supervised_loss(inv_depths, gt_inv_depth, supervised_method, num_scales, masks=None):
+def ssi_silog(pred, gt, mask, alpha=0.85, ratio2=0.85, ssi_weight=0.7, silog_weight=0.3, min_depth=None, max_depth=None):
+    """`SSISilogLoss.forward` with gradient_weight = 0 (losses/ssi_silog_loss.py:176-197, :218-262, :366-429)."""
+    if mask.sum() < 100:
+        return torch.zeros((), dtype=pred.dtype)
+    d = pred[mask] - gt[mask]
+    mean = d.mean()
+    ssi = ((d ** 2).mean() - mean ** 2) + alpha * mean ** 2
+    cmin = 1e-3 if min_depth is None else float(min_depth)
+    cmax = 100.0 if max_depth is None else float(max_depth)
+    P = (1. / pred.clamp(min=1e-6)).clamp(min=cmin, max=cmax)[mask]
+    G = (1. / gt.clamp(min=1e-6)).clamp(min=cmin, max=cmax)[mask]
+    l = torch.log(P) - torch.log(G)
+    silog = torch.sqrt(((l ** 2).mean() - ratio2 * l.mean() ** 2).abs() + 1e-8)
+    return ssi_weight * ssi + silog_weight * silog
+
+
+def supervised_loss(inv_depths, gt_inv_depth, supervised_method, num_scales, masks=None, **kw):
     """`SupervisedLoss.forward` (:420-437): ground truth matched to every scale with nearest interpolation
     (utils/image.py:178-214), sparse methods fill invalid pixels of both maps with 1e-6 (:323-345)."""
-    method = supervised_method.split('-')[-1]
+    method = 'ssi-silog' if supervised_method.endswith('ssi-silog') else supervised_method.split('-')[-1]
     sparse = supervised_method.startswith('sparse')
     total = 0.0
     for i in range(num_scales):
@@ -35,6 +51,9 @@ def supervised_loss(inv_depths, gt_inv_depth, supervised_method, num_scales, mas
             if masks is not None and masks[i] is not None:
                 valid = valid & masks[i]
             p, g = p.masked_fill(~valid, 1e-6), g.masked_fill(~valid, 1e-6)
+        if method == 'ssi-silog':
+            total = total + ssi_silog(p, g, valid if sparse else (1. / g.clamp(min=1e-6)) > 0, **kw)
+            continue
         total = total + loss_function(p, g, method)
     return total / float(num_scales)
 

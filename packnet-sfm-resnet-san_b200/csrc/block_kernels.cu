@@ -302,26 +302,47 @@ __global__ void __launch_bounds__(kBT) grid_sample_bwd_kernel(int Hi, int Wi, si
 
 // ------------------------------------------------------------------------------------------
 // SupervisedLoss.calculate_loss, one scale (reference losses/supervised_loss.py:292-417) with the loss functions
-// nn.L1Loss / nn.MSELoss / SilogLoss (:67-82, :84-92).
+// nn.L1Loss / nn.MSELoss / SilogLoss (:67-82, :84-92) and SSISilogLoss (losses/ssi_silog_loss.py:53-429).
 //   sparse methods: valid = (gt > 0) [& mask]; pred and gt are masked_fill'ed with 1e-6 where not valid, and the
 //   loss function then averages over ALL N elements (:323-345); dense methods use every element as it is.
 //   l1: mean |p - g|;  mse: mean (p - g)^2;  silog: sqrt(mean(l^2) - ratio2 * mean(l)^2), l = log p - log g.
-// state (double[8], caller-owned, forward -> backward): {sum |d|, sum d^2, sum l, sum l^2, valid count, N, loss, 0}.
+//   ssi-silog: means over the M valid elements only; ssi = var(d) + alpha mean(d)^2 on inverse depths (:176-197),
+//   silog = sqrt(|mean(l^2) - ratio2 mean(l)^2| + 1e-8) with l = log P - log G on depths P = 1 / max(p, 1e-6) clamped to
+//   [cmin, cmax] (:218-262); loss = w_ssi ssi + w_silog silog (:413-415); 0 when M < 100 (:398-400), 1 (constant) when
+//   a NaN shows up (:403-408).  The multi-scale gradient term (gradient_weight, default 0) is not provided.
+// hp (host, double[6]): {ratio2, alpha, w_ssi, w_silog, cmin, cmax}.
+// state (double[16], caller-owned, forward -> backward):
+//   {sum |d|, sum d^2, sum l, sum l^2, valid count M, sum d, N, loss, ssi, silog, mean d, var d, mean l^2, ratio2 mean(l)^2,
+//    sign of the silog radicand, 1 if the loss is a constant (no gradient)}.
 // ------------------------------------------------------------------------------------------
-constexpr int kSupVals = 5;
+constexpr int kSupVals = 6;
+struct SupHp { double ratio2, alpha, w_ssi, w_silog, cmin, cmax; };
 
 template <typename real>
-__device__ __forceinline__ bool sup_load(size_t i, int sparse, const real* pred, const real* gt, const uint8_t* mask,
-                                         real& p, real& g) {
+__device__ __forceinline__ bool sup_load(size_t i, int method, int sparse, const real* pred, const real* gt,
+                                         const uint8_t* mask, real& p, real& g) {
   p = pred[i]; g = gt[i];
-  const bool valid = !sparse || (g > real(0) && (!mask || mask[i] != 0));
+  const bool valid = !(sparse || method == PSFM_SUP_SSI_SILOG) || (g > real(0) && (!mask || mask[i] != 0));
   if (!valid) { p = real(1e-6); g = real(1e-6); }
   return valid;
 }
 
+// log-difference of the method; dl = d l / d p
+template <typename real>
+__device__ __forceinline__ real sup_logdiff(int method, real p, real g, real cmin, real cmax, real& dl) {
+  if (method == PSFM_SUP_SSI_SILOG) {
+    const real P0 = real(1) / rmax(p, real(1e-6)), G0 = real(1) / rmax(g, real(1e-6));      // inv2depth
+    const real P = rmin(rmax(P0, cmin), cmax), G = rmin(rmax(G0, cmin), cmax);
+    dl = (p >= real(1e-6) && P0 >= cmin && P0 <= cmax) ? real(-1) / p : real(0);
+    return log(P) - log(G);
+  }
+  dl = real(1) / p;
+  return log(p) - log(g);
+}
+
 template <typename real>
 __global__ void __launch_bounds__(kBT) sup_sums_kernel(size_t N, int method, int sparse, const real* pred, const real* gt,
-                                                       const uint8_t* mask, double* part) {
+                                                       const uint8_t* mask, SupHp hp, double* part) {
   const size_t i = (size_t)blockIdx.x * kBT + threadIdx.x;
   __shared__ real scratch[kSupVals * (kBT / 32)];
   real v[kSupVals];
@@ -329,25 +350,29 @@ __global__ void __launch_bounds__(kBT) sup_sums_kernel(size_t N, int method, int
   for (int k = 0; k < kSupVals; ++k) v[k] = real(0);
   if (i < N) {
     real p, g;
-    const bool valid = sup_load<real>(i, sparse, pred, gt, mask, p, g);
+    const bool valid = sup_load<real>(i, method, sparse, pred, gt, mask, p, g);
     const real d = p - g;
     v[0] = rabs(d);
     v[1] = d * d;
-    if (method == PSFM_SUP_SILOG) {
-      const real l = log(p) - log(g);
+    if (method >= PSFM_SUP_SILOG && (valid || method == PSFM_SUP_SILOG)) {
+      real dl;
+      const real l = sup_logdiff<real>(method, p, g, (real)hp.cmin, (real)hp.cmax, dl);
       v[2] = l; v[3] = l * l;
     }
     v[4] = valid ? real(1) : real(0);
+    v[5] = d;
   }
   block_reduce<real, kSupVals>(v, scratch);
   if (threadIdx.x < kSupVals) part[(size_t)blockIdx.x * kSupVals + threadIdx.x] = (double)v[threadIdx.x];
 }
 
 template <typename real>
-__global__ void __launch_bounds__(256) sup_finish_kernel(const double* part, int nblk, size_t N, int method, double ratio2,
+__global__ void __launch_bounds__(256) sup_finish_kernel(const double* part, int nblk, size_t N, int method, SupHp hp,
                                                          double* state, real* loss_out) {
   __shared__ double sh[kSupVals][256];
-  double a[kSupVals] = {0.0, 0.0, 0.0, 0.0, 0.0};
+  double a[kSupVals];
+#pragma unroll
+  for (int k = 0; k < kSupVals; ++k) a[k] = 0.0;
   for (int i = threadIdx.x; i < nblk; i += 256)
 #pragma unroll
     for (int k = 0; k < kSupVals; ++k) a[k] += part[(size_t)i * kSupVals + k];
@@ -362,34 +387,58 @@ __global__ void __launch_bounds__(256) sup_finish_kernel(const double* part, int
   }
   if (threadIdx.x == 0) {
     const double n = (double)N;
-    double loss;
+    double loss, st[8] = {0, 0, 0, 0, 0, 0, 1.0, 0};   // ssi, silog, mean d, var d, silog1, silog2, sign, constant
     if (method == PSFM_SUP_L1) loss = sh[0][0] / n;
     else if (method == PSFM_SUP_MSE) loss = sh[1][0] / n;
-    else { const double m = sh[2][0] / n; loss = sqrt(sh[3][0] / n - ratio2 * m * m); }
+    else if (method == PSFM_SUP_SILOG) { const double m = sh[2][0] / n; loss = sqrt(sh[3][0] / n - hp.ratio2 * m * m); }
+    else {
+      const double M = sh[4][0];
+      const double md = sh[5][0] / M, var = sh[1][0] / M - md * md;
+      const double ml = sh[2][0] / M, s1 = sh[3][0] / M, s2 = hp.ratio2 * ml * ml;
+      double rad = s1 - s2;
+      st[6] = rad < 0.0 ? -1.0 : 1.0;
+      rad = rad < 0.0 ? -rad : rad;
+      st[0] = var + hp.alpha * md * md; st[1] = sqrt(rad + 1e-8);
+      st[2] = md; st[3] = var; st[4] = s1; st[5] = s2;
+      loss = hp.w_ssi * st[0] + hp.w_silog * st[1];
+      if (M < 100.0) { loss = 0.0; st[7] = 1.0; }
+      else if (loss != loss) { loss = 1.0; st[7] = 1.0; }
+    }
 #pragma unroll
     for (int k = 0; k < kSupVals; ++k) state[k] = sh[k][0];
-    state[5] = n; state[6] = loss; state[7] = 0.0;
+    state[6] = n; state[7] = loss;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) state[8 + k] = st[k];
     loss_out[0] = (real)loss;
   }
 }
 
 template <typename real>
 __global__ void __launch_bounds__(kBT) sup_grad_kernel(size_t N, int method, int sparse, const real* pred, const real* gt,
-                                                       const uint8_t* mask, double ratio2, const double* state,
+                                                       const uint8_t* mask, SupHp hp, const double* state,
                                                        const real* grad_loss, real* d_pred) {
   const size_t i = (size_t)blockIdx.x * kBT + threadIdx.x;
   if (i >= N) return;
   real p, g;
-  const bool valid = sup_load<real>(i, sparse, pred, gt, mask, p, g);
+  const bool valid = sup_load<real>(i, method, sparse, pred, gt, mask, p, g);
   real out = real(0);
-  if (valid) {                                   // masked_fill: no gradient reaches a filled element
-    const real up = grad_loss[0], n = (real)state[5];
+  if (valid && state[15] == 0.0) {               // masked_fill / masked selection: no gradient reaches an invalid element
+    const real up = grad_loss[0], n = (real)state[6];
     const real d = p - g;
     if (method == PSFM_SUP_L1) out = up * rsign(d) / n;
     else if (method == PSFM_SUP_MSE) out = up * real(2) * d / n;
     else {
-      const real l = log(p) - log(g), m = (real)(state[2] / state[5]), loss = (real)state[6];
-      out = up * (l - (real)ratio2 * m) / (n * loss * p);
+      real dl;
+      const real l = sup_logdiff<real>(method, p, g, (real)hp.cmin, (real)hp.cmax, dl);
+      if (method == PSFM_SUP_SILOG) {
+        const real m = (real)(state[2] / state[6]), loss = (real)state[7];
+        out = up * (l - (real)hp.ratio2 * m) / (n * loss) * dl;
+      } else {
+        const real M = (real)state[4], md = (real)state[10], ml = (real)(state[2] / state[4]);
+        const real g_ssi = real(2) * (d - (real)(1.0 - hp.alpha) * md) / M;
+        const real g_sil = (real)state[14] * (l - (real)hp.ratio2 * ml) / (M * (real)state[9]) * dl;
+        out = up * ((real)hp.w_ssi * g_ssi + (real)hp.w_silog * g_sil);
+      }
     }
   }
   d_pred[i] = out;
@@ -906,29 +955,33 @@ int psfm_grid_sample_backward(int B, int Hi, int Wi, int Ho, int Wo, int dt, int
 }
 
 int psfm_supervised_loss(int method, int sparse, size_t N, int dt, const void* pred, const void* gt, const void* mask,
-                         double ratio2, void* loss_out, void* state, void* ws, size_t ws_bytes, void* stream) {
+                         const double* hp, void* loss_out, void* state, void* ws, size_t ws_bytes, void* stream) {
   PSFM_DT_CHECK(dt);
-  PSFM_BLOCK_CHECK(N >= 1 && pred && gt && loss_out && state && method >= PSFM_SUP_L1 && method <= PSFM_SUP_SILOG,
+  PSFM_BLOCK_CHECK(N >= 1 && pred && gt && hp && loss_out && state && method >= PSFM_SUP_L1 && method <= PSFM_SUP_SSI_SILOG,
                    "psfm_supervised_loss: bad argument");
   if (!ws || ws_bytes < psfm_block_workspace_bytes(1, N)) return psfm_fail(PSFM_ERR_WORKSPACE, "psfm_supervised_loss: workspace too small");
+  SupHp h = {hp[0], hp[1], hp[2], hp[3], hp[4], hp[5]};
+  if (h.cmax <= h.cmin) h.cmax = h.cmin + 1.0;                 // losses/ssi_silog_loss.py:227-228
   const unsigned nb = nblk_for(N);
   cudaStream_t st = (cudaStream_t)stream;
   count_launches(2);
   PSFM_DISPATCH(dt, {
-    sup_sums_kernel<real><<<nb, kBT, 0, st>>>(N, method, sparse, (const real*)pred, (const real*)gt, (const uint8_t*)mask, (double*)ws);
-    sup_finish_kernel<real><<<1, 256, 0, st>>>((const double*)ws, (int)nb, N, method, ratio2, (double*)state, (real*)loss_out);
+    sup_sums_kernel<real><<<nb, kBT, 0, st>>>(N, method, sparse, (const real*)pred, (const real*)gt, (const uint8_t*)mask, h, (double*)ws);
+    sup_finish_kernel<real><<<1, 256, 0, st>>>((const double*)ws, (int)nb, N, method, h, (double*)state, (real*)loss_out);
   });
   return launch_result("psfm_supervised_loss");
 }
 
 int psfm_supervised_loss_backward(int method, int sparse, size_t N, int dt, const void* pred, const void* gt, const void* mask,
-                                  double ratio2, const void* state, const void* grad_loss, void* d_pred, void* stream) {
+                                  const double* hp, const void* state, const void* grad_loss, void* d_pred, void* stream) {
   PSFM_DT_CHECK(dt);
-  PSFM_BLOCK_CHECK(N >= 1 && pred && gt && state && grad_loss && d_pred && method >= PSFM_SUP_L1 && method <= PSFM_SUP_SILOG,
+  PSFM_BLOCK_CHECK(N >= 1 && pred && gt && hp && state && grad_loss && d_pred && method >= PSFM_SUP_L1 && method <= PSFM_SUP_SSI_SILOG,
                    "psfm_supervised_loss_backward: bad argument");
+  SupHp h = {hp[0], hp[1], hp[2], hp[3], hp[4], hp[5]};
+  if (h.cmax <= h.cmin) h.cmax = h.cmin + 1.0;
   count_launches(1);
   PSFM_DISPATCH(dt, (sup_grad_kernel<real><<<nblk_for(N), kBT, 0, (cudaStream_t)stream>>>(
-                        N, method, sparse, (const real*)pred, (const real*)gt, (const uint8_t*)mask, ratio2,
+                        N, method, sparse, (const real*)pred, (const real*)gt, (const uint8_t*)mask, h,
                         (const double*)state, (const real*)grad_loss, (real*)d_pred)));
   return launch_result("psfm_supervised_loss_backward");
 }

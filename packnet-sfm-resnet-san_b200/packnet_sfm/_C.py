@@ -103,8 +103,8 @@ def _load():
             ('psfm_fisheye_project_backward', [i, sz, i, i, i, vp, vp, vp, vp, vp]),
             ('psfm_grid_sample', [i, i, i, i, i, i, i, vp, vp, vp, vp]),
             ('psfm_grid_sample_backward', [i, i, i, i, i, i, i, vp, vp, vp, vp, vp]),
-            ('psfm_supervised_loss', [i, i, sz, i, vp, vp, vp, d, vp, vp, vp, sz, vp]),
-            ('psfm_supervised_loss_backward', [i, i, sz, i, vp, vp, vp, d, vp, vp, vp, vp]),
+            ('psfm_supervised_loss', [i, i, sz, i, vp, vp, vp, C.POINTER(d), vp, vp, vp, sz, vp]),
+            ('psfm_supervised_loss_backward', [i, i, sz, i, vp, vp, vp, C.POINTER(d), vp, vp, vp, vp]),
             ('psfm_transform_points', [i, sz, i, vp, vp, vp, vp]),
             ('psfm_transform_points_backward', [i, sz, i, vp, vp, vp, vp, vp, vp, sz, vp]),
             ('psfm_photometric_map', [i, i, i, i, i, d, d, d, vp, vp, vp, vp]),

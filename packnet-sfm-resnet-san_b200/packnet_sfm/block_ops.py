@@ -500,12 +500,15 @@ def smoothness_op(inv_depth, image):
     return _SmoothMaps.apply(normalize_op(inv_depth), image)
 
 
-SUP_METHODS = {'l1': 0, 'mse': 1, 'silog': 2}
+SUP_METHODS = {'l1': 0, 'mse': 1, 'silog': 2, 'ssi-silog': 3}
+SUP_STATE = ('sum_abs', 'sum_sq', 'sum_log', 'sum_log_sq', 'valid', 'sum_diff', 'count', 'loss', 'ssi', 'silog', 'ssi_mean',
+             'ssi_var', 'silog1', 'silog2', 'silog_sign', 'constant')
 
 
 class _SupervisedLoss(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, pred, gt, mask, method, sparse, ratio2):
+    def forward(ctx, pred, gt, mask, method, sparse, hp):
+        import ctypes
         _C.require_cuda(pred, gt, mask)
         if pred.shape != gt.shape:
             raise ValueError('prediction and ground truth must have the same shape')
@@ -517,37 +520,39 @@ class _SupervisedLoss(torch.autograd.Function):
             mask = (mask if mask.dtype == torch.uint8 else (mask > 0).to(torch.uint8)).contiguous()
         N = pred.numel()
         out = torch.empty(1, dtype=pred.dtype, device=pred.device)
-        state = torch.empty(8, dtype=torch.float64, device=pred.device)
+        state = torch.empty(16, dtype=torch.float64, device=pred.device)
         ws, n = _ws(1, N, pred.device)
+        hp_c = (ctypes.c_double * 6)(*[float(x) for x in hp])
         with torch.cuda.device(pred.device):
             _C.check(_C.lib.psfm_supervised_loss(method, int(sparse), N, _real(pred), _C.ptr(pred), _C.ptr(gt), _C.ptr(mask),
-                                                 float(ratio2), _C.ptr(out), _C.ptr(state), _C.ptr(ws), n,
-                                                 _C.stream_ptr(pred.device)))
+                                                 hp_c, _C.ptr(out), _C.ptr(state), _C.ptr(ws), n, _C.stream_ptr(pred.device)))
         ctx.save_for_backward(pred, gt, mask, state)
-        ctx.cfg = (method, int(sparse), float(ratio2))
+        ctx.cfg = (method, int(sparse), hp_c)
         ctx.mark_non_differentiable(state)
         return out, state
 
     @staticmethod
     def backward(ctx, g, _gs=None):
         pred, gt, mask, state = ctx.saved_tensors
-        method, sparse, ratio2 = ctx.cfg
+        method, sparse, hp_c = ctx.cfg
         g = g.to(pred.dtype).contiguous()
         d_pred = torch.empty_like(pred)
         with torch.cuda.device(pred.device):
             _C.check(_C.lib.psfm_supervised_loss_backward(method, sparse, pred.numel(), _real(pred), _C.ptr(pred), _C.ptr(gt),
-                                                          _C.ptr(mask), ratio2, _C.ptr(state), _C.ptr(g), _C.ptr(d_pred),
+                                                          _C.ptr(mask), hp_c, _C.ptr(state), _C.ptr(g), _C.ptr(d_pred),
                                                           _C.stream_ptr(pred.device)))
         return d_pred, None, None, None, None, None
 
 
-def supervised_loss_op(pred, gt, method, sparse=False, mask=None, ratio2=0.85):
+def supervised_loss_op(pred, gt, method, sparse=False, mask=None, ratio2=0.85, alpha=0.85, ssi_weight=0.7,
+                       silog_weight=0.3, clamp_min=1e-3, clamp_max=100.0):
     """One scale of SupervisedLoss.calculate_loss (reference losses/supervised_loss.py:292-417) with the l1 / mse /
-    silog loss functions.  Returns (loss [], state [8] float64 = {sum|d|, sum d^2, sum l, sum l^2, valid count, N,
-    loss, 0}); differentiable w.r.t. `pred`."""
+    silog / ssi-silog loss functions.  Returns (loss [], state [16] float64, fields named by SUP_STATE);
+    differentiable w.r.t. `pred`."""
     if method not in SUP_METHODS:
-        raise NotImplementedError('supervised loss function %r is not provided (l1, mse, silog)' % (method,))
+        raise NotImplementedError('supervised loss function %r is not provided (%s)' % (method, ', '.join(SUP_METHODS)))
     _real(pred)
     _no_grad_supported(gt, 'the ground truth')
-    out, state = _SupervisedLoss.apply(pred, gt, mask, SUP_METHODS[method], bool(sparse), ratio2)
+    hp = (ratio2, alpha, ssi_weight, silog_weight, clamp_min, clamp_max)
+    out, state = _SupervisedLoss.apply(pred, gt, mask, SUP_METHODS[method], bool(sparse), hp)
     return out[0], state

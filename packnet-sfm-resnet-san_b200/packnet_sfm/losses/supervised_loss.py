@@ -1,11 +1,11 @@
 """Supervised loss for inverse depth maps (reference: losses/supervised_loss.py).
 
 Provided: `SupervisedLoss` with the loss functions the reference's `get_loss_func` returns for the methods
-ending in 'l1', 'mse' and 'silog' ('sparse-' and dense forms) -- what `train_resnet_san_kitti.yaml`,
-`train_packnet_san_kitti.yaml` and `train_packnet_san_ddad.yaml` run every step (`supervised_method:
-'sparse-silog'`).  Each scale is two reduction kernels forward and one kernel backward through the C ABI
+ending in 'l1', 'mse', 'silog' and 'ssi-silog' ('sparse-' and dense forms) -- what `train_resnet_san_kitti.yaml`,
+`train_packnet_san_kitti.yaml`, `train_packnet_san_ddad.yaml` (`supervised_method: 'sparse-silog'`) and the NCDB yamls
+(`'sparse-ssi-silog'`) run every step.  Each scale is two reduction kernels forward and one kernel backward through the C ABI
 (`psfm_supervised_loss[_backward]`).  Not provided: 'berhu' (the reference's own BerHuLoss raises, :65) and the
-SSI / SSI-Silog / dual-head families (separate loss modules of the fork)."""
+other SSI / dual-head families (separate loss modules of the fork)."""
 import torch.nn as nn
 
 from packnet_sfm.losses.loss_base import LossBase, ProgressiveScaling
@@ -49,8 +49,16 @@ def get_loss_func(supervised_method, **kwargs):
         return L1Loss()
     elif supervised_method.endswith('mse'):
         return MSELoss()
-    elif supervised_method.endswith('ssi-silog') or 'ssi' in supervised_method:
-        raise NotImplementedError('the SSI loss families are outside this library (method %s)' % supervised_method)
+    elif supervised_method.endswith('ssi-silog'):
+        from packnet_sfm.losses.ssi_silog_loss import SSISilogLoss
+        return SSISilogLoss(min_depth=kwargs.get('min_depth', None), max_depth=kwargs.get('max_depth', None),
+                            ssi_weight=kwargs.get('ssi_weight', 0.7), silog_weight=kwargs.get('silog_weight', 0.3),
+                            alpha=kwargs.get('alpha', 0.85), silog_ratio=kwargs.get('silog_ratio', 10),
+                            silog_ratio2=kwargs.get('silog_ratio2', 0.85),
+                            gradient_weight=kwargs.get('gradient_weight', 0.0),
+                            gradient_scales=kwargs.get('gradient_scales', 4))
+    elif 'ssi' in supervised_method:
+        raise NotImplementedError('the other SSI loss families are outside this library (method %s)' % supervised_method)
     elif supervised_method.endswith('silog'):
         return SilogLoss()
     elif supervised_method.endswith('berhu'):
@@ -96,7 +104,10 @@ class SupervisedLoss(LossBase):
                 state = self.loss_func.state
                 self.add_metric('s%d/loss' % i, loss_i)
                 self.add_metric('s%d/valid_px' % i, state[4])
-                self.add_metric('s%d/valid_ratio' % i, state[4] / state[5])
+                self.add_metric('s%d/valid_ratio' % i, state[4] / state[6])
+                if isinstance(self.loss_func, LossBase):          # e.g. SSISilogLoss: copy its parts (:358-360)
+                    for k, v in self.loss_func.metrics.items():
+                        self.add_metric('s%d/%s' % (i, k), v)
             total_loss = total_loss + loss_i
         return total_loss / float(num_scales)
 

@@ -1,9 +1,11 @@
 """Catalogue of tests/golden/supervised.npz (mirrors oracle/gen_golden_supervised.py)."""
 import torch
 
-CASES = [(m, n, pyr, use_mask) for m in ('sparse-l1', 'sparse-mse', 'sparse-silog', 'l1', 'mse', 'silog')
+CASES = [(m, n, pyr, use_mask) for m in ('sparse-l1', 'sparse-mse', 'sparse-silog', 'sparse-ssi-silog', 'l1', 'mse', 'silog')
          for (n, pyr, use_mask) in ((1, False, False), (4, True, False), (2, False, True))
          if not (use_mask and not m.startswith('sparse'))]
+
+EXTRA = {'sparse-ssi-silog': dict(min_depth=0.5, max_depth=30.0)}
 
 
 def key_of(case):

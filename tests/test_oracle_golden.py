@@ -139,14 +139,15 @@ def test_supervised_oracle_matches_reference():
     """oracle/supervised_oracle.py against the reference's own SupervisedLoss (fp64)."""
     import supervised_oracle as S
     from golden_cases import load_golden
-    from supervised_cases import CASES as SUP, key_of, make_inputs as sup_inputs
+    from supervised_cases import CASES as SUP, EXTRA, key_of, make_inputs as sup_inputs
     gold = load_golden('supervised')
     for case in SUP:
         preds, gt, masks = sup_inputs(case)
         preds = [p.requires_grad_() for p in preds]
-        loss = S.supervised_loss(preds, gt, case[0], case[1], masks)
+        loss = S.supervised_loss(preds, gt, case[0], case[1], masks, **EXTRA.get(case[0], {}))
         loss.backward()
         k = key_of(case)
         np.testing.assert_allclose(loss.item(), gold[k + '/loss'][0], rtol=1e-12)
         for i, p in enumerate(preds):
-            np.testing.assert_allclose(p.grad.numpy(), gold[k + '/d_pred%d' % i], rtol=1e-10, atol=1e-16)
+            got = torch.zeros_like(p) if p.grad is None else p.grad
+            np.testing.assert_allclose(got.numpy(), gold[k + '/d_pred%d' % i], rtol=1e-10, atol=1e-16)

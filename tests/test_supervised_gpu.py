@@ -7,7 +7,7 @@ import torch
 
 import supervised_oracle as S
 from golden_cases import load_golden
-from supervised_cases import CASES, key_of, make_inputs
+from supervised_cases import CASES, EXTRA, key_of, make_inputs
 
 pytestmark = pytest.mark.gpu
 
@@ -17,7 +17,7 @@ def _run(case, dtype):
     preds, gt, masks = make_inputs(case, dtype)
     dev = 'cuda:0'
     preds = [p.to(dev).requires_grad_() for p in preds]
-    L = SupervisedLoss(supervised_method=case[0], supervised_num_scales=case[1])
+    L = SupervisedLoss(supervised_method=case[0], supervised_num_scales=case[1], **EXTRA.get(case[0], {}))
     out = L(preds, gt.to(dev), masks=None if masks is None else [m.to(dev) for m in masks])
     out['loss'].backward()
     torch.cuda.synchronize()
@@ -38,9 +38,15 @@ def test_fp64_kernels_match_reference_fixtures(case):
         np.testing.assert_allclose([m['s%d/valid_px' % i].item() for i in range(case[1])], gold[k + '/valid_px'])
         np.testing.assert_allclose([m['s%d/loss' % i].item() for i in range(case[1])], gold[k + '/scale_loss'], rtol=1e-12)
         assert abs(m['supervised_loss'].item() - out['loss'].item()) == 0
+    if case[0].endswith('ssi-silog'):
+        for name in ('ssi_component', 'silog_component', 'ssi_mean', 'ssi_var', 'silog1', 'silog2'):
+            for i in range(case[1]):
+                if gold[k + '/valid_px'][i] >= 100:      # below that the reference returns before logging consistent parts
+                    np.testing.assert_allclose(out['metrics']['s%d/%s' % (i, name)].item(), gold[k + '/' + name][i],
+                                               rtol=1e-10, atol=1e-15)
 
 
-@pytest.mark.parametrize('method', ['sparse-l1', 'sparse-mse', 'sparse-silog'])
+@pytest.mark.parametrize('method', ['sparse-l1', 'sparse-mse', 'sparse-silog', 'sparse-ssi-silog'])
 def test_fp32_kernels_at_full_size(method):
     """640x192, batch 8, one scale (what the shipped yaml runs): fp32 kernels vs the fp64 oracle."""
     preds, gt, _ = S.synth_supervised(8, 192, 640, 1, torch.float64, seed=5)
@@ -63,7 +69,7 @@ def test_fp32_kernels_at_full_size(method):
 
 def test_unsupported_methods_are_refused():
     from packnet_sfm.losses.supervised_loss import SupervisedLoss, get_loss_func
-    for m in ('sparse-berhu', 'sparse-ssi-silog', 'sparse-ssi'):
+    for m in ('sparse-berhu', 'sparse-ssi-trim', 'sparse-ssi'):
         with pytest.raises(NotImplementedError):
             get_loss_func(m)
     with pytest.raises(ValueError):
