@@ -212,7 +212,7 @@ int psfm_grid_sample_backward(int B, int Hi, int Wi, int Ho, int Wo, int dt, int
  * (SSISilogLoss, losses/ssi_silog_loss.py:53-429, without its multi-scale gradient term, gradient_weight = 0).
  * sparse != 0: the 'sparse-*' methods -- valid = gt > 0 (and mask != 0 when a [N] byte mask is given); pred and gt are
  * filled with 1e-6 elsewhere and the mean still runs over all N elements, as the reference does; ssi-silog averages
- * over the valid elements only.  pred, gt: [N] of type dt.  hp: HOST double[6] = {silog ratio2, ssi alpha, ssi weight,
+ * over the valid elements only.  pred, gt, d_pred: [N] of type dt, 16-byte aligned.  hp: HOST double[6] = {silog ratio2, ssi alpha, ssi weight,
  * silog weight, depth clamp min, depth clamp max} (the last four: ssi-silog only).  loss_out: real[1].
  * state: DEVICE double[16], written by the forward call, read by the backward call and by callers that log parts:
  * {sum|d|, sum d^2, sum l, sum l^2, valid count, sum d, N, loss, ssi, silog, mean d, var d, silog1, silog2, sign, const}.

@@ -318,15 +318,6 @@ __global__ void __launch_bounds__(kBT) grid_sample_bwd_kernel(int Hi, int Wi, si
 constexpr int kSupVals = 6;
 struct SupHp { double ratio2, alpha, w_ssi, w_silog, cmin, cmax; };
 
-template <typename real>
-__device__ __forceinline__ bool sup_load(size_t i, int method, int sparse, const real* pred, const real* gt,
-                                         const uint8_t* mask, real& p, real& g) {
-  p = pred[i]; g = gt[i];
-  const bool valid = !(sparse || method == PSFM_SUP_SSI_SILOG) || (g > real(0) && (!mask || mask[i] != 0));
-  if (!valid) { p = real(1e-6); g = real(1e-6); }
-  return valid;
-}
-
 // log-difference of the method; dl = d l / d p
 template <typename real>
 __device__ __forceinline__ real sup_logdiff(int method, real p, real g, real cmin, real cmax, real& dl) {
@@ -340,28 +331,44 @@ __device__ __forceinline__ real sup_logdiff(int method, real p, real g, real cmi
   return log(p) - log(g);
 }
 
+// one element's contribution to the six sums
+template <typename real>
+__device__ __forceinline__ void sup_accumulate(int method, int sparse, real p, real g, bool masked_out, const SupHp& hp, real* v) {
+  const bool valid = !(sparse || method == PSFM_SUP_SSI_SILOG) || (g > real(0) && !masked_out);
+  if (!valid) { p = real(1e-6); g = real(1e-6); }
+  const real d = p - g;
+  v[0] += rabs(d);
+  v[1] += d * d;
+  if (method >= PSFM_SUP_SILOG && (valid || method == PSFM_SUP_SILOG)) {
+    real dl;
+    const real l = sup_logdiff<real>(method, p, g, (real)hp.cmin, (real)hp.cmax, dl);
+    v[2] += l; v[3] += l * l;
+  }
+  v[4] += valid ? real(1) : real(0);
+  v[5] += d;
+}
+
+// 16-byte vector loads (4 floats / 2 doubles per thread and iteration), grid-stride; the grid is a fixed function of N
+// (sup_grid), so the order of every sum is fixed.  The up-to-3 tail elements go to thread 0 of block 0.
 template <typename real>
 __global__ void __launch_bounds__(kBT) sup_sums_kernel(size_t N, int method, int sparse, const real* pred, const real* gt,
                                                        const uint8_t* mask, SupHp hp, double* part) {
-  const size_t i = (size_t)blockIdx.x * kBT + threadIdx.x;
+  constexpr int V = 16 / sizeof(real);
   __shared__ real scratch[kSupVals * (kBT / 32)];
   real v[kSupVals];
 #pragma unroll
   for (int k = 0; k < kSupVals; ++k) v[k] = real(0);
-  if (i < N) {
-    real p, g;
-    const bool valid = sup_load<real>(i, method, sparse, pred, gt, mask, p, g);
-    const real d = p - g;
-    v[0] = rabs(d);
-    v[1] = d * d;
-    if (method >= PSFM_SUP_SILOG && (valid || method == PSFM_SUP_SILOG)) {
-      real dl;
-      const real l = sup_logdiff<real>(method, p, g, (real)hp.cmin, (real)hp.cmax, dl);
-      v[2] = l; v[3] = l * l;
-    }
-    v[4] = valid ? real(1) : real(0);
-    v[5] = d;
+  const size_t nvec = N / V;
+#pragma unroll 2
+  for (size_t q = (size_t)blockIdx.x * kBT + threadIdx.x; q < nvec; q += (size_t)gridDim.x * kBT) {
+    alignas(16) real pv[V], gv[V];
+    *reinterpret_cast<int4*>(pv) = __ldg(reinterpret_cast<const int4*>(pred) + q);
+    *reinterpret_cast<int4*>(gv) = __ldg(reinterpret_cast<const int4*>(gt) + q);
+#pragma unroll
+    for (int e = 0; e < V; ++e) sup_accumulate<real>(method, sparse, pv[e], gv[e], mask && mask[q * V + e] == 0, hp, v);
   }
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    for (size_t i = nvec * V; i < N; ++i) sup_accumulate<real>(method, sparse, pred[i], gt[i], mask && mask[i] == 0, hp, v);
   block_reduce<real, kSupVals>(v, scratch);
   if (threadIdx.x < kSupVals) part[(size_t)blockIdx.x * kSupVals + threadIdx.x] = (double)v[threadIdx.x];
 }
@@ -414,34 +421,47 @@ __global__ void __launch_bounds__(256) sup_finish_kernel(const double* part, int
 }
 
 template <typename real>
+__device__ __forceinline__ real sup_grad_elem(int method, int sparse, real p, real g, bool masked_out, const SupHp& hp,
+                                              const double* state, real up, bool live) {
+  const bool valid = !(sparse || method == PSFM_SUP_SSI_SILOG) || (g > real(0) && !masked_out);
+  if (!valid || !live) return real(0);           // masked_fill / masked selection: no gradient reaches an invalid element
+  const real n = (real)state[6];
+  const real d = p - g;
+  if (method == PSFM_SUP_L1) return up * rsign(d) / n;
+  if (method == PSFM_SUP_MSE) return up * real(2) * d / n;
+  real dl;
+  const real l = sup_logdiff<real>(method, p, g, (real)hp.cmin, (real)hp.cmax, dl);
+  if (method == PSFM_SUP_SILOG) {
+    const real m = (real)(state[2] / state[6]), loss = (real)state[7];
+    return up * (l - (real)hp.ratio2 * m) / (n * loss) * dl;
+  }
+  const real M = (real)state[4], md = (real)state[10], ml = (real)(state[2] / state[4]);
+  const real g_ssi = real(2) * (d - (real)(1.0 - hp.alpha) * md) / M;
+  const real g_sil = (real)state[14] * (l - (real)hp.ratio2 * ml) / (M * (real)state[9]) * dl;
+  return up * ((real)hp.w_ssi * g_ssi + (real)hp.w_silog * g_sil);
+}
+
+template <typename real>
 __global__ void __launch_bounds__(kBT) sup_grad_kernel(size_t N, int method, int sparse, const real* pred, const real* gt,
                                                        const uint8_t* mask, SupHp hp, const double* state,
                                                        const real* grad_loss, real* d_pred) {
-  const size_t i = (size_t)blockIdx.x * kBT + threadIdx.x;
-  if (i >= N) return;
-  real p, g;
-  const bool valid = sup_load<real>(i, method, sparse, pred, gt, mask, p, g);
-  real out = real(0);
-  if (valid && state[15] == 0.0) {               // masked_fill / masked selection: no gradient reaches an invalid element
-    const real up = grad_loss[0], n = (real)state[6];
-    const real d = p - g;
-    if (method == PSFM_SUP_L1) out = up * rsign(d) / n;
-    else if (method == PSFM_SUP_MSE) out = up * real(2) * d / n;
-    else {
-      real dl;
-      const real l = sup_logdiff<real>(method, p, g, (real)hp.cmin, (real)hp.cmax, dl);
-      if (method == PSFM_SUP_SILOG) {
-        const real m = (real)(state[2] / state[6]), loss = (real)state[7];
-        out = up * (l - (real)hp.ratio2 * m) / (n * loss) * dl;
-      } else {
-        const real M = (real)state[4], md = (real)state[10], ml = (real)(state[2] / state[4]);
-        const real g_ssi = real(2) * (d - (real)(1.0 - hp.alpha) * md) / M;
-        const real g_sil = (real)state[14] * (l - (real)hp.ratio2 * ml) / (M * (real)state[9]) * dl;
-        out = up * ((real)hp.w_ssi * g_ssi + (real)hp.w_silog * g_sil);
-      }
-    }
+  constexpr int V = 16 / sizeof(real);
+  const bool live = state[15] == 0.0;
+  const real up = grad_loss[0];
+  const size_t nvec = N / V;
+#pragma unroll 2
+  for (size_t q = (size_t)blockIdx.x * kBT + threadIdx.x; q < nvec; q += (size_t)gridDim.x * kBT) {
+    alignas(16) real pv[V], gv[V], ov[V];
+    *reinterpret_cast<int4*>(pv) = __ldg(reinterpret_cast<const int4*>(pred) + q);
+    *reinterpret_cast<int4*>(gv) = __ldg(reinterpret_cast<const int4*>(gt) + q);
+#pragma unroll
+    for (int e = 0; e < V; ++e)
+      ov[e] = sup_grad_elem<real>(method, sparse, pv[e], gv[e], mask && mask[q * V + e] == 0, hp, state, up, live);
+    reinterpret_cast<int4*>(d_pred)[q] = *reinterpret_cast<const int4*>(ov);
   }
-  d_pred[i] = out;
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    for (size_t i = nvec * V; i < N; ++i)
+      d_pred[i] = sup_grad_elem<real>(method, sparse, pred[i], gt[i], mask && mask[i] == 0, hp, state, up, live);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -954,15 +974,19 @@ int psfm_grid_sample_backward(int B, int Hi, int Wi, int Ho, int Wo, int dt, int
   return launch_result("psfm_grid_sample_backward");
 }
 
+// blocks of the supervised-loss kernels: one 16-byte vector per thread up to 8 CTAs per SM of a 148-SM part, grid-stride beyond
+static inline unsigned sup_grid(size_t N) { const unsigned nb = nblk_for((N + 3) / 4); return nb < 148u * 8u ? nb : 148u * 8u; }
+
 int psfm_supervised_loss(int method, int sparse, size_t N, int dt, const void* pred, const void* gt, const void* mask,
                          const double* hp, void* loss_out, void* state, void* ws, size_t ws_bytes, void* stream) {
   PSFM_DT_CHECK(dt);
   PSFM_BLOCK_CHECK(N >= 1 && pred && gt && hp && loss_out && state && method >= PSFM_SUP_L1 && method <= PSFM_SUP_SSI_SILOG,
                    "psfm_supervised_loss: bad argument");
   if (!ws || ws_bytes < psfm_block_workspace_bytes(1, N)) return psfm_fail(PSFM_ERR_WORKSPACE, "psfm_supervised_loss: workspace too small");
+  if ((((uintptr_t)pred) | ((uintptr_t)gt)) & 15) return psfm_fail(PSFM_ERR_INVALID, "psfm_supervised_loss: pred / gt must be 16-byte aligned");
   SupHp h = {hp[0], hp[1], hp[2], hp[3], hp[4], hp[5]};
   if (h.cmax <= h.cmin) h.cmax = h.cmin + 1.0;                 // losses/ssi_silog_loss.py:227-228
-  const unsigned nb = nblk_for(N);
+  const unsigned nb = sup_grid(N);
   cudaStream_t st = (cudaStream_t)stream;
   count_launches(2);
   PSFM_DISPATCH(dt, {
@@ -977,10 +1001,12 @@ int psfm_supervised_loss_backward(int method, int sparse, size_t N, int dt, cons
   PSFM_DT_CHECK(dt);
   PSFM_BLOCK_CHECK(N >= 1 && pred && gt && hp && state && grad_loss && d_pred && method >= PSFM_SUP_L1 && method <= PSFM_SUP_SSI_SILOG,
                    "psfm_supervised_loss_backward: bad argument");
+  if ((((uintptr_t)pred) | ((uintptr_t)gt)) & 15) return psfm_fail(PSFM_ERR_INVALID, "psfm_supervised_loss: pred / gt must be 16-byte aligned");
   SupHp h = {hp[0], hp[1], hp[2], hp[3], hp[4], hp[5]};
   if (h.cmax <= h.cmin) h.cmax = h.cmin + 1.0;
+  if (((uintptr_t)d_pred) & 15) return psfm_fail(PSFM_ERR_INVALID, "psfm_supervised_loss_backward: d_pred must be 16-byte aligned");
   count_launches(1);
-  PSFM_DISPATCH(dt, (sup_grad_kernel<real><<<nblk_for(N), kBT, 0, (cudaStream_t)stream>>>(
+  PSFM_DISPATCH(dt, (sup_grad_kernel<real><<<sup_grid(N), kBT, 0, (cudaStream_t)stream>>>(
                         N, method, sparse, (const real*)pred, (const real*)gt, (const uint8_t*)mask, h,
                         (const double*)state, (const real*)grad_loss, (real*)d_pred)));
   return launch_result("psfm_supervised_loss_backward");

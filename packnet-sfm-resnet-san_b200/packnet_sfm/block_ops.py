@@ -514,6 +514,10 @@ class _SupervisedLoss(torch.autograd.Function):
             raise ValueError('prediction and ground truth must have the same shape')
         pred = pred.contiguous()
         gt = gt.to(pred.dtype).contiguous()
+        if pred.data_ptr() % 16:                 # the kernels use 16-byte vector loads
+            pred = pred.clone()
+        if gt.data_ptr() % 16:
+            gt = gt.clone()
         if mask is not None:
             if mask.numel() != pred.numel():
                 raise ValueError('the mask must have one element per pixel')

@@ -76,3 +76,24 @@ def test_unsupported_methods_are_refused():
         SupervisedLoss(supervised_method='sparse-huber')
     with pytest.raises(RuntimeError, match='no CPU fallback'):
         SupervisedLoss(supervised_method='l1', supervised_num_scales=1)([torch.rand(1, 1, 4, 4)], torch.rand(1, 1, 4, 4))
+
+
+def test_odd_sizes_and_unaligned_views():
+    """Vector loads: sizes that are not a multiple of 4 (scalar tail) and a prediction that is an offset view."""
+    from packnet_sfm.losses.supervised_loss import SupervisedLoss
+    dev = 'cuda:0'
+    g = torch.Generator('cpu').manual_seed(9)
+    for (B, H, W) in ((1, 7, 9), (3, 5, 11)):
+        base = (0.02 + torch.rand(B * H * W + 1, generator=g, dtype=torch.float64))
+        gt = (0.02 + torch.rand(B, 1, H, W, generator=g, dtype=torch.float64))
+        gt[gt < 0.3] = 0
+        for method in ('sparse-silog', 'sparse-l1'):
+            p64 = base[1:].view(B, 1, H, W).clone().requires_grad_()
+            ref = S.supervised_loss([p64], gt, method, 1)
+            ref.backward()
+            holder = base.to(dev)
+            pg = holder[1:].view(B, 1, H, W).requires_grad_()           # data_ptr offset by 8 bytes
+            out = SupervisedLoss(supervised_method=method, supervised_num_scales=1)([pg], gt.to(dev))
+            out['loss'].backward()
+            np.testing.assert_allclose(out['loss'].item(), ref.item(), rtol=1e-12)
+            np.testing.assert_allclose(pg.grad.cpu().numpy(), p64.grad.numpy(), rtol=1e-10, atol=1e-16)
