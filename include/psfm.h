@@ -224,6 +224,18 @@ int psfm_supervised_loss(int method, int sparse, size_t N, int dt, const void* p
 int psfm_supervised_loss_backward(int method, int sparse, size_t N, int dt, const void* pred, const void* gt, const void* mask,
                                   const double* hp, const void* state, const void* grad_loss, void* d_pred, void* stream);
 
+/* DualHeadDepthLoss.forward (losses/dual_head_depth_loss.py:23-201 with decompose_depth / dual_head_to_depth,
+ * networks/layers/resnet/layers.py:76-149): integer_pred, fractional_pred (sigmoid outputs) and
+ * depth_gt are [N] of type dt (depth_gt already at the prediction's size).  hp: HOST double[5] = {max_depth, min_depth,
+ * integer_weight, fractional_weight, consistency_weight}.  loss_out: real[4] = {loss, integer_loss, fractional_loss,
+ * consistency_loss}; state: DEVICE double[8] = {sum_i, sum_f, sum_c, valid count, #(integer error < 1 m), sum frac_err^2,
+ * 0, 1 if no pixel is valid}.  Backward: d_integer[N], d_fractional[N] = grad_loss[0] * d loss / d (.). */
+int psfm_dual_head_loss(size_t N, int dt, const void* integer_pred, const void* fractional_pred, const void* depth_gt,
+                        const double* hp, void* loss_out, void* state, void* workspace, size_t workspace_bytes, void* stream);
+int psfm_dual_head_loss_backward(size_t N, int dt, const void* integer_pred, const void* fractional_pred, const void* depth_gt,
+                                 const double* hp, const void* state, const void* grad_loss, void* d_integer, void* d_fractional,
+                                 void* stream);
+
 /* Pose.transform_points (geometry/pose.py:80-86): out[B,3,N] = R X + t.  Backward: dX, d_mat[B,4,4]. */
 int psfm_transform_points(int B, size_t N, int dt, const void* mat, const void* X, void* out, void* stream);
 int psfm_transform_points_backward(int B, size_t N, int dt, const void* mat, const void* X, const void* grad_out,

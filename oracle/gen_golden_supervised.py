@@ -52,3 +52,33 @@ def main():
 
 if __name__ == '__main__':
     main()
+
+
+def dual_head():
+    """DualHeadDepthLoss of the reference (fp64) -> tests/golden/dual_head.npz."""
+    from packnet_sfm.losses.dual_head_depth_loss import DualHeadDepthLoss
+    from supervised_oracle import synth_dual_head
+    out = {}
+    for name, kw, shape, gt_size in (('default', {}, (2, 24, 40), None),
+                                     ('weights', dict(max_depth=12.0, min_depth=1.0, integer_weight=0.5, fractional_weight=4.0,
+                                                      consistency_weight=2.0), (2, 24, 40), None),
+                                     ('resized_gt', {}, (2, 12, 20), (24, 40)),
+                                     ('no_valid', dict(max_depth=0.15, min_depth=0.1), (1, 8, 8), None)):
+        ip, fp, gt = synth_dual_head(*shape, gt_size=gt_size)
+        ip, fp = ip.requires_grad_(), fp.requires_grad_()
+        with contextlib.redirect_stdout(io.StringIO()):
+            L = DualHeadDepthLoss(**kw)
+            res = L({('integer', 0): ip, ('fractional', 0): fp}, gt, return_logs=True)
+        if res['loss'].requires_grad and ip.requires_grad and name != 'no_valid':
+            res['loss'].backward()
+        out[name + '/losses'] = np.array([float(res[k]) for k in ('loss', 'integer_loss', 'fractional_loss', 'consistency_loss')])
+        out[name + '/d_integer'] = (torch.zeros_like(ip) if ip.grad is None else ip.grad).numpy()
+        out[name + '/d_fractional'] = (torch.zeros_like(fp) if fp.grad is None else fp.grad).numpy()
+        if name != 'no_valid':
+            out[name + '/logs'] = np.array([float(L.metrics[k]) for k in ('mean_depth_error', 'integer_accuracy', 'fractional_rmse')])
+    np.savez_compressed(os.path.join(G.ROOT, 'tests', 'golden', 'dual_head.npz'), **out)
+    print('wrote dual_head.npz with', len(out), 'arrays')
+
+
+if __name__ == '__main__':
+    dual_head()

@@ -36,6 +36,7 @@ API = {
     'packnet_sfm.losses.supervised_loss': ['SilogLoss.__init__', 'SilogLoss.forward', 'get_loss_func', 'SupervisedLoss.__init__',
                                            'SupervisedLoss.calculate_loss', 'SupervisedLoss.forward'],
     'packnet_sfm.losses.ssi_silog_loss': ['SSISilogLoss.__init__', 'SSISilogLoss.forward', 'SSISilogLoss.set_depth_range'],
+    'packnet_sfm.losses.dual_head_depth_loss': ['DualHeadDepthLoss.__init__', 'DualHeadDepthLoss.forward'],
     'packnet_sfm.losses.loss_base': ['LossBase.add_metric', 'ProgressiveScaling.__init__', 'ProgressiveScaling.__call__'],
     'packnet_sfm.geometry.camera': ['Camera.__init__', 'Camera.scaled', 'Camera.reconstruct', 'Camera.project', 'Camera.to',
                                     'FisheyeCamera.__init__', 'FisheyeCamera.reconstruct', 'FisheyeCamera.project',

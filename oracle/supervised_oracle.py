@@ -68,3 +68,32 @@ def synth_supervised(B, H, W, n, dtype=torch.float64, seed=77, pyramid=False):
     gt = torch.where(r(B, 1, H, W) < 0.4, gt, torch.zeros_like(gt))
     masks = [r(B, 1, h, w) > 0.25 for h, w in sizes]
     return [p.to(dtype) for p in preds], gt.to(dtype), masks
+
+
+def dual_head_loss(integer_pred, fractional_pred, depth_gt, max_depth=15.0, min_depth=0.5, integer_weight=1.0,
+                   fractional_weight=10.0, consistency_weight=0.5):
+    """`DualHeadDepthLoss.forward` (losses/dual_head_depth_loss.py:83-201; decompose_depth / dual_head_to_depth,
+    networks/layers/resnet/layers.py:76-149).  Returns (loss, integer, fractional, consistency)."""
+    if depth_gt.shape[-2:] != integer_pred.shape[-2:]:
+        depth_gt = F.interpolate(depth_gt, size=integer_pred.shape[-2:], mode='nearest')
+    mask = (depth_gt > min_depth) & (depth_gt < max_depth)
+    if mask.sum() == 0:
+        z = torch.zeros((), dtype=depth_gt.dtype)
+        return z, z, z, z
+    fl = torch.floor(depth_gt)
+    li = (integer_pred[mask] - (fl / max_depth)[mask]).abs().mean()
+    lf = (fractional_pred[mask] - (depth_gt - fl)[mask]).abs().mean()
+    lc = ((integer_pred * max_depth + fractional_pred)[mask] - depth_gt[mask]).abs().mean()
+    return integer_weight * li + fractional_weight * lf + consistency_weight * lc, li, lf, lc
+
+
+def synth_dual_head(B, H, W, dtype=torch.float64, seed=91, gt_size=None):
+    """Deterministic dual-head inputs: sigmoid-like predictions near the decomposition of a 0.2..18 m ground truth."""
+    g = torch.Generator('cpu').manual_seed(seed)
+    r = lambda *s: torch.rand(*s, generator=g, dtype=torch.float64)
+    gh, gw = gt_size or (H, W)
+    gt = 0.2 + 17.8 * r(B, 1, gh, gw)
+    gt = torch.where(r(B, 1, gh, gw) < 0.6, gt, torch.zeros_like(gt))
+    ip = (r(B, 1, H, W)).clamp(0.01, 0.99)
+    fp = (r(B, 1, H, W)).clamp(0.01, 0.99)
+    return ip.to(dtype), fp.to(dtype), gt.to(dtype)

@@ -465,6 +465,95 @@ __global__ void __launch_bounds__(kBT) sup_grad_kernel(size_t N, int method, int
 }
 
 // ------------------------------------------------------------------------------------------
+// DualHeadDepthLoss.forward (reference losses/dual_head_depth_loss.py:23-201; decompose_depth / dual_head_to_depth,
+// networks/layers/resnet/layers.py:76-149): valid = min_depth < gt < max_depth; over the M valid pixels
+//   integer = mean |ip - floor(gt) / max_depth|, fractional = mean |fp - (gt - floor gt)|,
+//   consistency = mean |ip max_depth + fp - gt|, loss = w_i integer + w_f fractional + w_c consistency (0 when M = 0).
+// hp (host double[5]): {max_depth, min_depth, w_i, w_f, w_c}.
+// state (device double[8]): {sum_i, sum_f, sum_c, M, #(|integer error| < 1 m), sum frac_err^2, 0, 1 if M = 0}.
+// ------------------------------------------------------------------------------------------
+constexpr int kDualVals = 6;
+struct DualHp { double max_depth, min_depth, wi, wf, wc; };
+
+template <typename real>
+__device__ __forceinline__ bool dual_terms(real ip, real fp, real gt, const DualHp& hp, real& ei, real& ef, real& ec) {
+  const real mx = (real)hp.max_depth;
+  const bool valid = gt > (real)hp.min_depth && gt < mx;
+  const real fl = floor(gt);
+  ei = ip - fl / mx;
+  ef = fp - (gt - fl);
+  ec = (ip * mx + fp) - gt;
+  return valid;
+}
+
+template <typename real>
+__global__ void __launch_bounds__(kBT) dual_sums_kernel(size_t N, const real* ip, const real* fp, const real* gt, DualHp hp,
+                                                        double* part) {
+  __shared__ real scratch[kDualVals * (kBT / 32)];
+  real v[kDualVals];
+#pragma unroll
+  for (int k = 0; k < kDualVals; ++k) v[k] = real(0);
+#pragma unroll 4
+  for (size_t i = (size_t)blockIdx.x * kBT + threadIdx.x; i < N; i += (size_t)gridDim.x * kBT) {
+    real ei, ef, ec;
+    if (dual_terms<real>(__ldg(ip + i), __ldg(fp + i), __ldg(gt + i), hp, ei, ef, ec)) {
+      v[0] += rabs(ei); v[1] += rabs(ef); v[2] += rabs(ec); v[3] += real(1);
+      v[4] += (rabs(ei * (real)hp.max_depth) < real(1)) ? real(1) : real(0);
+      v[5] += ef * ef;
+    }
+  }
+  block_reduce<real, kDualVals>(v, scratch);
+  if (threadIdx.x < kDualVals) part[(size_t)blockIdx.x * kDualVals + threadIdx.x] = (double)v[threadIdx.x];
+}
+
+template <typename real>
+__global__ void __launch_bounds__(256) dual_finish_kernel(const double* part, int nblk, DualHp hp, double* state, real* loss_out) {
+  __shared__ double sh[kDualVals][256];
+  double a[kDualVals];
+#pragma unroll
+  for (int k = 0; k < kDualVals; ++k) a[k] = 0.0;
+  for (int i = threadIdx.x; i < nblk; i += 256)
+#pragma unroll
+    for (int k = 0; k < kDualVals; ++k) a[k] += part[(size_t)i * kDualVals + k];
+#pragma unroll
+  for (int k = 0; k < kDualVals; ++k) sh[k][threadIdx.x] = a[k];
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o)
+#pragma unroll
+      for (int k = 0; k < kDualVals; ++k) sh[k][threadIdx.x] += sh[k][threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const double M = sh[3][0];
+    const bool none = M == 0.0;
+    const double li = none ? 0.0 : sh[0][0] / M, lf = none ? 0.0 : sh[1][0] / M, lc = none ? 0.0 : sh[2][0] / M;
+#pragma unroll
+    for (int k = 0; k < kDualVals; ++k) state[k] = sh[k][0];
+    state[6] = 0.0; state[7] = none ? 1.0 : 0.0;
+    loss_out[0] = (real)(hp.wi * li + hp.wf * lf + hp.wc * lc);
+    loss_out[1] = (real)li; loss_out[2] = (real)lf; loss_out[3] = (real)lc;
+  }
+}
+
+template <typename real>
+__global__ void __launch_bounds__(kBT) dual_grad_kernel(size_t N, const real* ip, const real* fp, const real* gt, DualHp hp,
+                                                        const double* state, const real* grad_loss, real* d_ip, real* d_fp) {
+  const bool live = state[7] == 0.0;
+  const real up = live ? grad_loss[0] / (real)state[3] : real(0);
+#pragma unroll 4
+  for (size_t i = (size_t)blockIdx.x * kBT + threadIdx.x; i < N; i += (size_t)gridDim.x * kBT) {
+    real ei, ef, ec, gi = real(0), gf = real(0);
+    if (dual_terms<real>(__ldg(ip + i), __ldg(fp + i), __ldg(gt + i), hp, ei, ef, ec) && live) {
+      const real sc = rsign(ec) * (real)hp.wc;
+      gi = up * ((real)hp.wi * rsign(ei) + sc * (real)hp.max_depth);
+      gf = up * ((real)hp.wf * rsign(ef) + sc);
+    }
+    d_ip[i] = gi; d_fp[i] = gf;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // Pose.transform_points: out = R X + t on [B,3,N]
 // ------------------------------------------------------------------------------------------
 template <typename real>
@@ -1010,6 +1099,39 @@ int psfm_supervised_loss_backward(int method, int sparse, size_t N, int dt, cons
                         N, method, sparse, (const real*)pred, (const real*)gt, (const uint8_t*)mask, h,
                         (const double*)state, (const real*)grad_loss, (real*)d_pred)));
   return launch_result("psfm_supervised_loss_backward");
+}
+
+int psfm_dual_head_loss(size_t N, int dt, const void* integer_pred, const void* fractional_pred, const void* depth_gt,
+                        const double* hp, void* loss_out, void* state, void* ws, size_t ws_bytes, void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(N >= 1 && integer_pred && fractional_pred && depth_gt && hp && loss_out && state, "psfm_dual_head_loss: bad argument");
+  if (!(hp[0] > hp[1]) || !(hp[0] > 0.0) || hp[1] < 0.0)
+    return psfm_fail(PSFM_ERR_INVALID, "psfm_dual_head_loss: need max_depth > min_depth >= 0 (got %g, %g)", hp[0], hp[1]);
+  if (!ws || ws_bytes < psfm_block_workspace_bytes(1, N)) return psfm_fail(PSFM_ERR_WORKSPACE, "psfm_dual_head_loss: workspace too small");
+  const DualHp h = {hp[0], hp[1], hp[2], hp[3], hp[4]};
+  const unsigned nb = nblk_for(N) < 148u * 8u ? nblk_for(N) : 148u * 8u;
+  cudaStream_t st = (cudaStream_t)stream;
+  count_launches(2);
+  PSFM_DISPATCH(dt, {
+    dual_sums_kernel<real><<<nb, kBT, 0, st>>>(N, (const real*)integer_pred, (const real*)fractional_pred, (const real*)depth_gt, h, (double*)ws);
+    dual_finish_kernel<real><<<1, 256, 0, st>>>((const double*)ws, (int)nb, h, (double*)state, (real*)loss_out);
+  });
+  return launch_result("psfm_dual_head_loss");
+}
+
+int psfm_dual_head_loss_backward(size_t N, int dt, const void* integer_pred, const void* fractional_pred, const void* depth_gt,
+                                 const double* hp, const void* state, const void* grad_loss, void* d_integer, void* d_fractional,
+                                 void* stream) {
+  PSFM_DT_CHECK(dt);
+  PSFM_BLOCK_CHECK(N >= 1 && integer_pred && fractional_pred && depth_gt && hp && state && grad_loss && d_integer && d_fractional,
+                   "psfm_dual_head_loss_backward: bad argument");
+  const DualHp h = {hp[0], hp[1], hp[2], hp[3], hp[4]};
+  const unsigned nb = nblk_for(N) < 148u * 8u ? nblk_for(N) : 148u * 8u;
+  count_launches(1);
+  PSFM_DISPATCH(dt, (dual_grad_kernel<real><<<nb, kBT, 0, (cudaStream_t)stream>>>(
+                        N, (const real*)integer_pred, (const real*)fractional_pred, (const real*)depth_gt, h,
+                        (const double*)state, (const real*)grad_loss, (real*)d_integer, (real*)d_fractional)));
+  return launch_result("psfm_dual_head_loss_backward");
 }
 
 int psfm_pose_from_vec(int B, int dt, const void* vec, void* mat, void* stream) {

@@ -560,3 +560,49 @@ def supervised_loss_op(pred, gt, method, sparse=False, mask=None, ratio2=0.85, a
     hp = (ratio2, alpha, ssi_weight, silog_weight, clamp_min, clamp_max)
     out, state = _SupervisedLoss.apply(pred, gt, mask, SUP_METHODS[method], bool(sparse), hp)
     return out[0], state
+
+
+class _DualHeadLoss(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, ip, fp, gt, hp):
+        import ctypes
+        _C.require_cuda(ip, fp, gt)
+        if ip.shape != fp.shape or ip.shape != gt.shape:
+            raise ValueError('integer / fractional predictions and the ground truth must have the same shape')
+        ip = ip.contiguous()
+        fp = fp.to(ip.dtype).contiguous()
+        gt = gt.to(ip.dtype).contiguous()
+        N = ip.numel()
+        out = torch.empty(4, dtype=ip.dtype, device=ip.device)
+        state = torch.empty(8, dtype=torch.float64, device=ip.device)
+        ws, n = _ws(1, N, ip.device)
+        hp_c = (ctypes.c_double * 5)(*[float(x) for x in hp])
+        with torch.cuda.device(ip.device):
+            _C.check(_C.lib.psfm_dual_head_loss(N, _real(ip), _C.ptr(ip), _C.ptr(fp), _C.ptr(gt), hp_c, _C.ptr(out), _C.ptr(state),
+                                                _C.ptr(ws), n, _C.stream_ptr(ip.device)))
+        ctx.save_for_backward(ip, fp, gt, state)
+        ctx.hp = hp_c
+        loss, parts = out[0], out[1:]
+        ctx.mark_non_differentiable(parts, state)
+        return loss, parts, state
+
+    @staticmethod
+    def backward(ctx, g, _gp=None, _gs=None):
+        ip, fp, gt, state = ctx.saved_tensors
+        g = g.to(ip.dtype).reshape(1).contiguous()
+        d_ip, d_fp = torch.empty_like(ip), torch.empty_like(fp)
+        with torch.cuda.device(ip.device):
+            _C.check(_C.lib.psfm_dual_head_loss_backward(ip.numel(), _real(ip), _C.ptr(ip), _C.ptr(fp), _C.ptr(gt), ctx.hp,
+                                                         _C.ptr(state), _C.ptr(g), _C.ptr(d_ip), _C.ptr(d_fp),
+                                                         _C.stream_ptr(ip.device)))
+        return d_ip, d_fp, None, None
+
+
+def dual_head_loss_op(integer_pred, fractional_pred, depth_gt, max_depth, min_depth, integer_weight, fractional_weight,
+                      consistency_weight):
+    """DualHeadDepthLoss.forward (reference losses/dual_head_depth_loss.py:83-201).  Returns (loss [], parts [3] =
+    integer / fractional / consistency loss, state [8] float64); differentiable w.r.t. both predictions."""
+    _real(integer_pred)
+    _no_grad_supported(depth_gt, 'the ground truth')
+    return _DualHeadLoss.apply(integer_pred, fractional_pred, depth_gt,
+                               (max_depth, min_depth, integer_weight, fractional_weight, consistency_weight))

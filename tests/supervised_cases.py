@@ -20,3 +20,11 @@ def make_inputs(case, dtype=torch.float64):
     if not method.startswith('sparse'):
         gt = gt.clamp(min=0.02)
     return preds, gt, (masks if use_mask else None)
+
+DUAL_CASES = {
+    'default': ({}, (2, 24, 40), None),
+    'weights': (dict(max_depth=12.0, min_depth=1.0, integer_weight=0.5, fractional_weight=4.0, consistency_weight=2.0),
+                (2, 24, 40), None),
+    'resized_gt': ({}, (2, 12, 20), (24, 40)),
+    'no_valid': (dict(max_depth=0.15, min_depth=0.1), (1, 8, 8), None),
+}

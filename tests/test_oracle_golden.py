@@ -151,3 +151,21 @@ def test_supervised_oracle_matches_reference():
         for i, p in enumerate(preds):
             got = torch.zeros_like(p) if p.grad is None else p.grad
             np.testing.assert_allclose(got.numpy(), gold[k + '/d_pred%d' % i], rtol=1e-10, atol=1e-16)
+
+
+def test_dual_head_oracle_matches_reference():
+    """oracle/supervised_oracle.py::dual_head_loss against the reference's own DualHeadDepthLoss (fp64)."""
+    import supervised_oracle as S
+    from golden_cases import load_golden
+    from supervised_cases import DUAL_CASES
+    gold = load_golden('dual_head')
+    for name, (kw, shape, gt_size) in DUAL_CASES.items():
+        ip, fp, gt = S.synth_dual_head(*shape, gt_size=gt_size)
+        ip, fp = ip.requires_grad_(), fp.requires_grad_()
+        res = S.dual_head_loss(ip, fp, gt, **kw)
+        if res[0].requires_grad:
+            res[0].backward()
+        np.testing.assert_allclose([float(x) for x in res], gold[name + '/losses'], rtol=1e-12, atol=1e-300)
+        for t, key in ((ip, 'd_integer'), (fp, 'd_fractional')):
+            got = torch.zeros_like(t) if t.grad is None else t.grad
+            np.testing.assert_allclose(got.numpy(), gold[name + '/' + key], rtol=1e-10, atol=1e-16)

@@ -97,3 +97,48 @@ def test_odd_sizes_and_unaligned_views():
             out['loss'].backward()
             np.testing.assert_allclose(out['loss'].item(), ref.item(), rtol=1e-12)
             np.testing.assert_allclose(pg.grad.cpu().numpy(), p64.grad.numpy(), rtol=1e-10, atol=1e-16)
+
+
+# ---- DualHeadDepthLoss (reference losses/dual_head_depth_loss.py:23-201) -----------------------------------------
+
+@pytest.mark.parametrize('name', ['default', 'weights', 'resized_gt', 'no_valid'])
+def test_dual_head_fp64_kernels_match_reference_fixtures(name):
+    from packnet_sfm.losses.dual_head_depth_loss import DualHeadDepthLoss
+    from supervised_cases import DUAL_CASES
+    gold = load_golden('dual_head')
+    kw, shape, gt_size = DUAL_CASES[name]
+    ip, fp, gt = S.synth_dual_head(*shape, gt_size=gt_size)
+    dev = 'cuda:0'
+    ip, fp = ip.to(dev).requires_grad_(), fp.to(dev).requires_grad_()
+    L = DualHeadDepthLoss(**kw)
+    res = L({('integer', 0): ip, ('fractional', 0): fp}, gt.to(dev), return_logs=True)
+    res['loss'].backward()
+    torch.cuda.synchronize()
+    got = [res[k].item() for k in ('loss', 'integer_loss', 'fractional_loss', 'consistency_loss')]
+    np.testing.assert_allclose(got, gold[name + '/losses'], rtol=1e-12, atol=1e-300)
+    np.testing.assert_allclose(ip.grad.cpu().numpy(), gold[name + '/d_integer'], rtol=1e-10, atol=1e-16)
+    np.testing.assert_allclose(fp.grad.cpu().numpy(), gold[name + '/d_fractional'], rtol=1e-10, atol=1e-16)
+    if name != 'no_valid':
+        logs = [L.metrics[k].item() for k in ('mean_depth_error', 'integer_accuracy', 'fractional_rmse')]
+        # the reference forms integer_accuracy with .float() (fp32) even for fp64 inputs
+        np.testing.assert_allclose(logs, gold[name + '/logs'], rtol=1e-6)
+
+
+def test_dual_head_fp32_full_size():
+    from packnet_sfm.losses.dual_head_depth_loss import DualHeadDepthLoss
+    ip, fp, gt = S.synth_dual_head(16, 384, 640, seed=4)
+    i64, f64 = ip.clone().requires_grad_(), fp.clone().requires_grad_()
+    ref = S.dual_head_loss(i64, f64, gt)
+    ref[0].backward()
+    dev = 'cuda:0'
+    i32, f32 = ip.float().to(dev).requires_grad_(), fp.float().to(dev).requires_grad_()
+    res = DualHeadDepthLoss()({('integer', 0): i32, ('fractional', 0): f32}, gt.float().to(dev))
+    res['loss'].backward()
+    torch.cuda.synchronize()
+    assert abs(res['loss'].item() - ref[0].item()) <= 1e-5 * abs(ref[0].item())
+    # sign-type gradients: identical except where fp32 rounding of the ground truth flips a sign (|error| ~ 1e-7)
+    for a, b in ((i32.grad, i64.grad), (f32.grad, f64.grad)):
+        rel = ((a.double().cpu() - b).norm() / b.norm()).item()
+        assert rel <= 2e-3, rel
+    with pytest.raises(AssertionError):
+        DualHeadDepthLoss(max_depth=1.0, min_depth=2.0)
