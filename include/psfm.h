@@ -236,6 +236,20 @@ int psfm_dual_head_loss_backward(size_t N, int dt, const void* integer_pred, con
                                  const double* hp, const void* state, const void* grad_loss, void* d_integer, void* d_fractional,
                                  void* stream);
 
+/* compute_depth_metrics(config, gt, pred, use_gt_scale) (utils/depth.py:258-447 with scale_depth :450-481; SURVEY.md
+ * section 8(f) N4): gt[B,1,H,W], pred[B,1,h,w] of type dt.  scale_mode: 0 = config.scale_output 'resize' (bilinear,
+ * align_corners=True, evaluated per pixel; the prediction itself when the sizes agree), 1 = 'top-center' (prediction placed
+ * at the bottom, centred, zeros elsewhere); anything else is PSFM_ERR_INVALID like the reference's NotImplementedError.
+ * crop != 0: config.crop == 'garg'.  valid = min_depth < gt < max_depth (and inside the crop).  use_gt_scale != 0: the
+ * prediction of every image is multiplied by median(gt valid) / median(pred valid), torch.median's lower median, found by
+ * exact radix selection on the device.  out: real[7] = (abs_rel, sq_rel, rmse, rmse_log, a1, a2, a3), each the sum over the
+ * images that have a valid pixel divided by B.  state: DEVICE double[B * 12], per image {valid count, gt median, pred
+ * median, scale, the seven metrics of the image, 0}.  No host synchronisation (the reference reads valid.sum() back). */
+size_t psfm_depth_metrics_workspace_bytes(int B, int H, int W);
+int psfm_depth_metrics(int B, int H, int W, int h, int w, int dt, int scale_mode, int crop, int use_gt_scale,
+                       double min_depth, double max_depth, const void* gt, const void* pred, void* out, void* state,
+                       void* workspace, size_t workspace_bytes, void* stream);
+
 /* Pose.transform_points (geometry/pose.py:80-86): out[B,3,N] = R X + t.  Backward: dX, d_mat[B,4,4]. */
 int psfm_transform_points(int B, size_t N, int dt, const void* mat, const void* X, void* out, void* stream);
 int psfm_transform_points_backward(int B, size_t N, int dt, const void* mat, const void* X, const void* grad_out,

@@ -47,7 +47,8 @@ API = {
     'packnet_sfm.geometry.pose_utils': ['euler2mat', 'pose_vec2mat', 'invert_pose'],
     'packnet_sfm.utils.image': ['gradient_x', 'gradient_y', 'interpolate_image', 'interpolate_scales', 'match_scales',
                                 'meshgrid', 'image_grid'],
-    'packnet_sfm.utils.depth': ['inv2depth', 'depth2inv', 'inv_depths_normalize', 'calc_smoothness'],
+    'packnet_sfm.utils.depth': ['inv2depth', 'depth2inv', 'inv_depths_normalize', 'calc_smoothness', 'compute_depth_metrics',
+                                'scale_depth'],
 }
 
 

@@ -28,6 +28,7 @@ EXPORTS = ('psfm_abi_version', 'psfm_last_error', 'psfm_launch_count', 'psfm_pro
            'psfm_fisheye_reconstruct', 'psfm_fisheye_reconstruct_backward', 'psfm_fisheye_project',
            'psfm_fisheye_project_backward', 'psfm_grid_sample', 'psfm_grid_sample_backward',
            'psfm_supervised_loss', 'psfm_supervised_loss_backward', 'psfm_dual_head_loss', 'psfm_dual_head_loss_backward',
+           'psfm_depth_metrics_workspace_bytes', 'psfm_depth_metrics',
            'psfm_photometric_map', 'psfm_photometric_map_backward', 'psfm_normalize', 'psfm_normalize_backward',
            'psfm_smoothness_maps', 'psfm_smoothness_maps_backward', 'psfm_reduce_candidates',
            'psfm_reduce_candidates_backward', 'psfm_abs_mean', 'psfm_abs_mean_backward')
@@ -90,6 +91,8 @@ def _load():
     d = C.c_double
     lib.psfm_block_workspace_bytes.restype = sz
     lib.psfm_block_workspace_bytes.argtypes = [i, sz]
+    lib.psfm_depth_metrics_workspace_bytes.restype = sz
+    lib.psfm_depth_metrics_workspace_bytes.argtypes = [i, i, i]
     for name, args in (
             ('psfm_reconstruct', [i, i, i, i, vp, vp, vp, vp, vp]),
             ('psfm_reconstruct_backward', [i, i, i, i, vp, vp, vp, vp, vp]),
@@ -107,6 +110,7 @@ def _load():
             ('psfm_supervised_loss_backward', [i, i, sz, i, vp, vp, vp, C.POINTER(d), vp, vp, vp, vp]),
             ('psfm_dual_head_loss', [sz, i, vp, vp, vp, C.POINTER(d), vp, vp, vp, sz, vp]),
             ('psfm_dual_head_loss_backward', [sz, i, vp, vp, vp, C.POINTER(d), vp, vp, vp, vp, vp]),
+            ('psfm_depth_metrics', [i, i, i, i, i, i, i, i, i, d, d, vp, vp, vp, vp, vp, sz, vp]),
             ('psfm_transform_points', [i, sz, i, vp, vp, vp, vp]),
             ('psfm_transform_points_backward', [i, sz, i, vp, vp, vp, vp, vp, vp, sz, vp]),
             ('psfm_photometric_map', [i, i, i, i, i, d, d, d, vp, vp, vp, vp]),

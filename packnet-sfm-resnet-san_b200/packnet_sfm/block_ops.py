@@ -606,3 +606,25 @@ def dual_head_loss_op(integer_pred, fractional_pred, depth_gt, max_depth, min_de
     _no_grad_supported(depth_gt, 'the ground truth')
     return _DualHeadLoss.apply(integer_pred, fractional_pred, depth_gt,
                                (max_depth, min_depth, integer_weight, fractional_weight, consistency_weight))
+
+
+def depth_metrics_op(gt, pred, scale_mode, garg_crop, use_gt_scale, min_depth, max_depth):
+    """compute_depth_metrics (reference utils/depth.py:258-447).  Returns (metrics [7] of gt's dtype, state [B,12] float64)."""
+    _C.require_cuda(gt, pred)
+    _real(gt)
+    if gt.dim() != 4 or pred.dim() != 4 or gt.shape[1] != 1 or pred.shape[1] != 1 or gt.shape[0] != pred.shape[0]:
+        raise ValueError('compute_depth_metrics: gt [B,1,H,W] and pred [B,1,h,w] expected, got %s and %s'
+                         % (tuple(gt.shape), tuple(pred.shape)))
+    gt = gt.detach().contiguous()
+    pred = pred.detach().to(gt.dtype).contiguous()
+    B, _, H, W = gt.shape
+    h, w = pred.shape[-2:]
+    out = torch.empty(7, dtype=gt.dtype, device=gt.device)
+    state = torch.empty(B, 12, dtype=torch.float64, device=gt.device)
+    n = _C.lib.psfm_depth_metrics_workspace_bytes(B, H, W)
+    ws = torch.empty(n, dtype=torch.uint8, device=gt.device)
+    with torch.cuda.device(gt.device):
+        _C.check(_C.lib.psfm_depth_metrics(B, H, W, h, w, _real(gt), int(scale_mode), int(bool(garg_crop)), int(bool(use_gt_scale)),
+                                           float(min_depth), float(max_depth), _C.ptr(gt), _C.ptr(pred), _C.ptr(out),
+                                           _C.ptr(state), _C.ptr(ws), n, _C.stream_ptr(gt.device)))
+    return out, state

@@ -1,4 +1,5 @@
-"""Depth helpers on the photometric-loss path (reference: utils/depth.py:103-198)."""
+"""Depth helpers on the photometric-loss path (reference: utils/depth.py:103-198) and the evaluation metrics
+(reference: utils/depth.py:258-481)."""
 from packnet_sfm.utils.types import is_seq
 
 
@@ -34,3 +35,38 @@ def calc_smoothness(inv_depths, images, num_scales):
 
 # north-star name (BASELINE.json) for the same function; the reference only has calc_smoothness
 inv_depths_smoothness = calc_smoothness
+
+
+def compute_depth_metrics(config, gt, pred, use_gt_scale=True, return_state=False):
+    """Depth metrics of a batch (reference :258-447): `config` carries `min_depth`, `max_depth`, `crop` ('garg' or
+    anything else) and `scale_output` ('resize' | 'top-center', scale_depth :450-481); gt [B,1,H,W], pred [B,1,h,w].
+    Returns a [7] tensor (abs_rel, sq_rel, rmse, rmse_log, a1, a2, a3) of gt's dtype on gt's device.  One C-ABI call
+    (`psfm_depth_metrics`): exact per-image medians by radix selection, no gather / sort / host read-back.
+    `return_state=True` (extension) also returns the per-image block [B,12] float64 = {valid count, gt median, pred
+    median, scale, the image's seven metrics, 0}."""
+    from packnet_sfm.block_ops import depth_metrics_op
+    if config.scale_output == 'resize':
+        mode = 0
+    elif config.scale_output == 'top-center':
+        mode = 1
+    else:
+        raise NotImplementedError('Depth scale function {} not implemented.'.format(config.scale_output))
+    out, state = depth_metrics_op(gt, pred, mode, config.crop == 'garg', bool(use_gt_scale), float(config.min_depth),
+                                  float(config.max_depth))
+    return (out, state) if return_state else out
+
+
+def scale_depth(pred, gt, scale_fn):
+    """Match depth maps to the ground-truth resolution (reference :450-481): 'resize' = bilinear, align_corners=True
+    (the resize kernel behind `interpolate_image`); 'top-center' = prediction placed at the bottom, centred, zeros
+    elsewhere.  `compute_depth_metrics` does not call this: it evaluates the same values per pixel inside its kernels."""
+    if scale_fn == 'resize':
+        from packnet_sfm.utils.image import interpolate_image
+        return interpolate_image(pred, gt.shape, mode='bilinear', align_corners=True)
+    if scale_fn == 'top-center':
+        import torch
+        pred_uncropped = torch.zeros(gt.shape, dtype=pred.dtype, device=pred.device)
+        top, left = gt.shape[2] - pred.shape[2], (gt.shape[3] - pred.shape[3]) // 2
+        pred_uncropped[:, :, top:(top + pred.shape[2]), left:(left + pred.shape[3])] = pred
+        return pred_uncropped
+    raise NotImplementedError('Depth scale function {} not implemented.'.format(scale_fn))

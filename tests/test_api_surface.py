@@ -104,6 +104,18 @@ def test_abi_argument_validation_without_gpu():
     assert _C.lib.psfm_loss_workspace_bytes(ctypes.byref(cfg)) > 0
     assert _C.lib.psfm_reconstruct(1, 4, 4, 5, None, None, None, None, None) == -1      # bad dtype
     assert _C.lib.psfm_block_workspace_bytes(0, 10) == 0
+    # compute_depth_metrics: argument checks come before any CUDA call
+    assert _C.lib.psfm_depth_metrics_workspace_bytes(0, 8, 8) == 0
+    n = _C.lib.psfm_depth_metrics_workspace_bytes(2, 8, 8)
+    assert n > 0
+    one = ctypes.c_void_p(256)          # never dereferenced: every call below is refused
+    bad = lambda *a: _C.lib.psfm_depth_metrics(*a)
+    assert bad(2, 8, 8, 8, 8, 0, 2, 0, 1, 0.0, 80.0, one, one, one, one, one, n, None) == -1
+    assert b'not implemented' in _C.lib.psfm_last_error()
+    assert bad(2, 8, 8, 9, 8, 0, 1, 0, 1, 0.0, 80.0, one, one, one, one, one, n, None) == -1       # top-center, pred larger
+    assert bad(2, 8, 8, 8, 8, 0, 0, 0, 1, 0.0, 80.0, one, one, one, one, one, n - 1, None) == -3   # workspace
+    assert bad(2, 8, 8, 8, 8, 7, 0, 0, 1, 0.0, 80.0, one, one, one, one, one, n, None) == -1       # dtype
+    assert bad(2, 8, 8, 8, 8, 0, 0, 0, 1, 0.0, 80.0, None, one, one, one, one, n, None) == -1      # null pointer
     with pytest.raises(ValueError):
         _C.check(-1)
     with pytest.raises(_C.PsfmError):

@@ -169,3 +169,17 @@ def test_dual_head_oracle_matches_reference():
         for t, key in ((ip, 'd_integer'), (fp, 'd_fractional')):
             got = torch.zeros_like(t) if t.grad is None else t.grad
             np.testing.assert_allclose(got.numpy(), gold[name + '/' + key], rtol=1e-10, atol=1e-16)
+
+
+def test_depth_metrics_oracle_matches_reference():
+    """compute_depth_metrics restatement vs the reference's own function (oracle/gen_golden_metrics.py), incl. its float32
+    a1..a3 path: bit-exact on every catalogue case."""
+    import metrics_oracle as M
+    gold = load_golden('depth_metrics')
+    assert sorted(gold.keys()) == sorted(M.CASES)
+    for name, (B, _, _, crop, scale_output, use_gt_scale, lo, hi, _) in M.CASES.items():
+        gt, pred = M.synth_metrics(name)
+        got = M.compute_depth_metrics(gt, pred, lo, hi, crop, scale_output, use_gt_scale).numpy()
+        np.testing.assert_array_equal(got, gold[name], err_msg=name)
+    with pytest.raises(NotImplementedError):
+        M.scale_depth(torch.ones(1, 1, 2, 2), torch.ones(1, 1, 4, 4), 'bottom-left')
