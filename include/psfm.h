@@ -224,6 +224,24 @@ int psfm_supervised_loss(int method, int sparse, size_t N, int dt, const void* p
 int psfm_supervised_loss_backward(int method, int sparse, size_t N, int dt, const void* pred, const void* gt, const void* mask,
                                   const double* hp, const void* state, const void* grad_loss, void* d_pred, void* stream);
 
+/* The multi-scale Sobel gradient term of SSISilogLoss (losses/ssi_silog_loss.py:12-50 Gradient2D, :116-174
+ * compute_gradient_loss; `gradient_weight` / `gradient_scales` of the loss section, set by
+ * configs/train_resnet_san_ncdb_dual_head_640x384.yaml).  pred_inv, gt_inv: [B,1,H,W] inverse depths
+ * of type dt; valid = gt_inv > 0 (and mask != 0 when a [B*H*W] byte mask is given), as the sparse caller builds it
+ * (losses/supervised_loss.py:314-333).  Per scale s < scales: depth maps resized by 0.5^s (bilinear, align_corners=False),
+ * mask by nearest, mean |Sobel(pred) - Sobel(gt)| (x plus y) over the masked interior; average over the scales that have a
+ * masked pixel (0 when none).  loss_out: real[1].  state: DEVICE double[20] = {loss, scales used, 0, 0, count per scale [8],
+ * loss per scale [8]}.  codes: DEVICE bytes (psfm_sobel_gradient_code_bytes), written by the forward call and read by the
+ * backward call together with state.  Backward: d_pred[B,1,H,W] = grad_loss[0] * d loss / d pred_inv. */
+size_t psfm_sobel_gradient_code_bytes(int B, int H, int W, int scales);
+size_t psfm_sobel_gradient_workspace_bytes(int B, int H, int W, int scales);
+int psfm_sobel_gradient_loss(int B, int H, int W, int dt, int scales, const void* pred_inv, const void* gt_inv,
+                             const void* mask, void* loss_out, void* state, void* codes, void* workspace,
+                             size_t workspace_bytes, void* stream);
+int psfm_sobel_gradient_loss_backward(int B, int H, int W, int dt, int scales, const void* pred_inv, const void* gt_inv,
+                                      const void* mask, const void* state, const void* codes, const void* grad_loss,
+                                      void* d_pred, void* stream);
+
 /* DualHeadDepthLoss.forward (losses/dual_head_depth_loss.py:23-201 with decompose_depth / dual_head_to_depth,
  * networks/layers/resnet/layers.py:76-149): integer_pred, fractional_pred (sigmoid outputs) and
  * depth_gt are [N] of type dt (depth_gt already at the prediction's size).  hp: HOST double[5] = {max_depth, min_depth,

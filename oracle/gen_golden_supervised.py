@@ -82,3 +82,30 @@ def dual_head():
 
 if __name__ == '__main__':
     dual_head()
+
+
+def gradient_term():
+    """SSISilogLoss with gradient_weight = 0.2 through the reference's SupervisedLoss (fp64) -> tests/golden/ssi_gradient.npz."""
+    import sys
+    sys.path.insert(0, os.path.join(G.ROOT, 'tests'))
+    from supervised_cases import GRAD_CASES, GRAD_KW, make_grad_inputs
+    out = {}
+    for name, (B, H, W, use_mask, gs) in GRAD_CASES.items():
+        preds, gt, masks = make_grad_inputs(name)
+        preds = [p.requires_grad_() for p in preds]
+        with contextlib.redirect_stdout(io.StringIO()):
+            L = SupervisedLoss(supervised_method='sparse-ssi-silog', supervised_num_scales=1, **dict(GRAD_KW, gradient_scales=gs))
+            L = L.double()          # the Sobel weights are float32 buffers of the module (:25-38)
+            res = L(preds, gt, masks=[m.clone() for m in masks] if masks is not None else None)
+        if res['loss'].requires_grad:
+            res['loss'].backward()
+        out[name + '/loss'] = res['loss'].detach().numpy()
+        out[name + '/d_pred'] = (torch.zeros_like(preds[0]) if preds[0].grad is None else preds[0].grad).numpy()
+        out[name + '/gradient_component'] = np.array(float(res['metrics'].get('s0/gradient_component', 0.0)))
+        print(name, float(res['loss']), out[name + '/gradient_component'])
+    np.savez_compressed(os.path.join(G.ROOT, 'tests', 'golden', 'ssi_gradient.npz'), **out)
+    print('wrote ssi_gradient.npz with', len(out), 'arrays')
+
+
+if __name__ == '__main__':
+    gradient_term()

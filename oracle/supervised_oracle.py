@@ -36,7 +36,33 @@ def ssi_silog(pred, gt, mask, alpha=0.85, ratio2=0.85, ssi_weight=0.7, silog_wei
     return ssi_weight * ssi + silog_weight * silog
 
 
-def supervised_loss(inv_depths, gt_inv_depth, supervised_method, num_scales, masks=None, **kw):
+def sobel_gradient_term(pred, gt, mask, scales=4):
+    """`SSISilogLoss.compute_gradient_loss` (losses/ssi_silog_loss.py:116-174) with `Gradient2D` (:12-50) on the depth maps
+    of the (filled) inverse depths.  pred, gt: [B,1,H,W] inverse depths; mask: [B,1,H,W] bool."""
+    kx = torch.tensor([[-1., 0., 1.], [-2., 0., 2.], [-1., 0., 1.]], dtype=pred.dtype).view(1, 1, 3, 3)
+    ky = kx.transpose(2, 3).contiguous()
+    P, G = 1. / pred.clamp(min=1e-6), 1. / gt.clamp(min=1e-6)
+    total, used = 0.0, 0
+    for s in range(scales):
+        if s == 0:
+            p, g, m = P, G, mask
+        else:
+            f = 1.0 / 2 ** s
+            p = F.interpolate(P, scale_factor=f, mode='bilinear', align_corners=False)
+            g = F.interpolate(G, scale_factor=f, mode='bilinear', align_corners=False)
+            m = F.interpolate(mask.to(pred.dtype), scale_factor=f, mode='nearest') > 0.5
+        if p.shape[2] < 3 or p.shape[3] < 3:
+            continue
+        m = m[:, :, 1:-1, 1:-1]
+        if m.sum() > 0:
+            total = total + ((F.conv2d(p, kx) - F.conv2d(g, kx)).abs()[m].mean() +
+                             (F.conv2d(p, ky) - F.conv2d(g, ky)).abs()[m].mean())
+            used += 1
+    return total / used if used else torch.zeros((), dtype=pred.dtype)
+
+
+def supervised_loss(inv_depths, gt_inv_depth, supervised_method, num_scales, masks=None, gradient_weight=0.0,
+                    gradient_scales=4, **kw):
     """`SupervisedLoss.forward` (:420-437): ground truth matched to every scale with nearest interpolation
     (utils/image.py:178-214), sparse methods fill invalid pixels of both maps with 1e-6 (:323-345)."""
     method = 'ssi-silog' if supervised_method.endswith('ssi-silog') else supervised_method.split('-')[-1]
@@ -52,7 +78,10 @@ def supervised_loss(inv_depths, gt_inv_depth, supervised_method, num_scales, mas
                 valid = valid & masks[i]
             p, g = p.masked_fill(~valid, 1e-6), g.masked_fill(~valid, 1e-6)
         if method == 'ssi-silog':
-            total = total + ssi_silog(p, g, valid if sparse else (1. / g.clamp(min=1e-6)) > 0, **kw)
+            m = valid if sparse else (1. / g.clamp(min=1e-6)) > 0
+            total = total + ssi_silog(p, g, m, **kw)
+            if gradient_weight > 0 and m.sum() >= 100:
+                total = total + gradient_weight * sobel_gradient_term(p, g, m, gradient_scales)
             continue
         total = total + loss_function(p, g, method)
     return total / float(num_scales)

@@ -29,6 +29,8 @@ EXPORTS = ('psfm_abi_version', 'psfm_last_error', 'psfm_launch_count', 'psfm_pro
            'psfm_fisheye_project_backward', 'psfm_grid_sample', 'psfm_grid_sample_backward',
            'psfm_supervised_loss', 'psfm_supervised_loss_backward', 'psfm_dual_head_loss', 'psfm_dual_head_loss_backward',
            'psfm_depth_metrics_workspace_bytes', 'psfm_depth_metrics',
+           'psfm_sobel_gradient_code_bytes', 'psfm_sobel_gradient_workspace_bytes', 'psfm_sobel_gradient_loss',
+           'psfm_sobel_gradient_loss_backward',
            'psfm_photometric_map', 'psfm_photometric_map_backward', 'psfm_normalize', 'psfm_normalize_backward',
            'psfm_smoothness_maps', 'psfm_smoothness_maps_backward', 'psfm_reduce_candidates',
            'psfm_reduce_candidates_backward', 'psfm_abs_mean', 'psfm_abs_mean_backward')
@@ -91,6 +93,9 @@ def _load():
     d = C.c_double
     lib.psfm_block_workspace_bytes.restype = sz
     lib.psfm_block_workspace_bytes.argtypes = [i, sz]
+    for name in ('psfm_sobel_gradient_code_bytes', 'psfm_sobel_gradient_workspace_bytes'):
+        getattr(lib, name).restype = sz
+        getattr(lib, name).argtypes = [i, i, i, i]
     lib.psfm_depth_metrics_workspace_bytes.restype = sz
     lib.psfm_depth_metrics_workspace_bytes.argtypes = [i, i, i]
     for name, args in (
@@ -110,6 +115,8 @@ def _load():
             ('psfm_supervised_loss_backward', [i, i, sz, i, vp, vp, vp, C.POINTER(d), vp, vp, vp, vp]),
             ('psfm_dual_head_loss', [sz, i, vp, vp, vp, C.POINTER(d), vp, vp, vp, sz, vp]),
             ('psfm_dual_head_loss_backward', [sz, i, vp, vp, vp, C.POINTER(d), vp, vp, vp, vp, vp]),
+            ('psfm_sobel_gradient_loss', [i, i, i, i, i, vp, vp, vp, vp, vp, vp, vp, sz, vp]),
+            ('psfm_sobel_gradient_loss_backward', [i, i, i, i, i, vp, vp, vp, vp, vp, vp, vp, vp]),
             ('psfm_depth_metrics', [i, i, i, i, i, i, i, i, i, d, d, vp, vp, vp, vp, vp, sz, vp]),
             ('psfm_transform_points', [i, sz, i, vp, vp, vp, vp]),
             ('psfm_transform_points_backward', [i, sz, i, vp, vp, vp, vp, vp, vp, sz, vp]),

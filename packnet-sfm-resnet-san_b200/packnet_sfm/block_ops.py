@@ -628,3 +628,52 @@ def depth_metrics_op(gt, pred, scale_mode, garg_crop, use_gt_scale, min_depth, m
                                            float(min_depth), float(max_depth), _C.ptr(gt), _C.ptr(pred), _C.ptr(out),
                                            _C.ptr(state), _C.ptr(ws), n, _C.stream_ptr(gt.device)))
     return out, state
+
+
+class _SobelGradientLoss(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, pred, gt, mask, scales):
+        _C.require_cuda(pred, gt, mask)
+        if pred.dim() != 4 or pred.shape[1] != 1 or pred.shape != gt.shape:
+            raise ValueError('[B,1,H,W] prediction and ground truth of the same shape expected')
+        pred = pred.contiguous()
+        gt = gt.to(pred.dtype).contiguous()
+        if mask is not None:
+            if mask.numel() != pred.numel():
+                raise ValueError('the mask must have one element per pixel')
+            mask = (mask if mask.dtype == torch.uint8 else (mask > 0).to(torch.uint8)).contiguous()
+        B, _, H, W = pred.shape
+        dev = pred.device
+        out = torch.empty(1, dtype=pred.dtype, device=dev)
+        state = torch.empty(20, dtype=torch.float64, device=dev)
+        codes = torch.empty(int(_C.lib.psfm_sobel_gradient_code_bytes(B, H, W, scales)), dtype=torch.uint8, device=dev)
+        n = int(_C.lib.psfm_sobel_gradient_workspace_bytes(B, H, W, scales))
+        ws = torch.empty(n, dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            _C.check(_C.lib.psfm_sobel_gradient_loss(B, H, W, _real(pred), scales, _C.ptr(pred), _C.ptr(gt), _C.ptr(mask),
+                                                     _C.ptr(out), _C.ptr(state), _C.ptr(codes), _C.ptr(ws), n,
+                                                     _C.stream_ptr(dev)))
+        ctx.save_for_backward(pred, gt, mask, state, codes)
+        ctx.scales = scales
+        ctx.mark_non_differentiable(state)
+        return out[0], state
+
+    @staticmethod
+    def backward(ctx, g, _gs=None):
+        pred, gt, mask, state, codes = ctx.saved_tensors
+        B, _, H, W = pred.shape
+        g = g.to(pred.dtype).reshape(1).contiguous()
+        d_pred = torch.empty_like(pred)
+        with torch.cuda.device(pred.device):
+            _C.check(_C.lib.psfm_sobel_gradient_loss_backward(B, H, W, _real(pred), ctx.scales, _C.ptr(pred), _C.ptr(gt),
+                                                              _C.ptr(mask), _C.ptr(state), _C.ptr(codes), _C.ptr(g),
+                                                              _C.ptr(d_pred), _C.stream_ptr(pred.device)))
+        return d_pred, None, None, None
+
+
+def sobel_gradient_loss_op(pred_inv_depth, gt_inv_depth, mask=None, scales=4):
+    """SSISilogLoss.compute_gradient_loss on the sparse caller's filled maps (reference losses/ssi_silog_loss.py:116-174).
+    Returns (loss [], state [20] float64); differentiable w.r.t. the prediction."""
+    _real(pred_inv_depth)
+    _no_grad_supported(gt_inv_depth, 'the ground truth')
+    return _SobelGradientLoss.apply(pred_inv_depth, gt_inv_depth, mask, int(scales))

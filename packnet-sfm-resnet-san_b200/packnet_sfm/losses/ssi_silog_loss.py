@@ -5,9 +5,10 @@ loss = ssi_weight * ssi + silog_weight * silog over the valid pixels:
   silog = sqrt(|mean(l^2) - silog_ratio2 * mean(l)^2| + 1e-8),  l = log P - log G on depths 1 / max(., 1e-6) clamped to
           [min_depth or 1e-3, max_depth or 100] (:218-262)
 0 with fewer than 100 valid pixels (:398-400).  One pair of reduction kernels + one gradient kernel through
-`psfm_supervised_loss[_backward]`.  The optional multi-scale Sobel gradient term (`gradient_weight`, default 0.0)
-is not provided and is refused; the reference's diagnostic statistics (quantiles, out-of-range fractions) are not
-computed -- the parts of the loss are logged."""
+`psfm_supervised_loss[_backward]`.  With `gradient_weight > 0` (train_resnet_san_ncdb_dual_head_640x384.yaml: 0.2) the
+multi-scale Sobel gradient term (:116-174) is added through `psfm_sobel_gradient_loss[_backward]`.  The reference's
+diagnostic statistics (quantiles, out-of-range fractions) and its NaN guards are not reproduced -- the parts of the loss
+are logged."""
 from typing import Optional
 
 from packnet_sfm.losses.loss_base import LossBase
@@ -18,8 +19,6 @@ class SSISilogLoss(LossBase):
                  gradient_weight=0.0, gradient_scales=4,
                  min_depth: Optional[float] = None, max_depth: Optional[float] = None):
         super().__init__()
-        if gradient_weight > 0:
-            raise NotImplementedError('the multi-scale gradient term of SSISilogLoss (gradient_weight > 0) is not provided')
         self.alpha = alpha
         self.silog_ratio = silog_ratio
         self.silog_ratio2 = silog_ratio2
@@ -46,6 +45,13 @@ class SSISilogLoss(LossBase):
                                       ratio2=self.silog_ratio2, alpha=self.alpha, ssi_weight=self.ssi_weight,
                                       silog_weight=self.silog_weight, clamp_min=cmin, clamp_max=cmax)
         self.state = st
+        gradient_loss = 0.0
+        if self.gradient_weight > 0:
+            from packnet_sfm.block_ops import sobel_gradient_loss_op
+            gradient_loss, self.gradient_state = sobel_gradient_loss_op(pred_inv_depth, gt_inv_depth, mask=mask,
+                                                                        scales=self.gradient_scales)
+            # fewer than 100 valid pixels: the whole loss is the constant 0 (:398-400); decided on the device
+            loss = loss + (st[4] >= 100).to(loss.dtype) * (self.gradient_weight * gradient_loss)
         self.add_metric('ssi_mean', st[10])
         self.add_metric('ssi_var', st[11])
         self.add_metric('silog1', st[12])
@@ -53,7 +59,7 @@ class SSISilogLoss(LossBase):
         self.add_metric('silog_var', (st[12] - st[13]).abs())
         self.add_metric('ssi_component', st[8])
         self.add_metric('silog_component', st[9])
-        self.add_metric('gradient_component', 0.0)
+        self.add_metric('gradient_component', gradient_loss)
         self.add_metric('ssi_weight_used', self.ssi_weight)
         self.add_metric('silog_weight_used', self.silog_weight)
         self.add_metric('gradient_weight_used', self.gradient_weight)

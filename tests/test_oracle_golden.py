@@ -183,3 +183,21 @@ def test_depth_metrics_oracle_matches_reference():
         np.testing.assert_array_equal(got, gold[name], err_msg=name)
     with pytest.raises(NotImplementedError):
         M.scale_depth(torch.ones(1, 1, 2, 2), torch.ones(1, 1, 4, 4), 'bottom-left')
+
+
+def test_ssi_gradient_term_oracle_matches_reference():
+    """SSISilogLoss with gradient_weight = 0.2 (multi-scale Sobel term, losses/ssi_silog_loss.py:116-174) vs the reference's
+    own SupervisedLoss (oracle/gen_golden_supervised.py::gradient_term)."""
+    import supervised_oracle as S
+    from supervised_cases import GRAD_CASES, GRAD_KW, make_grad_inputs
+    gold = load_golden('ssi_gradient')
+    for name, (B, H, W, use_mask, gs) in GRAD_CASES.items():
+        preds, gt, masks = make_grad_inputs(name)
+        preds = [p.requires_grad_() for p in preds]
+        loss = S.supervised_loss(preds, gt, 'sparse-ssi-silog', 1, masks=masks, **dict(GRAD_KW, gradient_scales=gs))
+        np.testing.assert_allclose(float(loss), gold[name + '/loss'], rtol=1e-12, atol=1e-300, err_msg=name)
+        if torch.is_tensor(loss) and loss.requires_grad:
+            loss.backward()
+            np.testing.assert_allclose(preds[0].grad.numpy(), gold[name + '/d_pred'], rtol=1e-10, atol=1e-14, err_msg=name)
+        else:
+            assert not gold[name + '/d_pred'].any()

@@ -142,3 +142,51 @@ def test_dual_head_fp32_full_size():
         assert rel <= 2e-3, rel
     with pytest.raises(AssertionError):
         DualHeadDepthLoss(max_depth=1.0, min_depth=2.0)
+
+
+# ---- SSISilogLoss with its multi-scale Sobel gradient term (gradient_weight > 0) ----
+from supervised_cases import GRAD_CASES, GRAD_KW, make_grad_inputs  # noqa: E402
+
+
+@pytest.mark.parametrize('name', sorted(GRAD_CASES))
+def test_gradient_term_fp64_matches_reference_fixtures(name):
+    """fp64 kernels vs the reference's SupervisedLoss('sparse-ssi-silog', gradient_weight=0.2).  The reference subtracts two
+    Sobel responses that both carry the 1e6 m fills of the invalid pixels (cancellation noise ~1e-10 absolute per pixel);
+    the kernels take the Sobel of the difference, hence 1e-9 relative on the loss and 1e-12 absolute on the gradient."""
+    from packnet_sfm.losses.supervised_loss import SupervisedLoss
+    gold = load_golden('ssi_gradient')
+    B, H, W, use_mask, gs = GRAD_CASES[name]
+    preds, gt, masks = make_grad_inputs(name)
+    dev = 'cuda:0'
+    preds = [p.to(dev).requires_grad_() for p in preds]
+    L = SupervisedLoss(supervised_method='sparse-ssi-silog', supervised_num_scales=1, **dict(GRAD_KW, gradient_scales=gs))
+    out = L(preds, gt.to(dev), masks=None if masks is None else [m.to(dev) for m in masks])
+    out['loss'].backward()
+    np.testing.assert_allclose(out['loss'].item(), gold[name + '/loss'], rtol=1e-9, atol=1e-300)
+    np.testing.assert_allclose(out['metrics']['s0/gradient_component'].item() if name != 'few_valid' else 0.0,
+                               gold[name + '/gradient_component'], rtol=1e-9)
+    g = gold[name + '/d_pred']
+    np.testing.assert_allclose(preds[0].grad.cpu().numpy(), g, rtol=1e-9, atol=1e-12 * max(1.0, np.abs(g).max()))
+
+
+def test_gradient_term_fp32_at_full_size():
+    """NCDB 640x384, batch 4: fp32 kernels vs the fp64 oracle (the oracle's own fp32 run loses ~0.1 m per Sobel response
+    to the 1e6 m fills; the kernels do not)."""
+    preds, gt, _ = S.synth_supervised(4, 384, 640, 1, torch.float64, seed=9)
+    p64 = [p.clone().requires_grad_() for p in preds]
+    ref = S.supervised_loss(p64, gt, 'sparse-ssi-silog', 1, **GRAD_KW)
+    ref.backward()
+    from packnet_sfm.losses.supervised_loss import SupervisedLoss
+    dev = 'cuda:0'
+    p32 = [p.float().to(dev).requires_grad_() for p in preds]
+    out = SupervisedLoss(supervised_method='sparse-ssi-silog', supervised_num_scales=1, **GRAD_KW)(p32, gt.float().to(dev))
+    out['loss'].backward()
+    assert abs(out['loss'].item() - ref.item()) / abs(ref.item()) < 1e-5
+    # the gradient of |.| flips sign where a Sobel response of the difference is within rounding of 0: compare in L2
+    err = (p32[0].grad.double().cpu() - p64[0].grad).norm() / p64[0].grad.norm()
+    assert err < 1e-3, err
+    # deterministic
+    p32b = [p.float().to(dev).requires_grad_() for p in preds]
+    out2 = SupervisedLoss(supervised_method='sparse-ssi-silog', supervised_num_scales=1, **GRAD_KW)(p32b, gt.float().to(dev))
+    out2['loss'].backward()
+    assert torch.equal(out['loss'], out2['loss']) and torch.equal(p32[0].grad, p32b[0].grad)
