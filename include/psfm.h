@@ -209,7 +209,7 @@ int psfm_grid_sample_backward(int B, int Hi, int Wi, int Ho, int Wo, int dt, int
 
 /* SupervisedLoss.calculate_loss for one scale (losses/supervised_loss.py:292-417) with the loss
  * functions get_loss_func returns for '...l1' / '...mse' / '...silog' (:84-92, SilogLoss :67-82) and '...ssi-silog'
- * (SSISilogLoss, losses/ssi_silog_loss.py:53-429, without its multi-scale gradient term, gradient_weight = 0).
+ * (SSISilogLoss, losses/ssi_silog_loss.py:53-429; its multi-scale gradient term: psfm_sobel_gradient_loss below).
  * sparse != 0: the 'sparse-*' methods -- valid = gt > 0 (and mask != 0 when a [N] byte mask is given); pred and gt are
  * filled with 1e-6 elsewhere and the mean still runs over all N elements, as the reference does; ssi-silog averages
  * over the valid elements only.  pred, gt, d_pred: [N] of type dt, 16-byte aligned.  hp: HOST double[6] = {silog ratio2, ssi alpha, ssi weight,

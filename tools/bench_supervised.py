@@ -28,8 +28,12 @@ def main():
             gt = 1.0 / (2.0 + 38.0 * torch.rand(B, 1, H, W, generator=g))
             gt = torch.where(torch.rand(B, 1, H, W, generator=g) < 0.4, gt, torch.zeros_like(gt)).to(dev)
             sets.append((pred, gt))
-        for method in ('sparse-l1', 'sparse-silog', 'sparse-ssi-silog'):
-            L = SupervisedLoss(supervised_method=method, supervised_num_scales=1)
+        for method in ('sparse-l1', 'sparse-silog', 'sparse-ssi-silog', 'sparse-ssi-silog+sobel'):
+            if method.endswith('+sobel'):   # the dual-head NCDB yaml: gradient_weight 0.2 over 4 scales
+                L = SupervisedLoss(supervised_method='sparse-ssi-silog', supervised_num_scales=1, gradient_weight=0.2,
+                                   gradient_scales=4, min_depth=0.5, max_depth=80.0)
+            else:
+                L = SupervisedLoss(supervised_method=method, supervised_num_scales=1)
 
             def step(i):
                 pred, gt = sets[i % R]
@@ -64,7 +68,7 @@ def main():
                     step(r)
                 graphs.append(gr)
             ms = timed(lambda i: graphs[i % R].replay())
-            gbs = B * H * W * 20 / (ms * 1e-3) / 1e9
+            gbs = B * H * W * (40 if method.endswith('+sobel') else 20) / (ms * 1e-3) / 1e9
             print(json.dumps({'method': method, 'shape': [B, H, W], 'ms_per_step_eager': ms_eager, 'ms_per_step_graph': ms, 'frames_per_s': B / (ms * 1e-3),
                               'algorithmic_GBs': gbs, 'frac_of_hbm_peak': gbs / peak}))
 
