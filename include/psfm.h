@@ -231,8 +231,8 @@ int psfm_supervised_loss_backward(int method, int sparse, size_t N, int dt, cons
  * (losses/supervised_loss.py:314-333).  Per scale s < scales: depth maps resized by 0.5^s (bilinear, align_corners=False),
  * mask by nearest, mean |Sobel(pred) - Sobel(gt)| (x plus y) over the masked interior; average over the scales that have a
  * masked pixel (0 when none).  loss_out: real[1].  state: DEVICE double[20] = {loss, scales used, 0, 0, count per scale [8],
- * loss per scale [8]}.  codes: DEVICE bytes (psfm_sobel_gradient_code_bytes), written by the forward call and read by the
- * backward call together with state.  Backward: d_pred[B,1,H,W] = grad_loss[0] * d loss / d pred_inv. */
+ * loss per scale [8]}.  codes: DEVICE bytes (psfm_sobel_gradient_code_bytes: one sign code per pyramid pixel, then the eight
+ * per-scale coefficients of the backward as doubles), written by the forward call and read by the backward call.  Backward: d_pred[B,1,H,W] = grad_loss[0] * d loss / d pred_inv. */
 size_t psfm_sobel_gradient_code_bytes(int B, int H, int W, int scales);
 size_t psfm_sobel_gradient_workspace_bytes(int B, int H, int W, int scales);
 int psfm_sobel_gradient_loss(int B, int H, int W, int dt, int scales, const void* pred_inv, const void* gt_inv,

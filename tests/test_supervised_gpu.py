@@ -190,3 +190,30 @@ def test_gradient_term_fp32_at_full_size():
     out2 = SupervisedLoss(supervised_method='sparse-ssi-silog', supervised_num_scales=1, **GRAD_KW)(p32b, gt.float().to(dev))
     out2['loss'].backward()
     assert torch.equal(out['loss'], out2['loss']) and torch.equal(p32[0].grad, p32b[0].grad)
+
+
+@pytest.mark.parametrize('use_mask', [False, True])
+def test_gradient_term_block_and_pixel_kernels_agree(use_mask):
+    """H, W multiples of 4 with 16-byte aligned maps run the 4 x 4 block pyramid and the quad backward kernels, anything else
+    the per-pixel kernels (same expressions): identical bits for the loss, the per-scale state and the gradient."""
+    from packnet_sfm.block_ops import sobel_gradient_loss_op
+    dev = 'cuda:0'
+    preds, gt, _ = S.synth_supervised(2, 48, 72, 1, torch.float32, seed=5)
+    mask = (torch.rand(gt.shape, generator=torch.Generator().manual_seed(1)) < 0.8).to(torch.uint8) if use_mask else None
+    n = gt.numel()
+
+    def run(shift):
+        bp, bg = torch.zeros(n + 8, device=dev), torch.zeros(n + 8, device=dev)
+        p, g = bp[shift:shift + n].view(gt.shape), bg[shift:shift + n].view(gt.shape)
+        p.copy_(preds[0])
+        g.copy_(gt)
+        p.requires_grad_()
+        assert p.data_ptr() % 16 == 4 * shift
+        loss, state = sobel_gradient_loss_op(p, g, mask=None if mask is None else mask.to(dev), scales=4)
+        (3.0 * loss).backward()
+        return loss.detach().clone(), state.clone(), p.grad.clone()
+
+    a, b = run(0), run(1)
+    assert a[0].item() > 0 and a[2].abs().max().item() > 0
+    for u, v in zip(a, b):
+        assert torch.equal(u, v)

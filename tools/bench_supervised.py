@@ -18,7 +18,11 @@ def main():
         peak = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))['hbm_gbs']
     except Exception:
         pass
-    for (B, H, W) in ((8, 192, 640), (16, 384, 640), (4, 1216, 1936)):
+    shapes = ((8, 192, 640), (16, 384, 640), (4, 1216, 1936))
+    if os.environ.get('PSFM_BENCH_SHAPES'):      # e.g. 4x1216x1936,8x192x640 (for a short ncu launch list)
+        shapes = tuple(tuple(int(v) for v in t.split('x')) for t in os.environ['PSFM_BENCH_SHAPES'].split(','))
+    only = os.environ.get('PSFM_BENCH_METHODS')
+    for (B, H, W) in shapes:
         g = torch.Generator('cpu').manual_seed(3)
         # rotate > 3x L2 worth of inputs
         R = max(2, int(3 * 126e6 / (B * H * W * 12)) + 1)
@@ -29,6 +33,8 @@ def main():
             gt = torch.where(torch.rand(B, 1, H, W, generator=g) < 0.4, gt, torch.zeros_like(gt)).to(dev)
             sets.append((pred, gt))
         for method in ('sparse-l1', 'sparse-silog', 'sparse-ssi-silog', 'sparse-ssi-silog+sobel'):
+            if only and method not in only.split(','):
+                continue
             if method.endswith('+sobel'):   # the dual-head NCDB yaml: gradient_weight 0.2 over 4 scales
                 L = SupervisedLoss(supervised_method='sparse-ssi-silog', supervised_num_scales=1, gradient_weight=0.2,
                                    gradient_scales=4, min_depth=0.5, max_depth=80.0)
