@@ -17,6 +17,7 @@
 // Algorithmic bytes: forward reads pred + gt (8 B/px), backward reads them again and writes d pred (12 B/px).
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include "psfm_device.cuh"
 #include "profile.h"
 
@@ -140,7 +141,10 @@ __device__ __forceinline__ int sgn_code(double v) { return v > 0 ? 2 : (v < 0 ? 
 
 // grid (max CTAs of a level, S): CTA (k, s) owns pixels [k kST kSP, (k + 1) kST kSP) of level s over the whole batch,
 // kSP per thread at stride kST (coalesced), so that the finish kernel has few partials to add
-template <typename real>
+// QUAD0 (W a multiple of 4, 16-byte aligned maps): at level 0 a thread takes quads of a row -- three rows of D as one
+// 16-byte load + two scalars each (18 values for 4 responses instead of 32), gt and mask as vectors, the 4 codes as one word;
+// same response expressions, same pixels per CTA (the partials keep their layout)
+template <typename real, bool QUAD0>
 __global__ void __launch_bounds__(kST) sobel_kernel(SobelCfg c, const real* gt, const uint8_t* mask, const real* D,
                                                     uint8_t* codes, double* part) {
   __shared__ real scratch[3 * (kST / 32)];
@@ -150,6 +154,43 @@ __global__ void __launch_bounds__(kST) sobel_kernel(SobelCfg c, const real* gt, 
   const unsigned int plane = (unsigned int)Hs * Ws, total = plane * c.B;
   const bool has_out = Hs >= 3 && Ws >= 3;
   real v[3] = {real(0), real(0), real(0)};
+  if (QUAD0 && s == 0) {
+#pragma unroll
+    for (int j = 0; j < kSP / 4; ++j) {
+      const unsigned int r = ((blockIdx.x * (kSP / 4) + j) * kST + threadIdx.x) * 4;
+      if (r >= total) break;
+      const unsigned int b = r / plane, q = r - b * plane;
+      const int yy = (int)(q / Ws), xx = (int)(q - (unsigned int)yy * Ws);
+      unsigned int word = 0x01010101u * (unsigned int)kNoCode;
+      if (has_out && yy >= 1 && yy <= Hs - 2) {
+        real g4[4];
+        ld4(gt + r, g4);
+        const unsigned int mk = mask ? __ldg(reinterpret_cast<const unsigned int*>(mask + r)) : 0x01010101u;
+        const real* p = D + r;
+        real n[6], m[6], o[6];
+        ld4(p - Ws, n + 1); ld4(p, m + 1); ld4(p + Ws, o + 1);
+        const bool hl = xx > 0, hr = xx + 4 < Ws;
+        n[0] = hl ? p[-Ws - 1] : real(0); m[0] = hl ? p[-1] : real(0); o[0] = hl ? p[Ws - 1] : real(0);
+        n[5] = hr ? p[-Ws + 4] : real(0); m[5] = hr ? p[4] : real(0); o[5] = hr ? p[Ws + 4] : real(0);
+        word = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          unsigned int code = kNoCode;
+          if (xx + k >= 1 && xx + k <= Ws - 2 && g4[k] > real(0) && ((mk >> (8 * k)) & 0xffu) != 0) {
+            const real gx = (n[k + 2] + real(2) * m[k + 2] + o[k + 2]) - (n[k] + real(2) * m[k] + o[k]);
+            const real gy = (o[k] + real(2) * o[k + 1] + o[k + 2]) - (n[k] + real(2) * n[k + 1] + n[k + 2]);
+            v[0] += rabs(gx); v[1] += rabs(gy); v[2] += real(1);
+            code = (unsigned int)(sgn_code((double)gx) | (sgn_code((double)gy) << 2));
+          }
+          word |= code << (8 * k);
+        }
+      }
+      *reinterpret_cast<unsigned int*>(codes + r) = word;
+    }
+    block_reduce<real, 3>(v, scratch);
+    if (threadIdx.x < 3) part[((size_t)s * gridDim.x + blockIdx.x) * 3 + threadIdx.x] = (double)v[threadIdx.x];
+    return;
+  }
 #pragma unroll 4
   for (int j = 0; j < kSP; ++j) {
     const unsigned int r = (blockIdx.x * kSP + j) * kST + threadIdx.x;
@@ -477,17 +518,27 @@ int psfm_sobel_gradient_loss(int B, int H, int W, int dt, int scales, const void
   cudaStream_t st = (cudaStream_t)stream;
   const unsigned int total = c.off[kMaxGS];
   double* part = (double*)((char*)workspace + al256s((size_t)total * sizeof(double)));
+  // level-0 quads in the response kernel (PSFM_SOBEL_QUADS=0: the per-pixel form, for comparison)
+  static const bool quads_on = [] { const char* e = getenv("PSFM_SOBEL_QUADS"); return !(e && e[0] == '0'); }();
+  const bool quad0 = quads_on && W % 4 == 0 && ((uintptr_t)gt_inv | (uintptr_t)workspace) % 16 == 0 &&
+                     ((uintptr_t)mask | (uintptr_t)codes) % 4 == 0;
   count_launches(3);
   if (dt == PSFM_F64) {
     typedef double real;
     launch_pyramid<real>(c, (const real*)pred_inv, (const real*)gt_inv, (const uint8_t*)mask, (real*)workspace, st);
-    sobel_kernel<real><<<dim3(c.nblk[0], scales), kST, 0, st>>>(c, (const real*)gt_inv, (const uint8_t*)mask, (const real*)workspace, (uint8_t*)codes, part);
+    if (quad0)
+      sobel_kernel<real, true><<<dim3(c.nblk[0], scales), kST, 0, st>>>(c, (const real*)gt_inv, (const uint8_t*)mask, (const real*)workspace, (uint8_t*)codes, part);
+    else
+      sobel_kernel<real, false><<<dim3(c.nblk[0], scales), kST, 0, st>>>(c, (const real*)gt_inv, (const uint8_t*)mask, (const real*)workspace, (uint8_t*)codes, part);
     sobel_finish_kernel<real><<<1, kFT, 0, st>>>(c, c.nblk[0], part, (double*)state, (real*)loss_out,
                                                  (double*)((char*)codes + al256s(total)));
   } else {
     typedef float real;
     launch_pyramid<real>(c, (const real*)pred_inv, (const real*)gt_inv, (const uint8_t*)mask, (real*)workspace, st);
-    sobel_kernel<real><<<dim3(c.nblk[0], scales), kST, 0, st>>>(c, (const real*)gt_inv, (const uint8_t*)mask, (const real*)workspace, (uint8_t*)codes, part);
+    if (quad0)
+      sobel_kernel<real, true><<<dim3(c.nblk[0], scales), kST, 0, st>>>(c, (const real*)gt_inv, (const uint8_t*)mask, (const real*)workspace, (uint8_t*)codes, part);
+    else
+      sobel_kernel<real, false><<<dim3(c.nblk[0], scales), kST, 0, st>>>(c, (const real*)gt_inv, (const uint8_t*)mask, (const real*)workspace, (uint8_t*)codes, part);
     sobel_finish_kernel<real><<<1, kFT, 0, st>>>(c, c.nblk[0], part, (double*)state, (real*)loss_out,
                                                  (double*)((char*)codes + al256s(total)));
   }

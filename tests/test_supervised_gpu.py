@@ -195,7 +195,7 @@ def test_gradient_term_fp32_at_full_size():
 @pytest.mark.parametrize('use_mask', [False, True])
 def test_gradient_term_block_and_pixel_kernels_agree(use_mask):
     """H, W multiples of 4 with 16-byte aligned maps run the 4 x 4 block pyramid and the quad backward kernels, anything else
-    the per-pixel kernels (same expressions): identical bits for the loss, the per-scale state and the gradient."""
+    the per-pixel kernels (same expressions): same loss, identical counts and gradient bits."""
     from packnet_sfm.block_ops import sobel_gradient_loss_op
     dev = 'cuda:0'
     preds, gt, _ = S.synth_supervised(2, 48, 72, 1, torch.float32, seed=5)
@@ -215,5 +215,9 @@ def test_gradient_term_block_and_pixel_kernels_agree(use_mask):
 
     a, b = run(0), run(1)
     assert a[0].item() > 0 and a[2].abs().max().item() > 0
-    for u, v in zip(a, b):
-        assert torch.equal(u, v)
+    # the response kernel's quad form adds the same |gx|, |gy| in another order: loss and per-scale losses to fp32 summation
+    # order, the counts (hence the backward's coefficients) and the gradient bit for bit
+    torch.testing.assert_close(a[0], b[0], rtol=2e-6, atol=0)
+    torch.testing.assert_close(a[1], b[1], rtol=2e-6, atol=0)
+    assert torch.equal(a[1][1:12], b[1][1:12])
+    assert torch.equal(a[2], b[2])
