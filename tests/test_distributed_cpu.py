@@ -43,7 +43,9 @@ def _worker(rank, world, port, q):
     bucket = torch.cat([loss.view(1)] + [g.sum(0) for g in d_vecs])
     dist.all_reduce(bucket, op=dist.ReduceOp.SUM)
     bucket /= world
-    q.put((rank, bucket, [g.clone() for g in d_invd]))
+    # numpy arrays travel by value: a tensor in a Queue is a shared-memory handle the parent may fetch after this
+    # process has exited (ConnectionResetError)
+    q.put((rank, bucket.numpy().copy(), [g.detach().numpy().copy() for g in d_invd]))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -60,6 +62,7 @@ def test_batch_sharded_loss_allreduce_world2():
     for p in procs:
         p.start()
     res = sorted([q.get(timeout=240) for _ in range(world)], key=lambda r: r[0])
+    res = [(r, torch.from_numpy(b), [torch.from_numpy(g) for g in gs]) for r, b, gs in res]
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
