@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define PSFM_ABI_VERSION 3
+#define PSFM_ABI_VERSION 4
 #define PSFM_MAX_SCALES 4
 #define PSFM_MAX_CTX 8
 
@@ -98,6 +98,14 @@ typedef struct psfm_loss_io {
   uint8_t* sel[PSFM_MAX_SCALES];                    /* [B,Hs,Ws] u8: arg-min candidate (fwd out, bwd in) */
   void* d_inv_depth[PSFM_MAX_SCALES];               /* [B,1,Hs,Ws] real (bwd out, overwritten)       */
   void* d_pose[PSFM_MAX_CTX];                       /* [B,4,4] real (bwd out, overwritten; row 3 = 0) */
+  uint32_t* dbg[PSFM_MAX_SCALES];                   /* NULL, or [C,B,Hs,Ws] u32 (test hook of psfm_loss_forward_backward,
+                                                     * pinhole sweep kernels): the discrete decisions the loss took at
+                                                     * each pixel -- bits 0-11 floor(ix) + 8, bits 12-23 floor(iy) + 8 of
+                                                     * the bilinear tap of context c (after the padding mode's clipping);
+                                                     * io->sel[i] then receives the arg-min candidate as in
+                                                     * psfm_loss_forward.  Lets the parity tests name the pixels whose
+                                                     * tap or arg-min ACTUALLY differs from the fp64 oracle's
+                                                     * (SURVEY.md section 8(c), T2). */
 } psfm_loss_io;
 
 int psfm_abi_version(void);

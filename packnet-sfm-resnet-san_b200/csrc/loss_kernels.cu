@@ -487,7 +487,7 @@ void build_params(const psfm_loss_cfg* cfg, const psfm_loss_io* io, void* ws, Lo
   P.loss_part = (double*)(w + L.loss_part); P.pose_part = w + L.pose_part; P.clip_part = (double*)(w + L.clip_part);
   for (int s = 0; s < cfg->n; ++s) {
     ScaleDesc& S = P.sc[s];
-    S.image = io->image[s]; S.invd = io->inv_depth[s]; S.mask = io->mask[s]; S.sel = io->sel[s];
+    S.image = io->image[s]; S.invd = io->inv_depth[s]; S.mask = io->mask[s]; S.sel = io->sel[s]; S.dbg = io->dbg[s];
     S.d_invd = io->d_inv_depth[s];
     for (int j = 0; j < cfg->C; ++j) S.ctx[j] = io->ctx[s][j];
     S.H = cfg->Hs[s]; S.W = cfg->Ws[s];

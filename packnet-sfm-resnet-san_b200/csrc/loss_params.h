@@ -17,6 +17,7 @@ struct ScaleDesc {
   const void* invd;                  // [B,1,H,W] real
   const void* mask;                  // [B,1,H,W] or null
   uint8_t* sel;                      // [B,H,W]
+  uint32_t* dbg;                     // [C][B][H][W] decision words of the debug instantiations, or null
   void* d_invd;                      // [B,1,H,W] real
   int H, W;
   int Hd, Wd;                        // size of the inverse-depth map in memory (== H, W unless upsampled in-kernel)

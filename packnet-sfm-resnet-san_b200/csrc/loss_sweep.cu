@@ -25,87 +25,10 @@
 #include "loss_tile.cuh"
 #include "profile.h"
 
+#include "sweep_common.cuh"
+
 namespace psfm {
 
-constexpr int kPrepVals = 3;         // sum d, sum |dx d| wx, sum |dy d| wy
-constexpr int kPrepInner = 30;       // columns a prep warp produces (32 lanes - 1 halo each side)
-constexpr int kPrepWarps = 4;        // independent warps per prep CTA
-constexpr int kInner = 28;           // columns a sweep warp produces (32 lanes - 2 halo each side)
-
-constexpr int kPadLo = 2;            // zero border of the packed context images: taps reach -2 .. size + 2
-constexpr int kPadHi = 3;
-
-struct SweepSet {                    // scales of equal resolution sharing the same images
-  int ns;
-  int scale[PSFM_MAX_SCALES];
-  int H, W;
-  int nstrips, nchunks, chunk_h;     // sweep kernel decomposition
-  int pstrips, pchunks, pchunk_h;    // prep kernel decomposition
-  int Hp, Wp;                        // padded size of the packed context images
-  void* ra;                          // real4 [B][H][W]: target pixel y x3, mask value
-  void* rb;                          // real4 [B][H][W]: mean(y) x3, min identity photometric value (automask)
-  void* rc;                          // real4 [B][H][W]: E[y^2]-mean(y)^2+C2 x3, candidate index of that min
-  void* wxy;                         // real [B][H][W][2]: exp(-mean|dx I|), exp(-mean|dy I|)
-  void* ray;                         // real [B][H][W][2]: fisheye only, x and y of the pixel's viewing ray (z = 1)
-  void* ctxp[PSFM_MAX_CTX];          // real4 [B][Hp][Wp]: context image (r, g, b, 0), zero border
-};
-
-template <int V> struct IntC { static constexpr int value = V; };
-
-// 4-vector of the arithmetic type with 16-byte vector loads / stores
-template <typename real> struct alignas(16) Real4 { real x, y, z, w; };
-__device__ __forceinline__ Real4<float> ld4(const Real4<float>* p) {
-  const float4 v = __ldg((const float4*)p);
-  return Real4<float>{v.x, v.y, v.z, v.w};
-}
-__device__ __forceinline__ Real4<double> ld4(const Real4<double>* p) {
-  const double2 a = __ldg((const double2*)p), b = __ldg((const double2*)p + 1);
-  return Real4<double>{a.x, a.y, b.x, b.y};
-}
-__device__ __forceinline__ void st4(Real4<float>* p, float x, float y, float z, float w) {
-  *(float4*)p = make_float4(x, y, z, w);
-}
-__device__ __forceinline__ void st4(Real4<double>* p, double x, double y, double z, double w) {
-  ((double2*)p)[0] = make_double2(x, y);
-  ((double2*)p)[1] = make_double2(z, w);
-}
-
-template <typename real> struct SweepConsts {   // hyper-parameters pre-converted to the arithmetic type
-  real ssim_w3;                      // ssim_loss_weight / 3
-  real k1;                           // (1 - ssim_loss_weight) / 3
-  real C1, C2;
-  real inv_count;                    // weight of one pixel in the photometric mean (same for a set)
-  real premap_lo, premap_hi;
-  real pad_;
-  real coef_x[PSFM_MAX_SCALES], coef_y[PSFM_MAX_SCALES], sf[PSFM_MAX_SCALES];   // per scale id
-};
-
-struct SweepParams {
-  LossParams P;
-  SweepSet set;
-  SweepConsts<float> cf;
-  SweepConsts<double> cd;
-  // per scale (indexed by the scale id)
-  double* prep_part[PSFM_MAX_SCALES];   // [B][punits][kPrepVals]
-  void* stats[PSFM_MAX_SCALES];         // real [B][4]: clamped mean, coupling constant, SX, SY
-  double* loss_part[PSFM_MAX_SCALES];   // [B][nunits] photometric sums
-  void* pose_part[PSFM_MAX_SCALES];     // real [B][nunits][C][12]
-};
-
-// ------------------------------------------------------------------------------------------
-// prep kernel: grid (ceil(punits / kPrepWarps), B), 32 * kPrepWarps threads; every warp is an
-// independent (strip, chunk) unit.  Lane l is column c0 - 1 + l; step t loads row t + 1 and finishes
-// row p = t - 1.  One pass over the rows handles the CT contexts [j0, j0 + CT) together (packed copy,
-// identity-reprojection term); the pass with j0 == 0 also emits the image-only outputs.
-// Per-channel arithmetic runs on (channel 0, channel 1) pairs + a scalar channel 2 (pair_math.cuh).
-// ------------------------------------------------------------------------------------------
-// F.interpolate(mode='nearest') source index (utils/image.py:148-176 via models/model_utils.py:152-176)
-__device__ __forceinline__ int nearest_src(int dst, float scale, int size, bool active) {
-  return active ? min((int)floorf((float)dst * scale), size - 1) : dst;
-}
-
-__device__ __forceinline__ int value_bits(float v) { return __float_as_int(v); }
-__device__ __forceinline__ int value_bits(double v) { return __double2hiint(v); }
 
 template <typename real, typename img_t, int CT, bool AUTOMASK, bool FIRST>
 __global__ void __launch_bounds__(32 * kPrepWarps) prep_kernel(const SweepParams SP, const int j0) {
@@ -428,45 +351,6 @@ __global__ void __launch_bounds__(256) fisheye_ray_kernel(const SweepParams SP) 
 // evaluates SSIM / the candidate min at row p = t - 1 and the adjoint (d/d inv_depth, d/d pose)
 // at row q = t - 2.
 // ------------------------------------------------------------------------------------------
-template <typename real> struct SweepCam {
-  real ki[9];   // reference `Kinv` (camera.py:73-81)
-  real rk[9];   // scaled ref_K
-  real T[12];   // rows of the 3x4 [R|t] (pose.py:80-86)
-};
-
-template <typename real>
-__device__ __forceinline__ void sweep_cam(SweepCam<real>& c, const LossParams& P, int b, int j, real sf) {
-  CamPair<real> cp;
-  setup_cam<real>(cp, (const real*)P.K, (const real*)P.refK, b, sf);
-#pragma unroll
-  for (int i = 0; i < 9; ++i) { c.ki[i] = cp.ki[i]; c.rk[i] = cp.rk[i]; }
-  const real* T = (const real*)P.pose[j] + (size_t)b * 16;
-#pragma unroll
-  for (int i = 0; i < 12; ++i) c.T[i] = T[i];
-}
-
-
-template <typename real> __device__ __forceinline__ const SweepConsts<real>& sweep_consts(const SweepParams& SP);
-template <> __device__ __forceinline__ const SweepConsts<float>& sweep_consts<float>(const SweepParams& SP) { return SP.cf; }
-template <> __device__ __forceinline__ const SweepConsts<double>& sweep_consts<double>(const SweepParams& SP) { return SP.cd; }
-
-__device__ __forceinline__ void load_pair(const float* p, float& a, float& b) {
-  const float2 v = __ldg((const float2*)p);
-  a = v.x; b = v.y;
-}
-__device__ __forceinline__ void load_pair(const double* p, double& a, double& b) {
-  const double2 v = __ldg((const double2*)p);
-  a = v.x; b = v.y;
-}
-
-// mag * sign(x) with sign(0) = 0
-__device__ __forceinline__ float signed_by(float mag, float x) {
-  const float s = __int_as_float(__float_as_int(mag) ^ (__float_as_int(x) & 0x80000000));
-  return x == 0.0f ? 0.0f : s;
-}
-__device__ __forceinline__ double signed_by(double mag, double x) {
-  return x > 0.0 ? mag : (x < 0.0 ? -mag : 0.0);
-}
 
 #ifndef PSFM_SWEEP_MINB
 #define PSFM_SWEEP_MINB 1            // resident CTAs per SM the 2-context fp32 instantiation is compiled for
@@ -1101,6 +985,22 @@ static int pick_sweep_chunk(int H, long ctas_per_chunk, int C, bool f64) {
   return best;
 }
 
+// Rows per unit of the two-pixels-per-lane sweep (loss_sweep2.cu): h rows run h + 4 steps, any height is allowed;
+// 148 SMs x (8 / C) CTAs are resident (255 registers per thread).
+static int pick_sweep2_chunk(int H, long ctas_per_chunk, int C, bool f64) {
+  const long resident = 148L * (f64 ? 1 : (C <= 1 ? 8 : (C == 2 ? 4 : 2)));
+  int best = H;
+  double best_cost = 1e300;
+  for (int ch = (H < kMinChunk ? H : kMinChunk); ch <= H; ++ch) {
+    const long chunks = cdiv(H, ch);
+    if (ch != cdiv(H, (int)chunks)) continue;            // the balanced height for this number of chunks
+    const long waves = (chunks * ctas_per_chunk + resident - 1) / resident;
+    const double cost = (double)waves * (double)(ch + 4);
+    if (cost < best_cost * 0.999) { best_cost = cost; best = ch; }
+  }
+  return best;
+}
+
 // Rows per prep unit (one warp): h rows run h + 2 steps, rounded up to the 2-step unrolling; 148 SMs x 2 CTAs x
 // 4 warps are resident.  Measured at config 2: 32 rows 63 us, 16 rows 68 us, 24 / 48 rows 78-79 us.
 static int pick_prep_chunk(int H, long warps_per_chunk) {
@@ -1118,6 +1018,8 @@ static int pick_prep_chunk(int H, long warps_per_chunk) {
   }
   return best;
 }
+
+static bool use_sweep2(const psfm_loss_cfg* cfg) { return sweep2_eligible(cfg) && env_int("PSFM_SWEEP2", 1) != 0; }
 
 static void make_plan(const psfm_loss_cfg* cfg, const psfm_loss_io* io, SweepPlan& pl) {
   const size_t rs = cfg->real_dtype == PSFM_F64 ? 8 : 4;
@@ -1143,6 +1045,12 @@ static void make_plan(const psfm_loss_cfg* cfg, const psfm_loss_io* io, SweepPla
                            : pick_sweep_chunk(S.H, (long)S.nstrips * S.ns * cfg->B, cfg->C, cfg->real_dtype == PSFM_F64);
     if (S.chunk_h < kMinChunk) S.chunk_h = S.H < kMinChunk ? S.H : kMinChunk;
     S.nchunks = cdiv(S.H, S.chunk_h);
+    S.nstrips2 = cdiv(S.W, kInner2);
+    const int forced2 = env_int("PSFM_SWEEP2_CHUNK", 0);
+    S.chunk_h2 = forced2 > 0 ? (forced2 < S.H ? forced2 : S.H)
+                             : pick_sweep2_chunk(S.H, (long)S.nstrips2 * S.ns * cfg->B, cfg->C, cfg->real_dtype == PSFM_F64);
+    if (S.chunk_h2 < kMinChunk) S.chunk_h2 = S.H < kMinChunk ? S.H : kMinChunk;
+    S.nchunks2 = cdiv(S.H, S.chunk_h2);
     S.pstrips = cdiv(S.W, kPrepInner);
     const int pforced = env_int("PSFM_PREP_CHUNK", 0);
     S.pchunk_h = pforced > 0 ? (pforced < S.H ? pforced : S.H) : pick_prep_chunk(S.H, (long)S.pstrips * cfg->B);
@@ -1171,7 +1079,7 @@ static void make_plan(const psfm_loss_cfg* cfg, const psfm_loss_io* io, SweepPla
   }
   for (int i = 0; i < pl.nsets; ++i) {
     const SweepSet& S = pl.sets[i];
-    for (int k = 0; k < S.ns; ++k) pl.nunits[S.scale[k]] = S.nstrips * S.nchunks;
+    for (int k = 0; k < S.ns; ++k) pl.nunits[S.scale[k]] = use_sweep2(cfg) ? S.nstrips2 * S.nchunks2 : S.nstrips * S.nchunks;
   }
   pl.total = off;
 }
@@ -1271,6 +1179,17 @@ static cudaError_t run_sweep(const psfm_loss_cfg* cfg, const psfm_loss_io* io, v
       if (cfg->camera_model == PSFM_CAM_FISHEYE)
         fisheye_ray_kernel<real><<<dim3(cdiv(S.H * S.W, 256), cfg->B), 256, 0, st>>>(SP);
     }
+    const bool debug = io->dbg[s0] != nullptr;
+    if (use_sweep2(cfg)) {
+      ProfScope ps(st, kTagFused, 1);
+      bool ups2 = false;
+      for (int k = 0; k < S.ns; ++k)
+        if (SP.P.sc[S.scale[k]].d_full != SP.P.sc[S.scale[k]].d_invd) ups2 = true;
+      const cudaError_t e2 = launch_sweep2<real>(SP, ups2, debug, st);
+      if (e2 != cudaSuccess) return e2;
+      continue;
+    }
+    if (debug) return cudaErrorNotSupported;        // decision words: two-pixels-per-lane sweep only
     const bool fisheye = cfg->camera_model == PSFM_CAM_FISHEYE;
     const int ring = fisheye ? 15 : (cfg->padding == PSFM_PAD_BORDER ? 11 : 10);
     const size_t smem = ((size_t)cfg->C * 4 * ring * 32 + (size_t)4 * cfg->C * 32 + (fisheye ? 24 * cfg->C : 0)) * sizeof(real);

@@ -55,7 +55,8 @@ class LossIO(C.Structure):
                 ('pose', C.c_void_p * MAX_CTX),
                 ('sel', C.c_void_p * MAX_SCALES),
                 ('d_inv_depth', C.c_void_p * MAX_SCALES),
-                ('d_pose', C.c_void_p * MAX_CTX)]
+                ('d_pose', C.c_void_p * MAX_CTX),
+                ('dbg', C.c_void_p * MAX_SCALES)]
 
 
 def _load():
@@ -133,7 +134,7 @@ def _load():
         fn = getattr(lib, name)
         fn.restype = i
         fn.argtypes = args
-    if lib.psfm_abi_version() != 3:
+    if lib.psfm_abi_version() != 4:
         raise ImportError('libpsfm_b200.so ABI version mismatch: %d' % lib.psfm_abi_version())
     return lib
 

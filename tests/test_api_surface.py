@@ -83,7 +83,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), 'libpsfm_b200.so does not export %s' % n
     assert sorted(_C.EXPORTS) == names, 'ctypes table and include/psfm.h disagree'
-    assert lib.psfm_abi_version() == 3
+    assert lib.psfm_abi_version() == 4
 
 
 def test_abi_argument_validation_without_gpu():
