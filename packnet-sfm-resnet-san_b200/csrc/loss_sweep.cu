@@ -73,9 +73,10 @@ __global__ void __launch_bounds__(32 * kPrepWarps) prep_kernel(const SweepParams
     xp0[jj] = (const img_t*)S0.ctx[j0 + jj] + (size_t)b * 3 * plane;
     cpk[jj] = (vec4*)S.ctxp[j0 + jj] + (size_t)b * S.Hp * S.Wp + kPadLo * S.Wp + kPadLo;
   }
-  vec4* ra = (vec4*)S.ra + (size_t)b * plane;
-  vec4* rb = (vec4*)S.rb + (size_t)b * plane;
-  vec4* rc = (vec4*)S.rc + (size_t)b * plane;
+  const int Wh = S.Wh, rplane = H * 2 * Wh * 3;
+  vec4* ra = (vec4*)S.ra + (size_t)b * rplane;
+  vec4* rb = (vec4*)S.rb + (size_t)b * rplane;
+  vec4* rc = (vec4*)S.rc + (size_t)b * rplane;
   real* wxy = (real*)S.wxy + (size_t)b * plane * 2;
   const img_t* maskp = S0.mask ? (const img_t*)S0.mask + (size_t)b * plane : nullptr;
   const real C1 = (real)P.C1, C2 = (real)P.C2;
@@ -127,7 +128,7 @@ __global__ void __launch_bounds__(32 * kPrepWarps) prep_kernel(const SweepParams
   const int never = H >> 31;
   auto load_row = [&](int t, int dep) {
     const int o = reflect1(t, H) * W + su + dep;
-    if (AUTOMASK && !FIRST) idn = rb[min(max(t - 1, 0), H - 1) * W + su + dep].w;
+    if (AUTOMASK && !FIRST) idn = rb[rec_ofs(min(max(t - 1, 0), H - 1), su, Wh) + dep].w;
     yn[0] = ldimg<real>(y0p, o); yn[1] = ldimg<real>(y1p, o); yn[2] = ldimg<real>(y2p, o);
 #pragma unroll
     for (int jj = 0; jj < CT; ++jj) {
@@ -213,15 +214,17 @@ __global__ void __launch_bounds__(32 * kPrepWarps) prep_kernel(const SweepParams
           // candidate order [.., id_j, ..]: the first minimum wins (reference :269-297, torch.min)
           if ((first && jj == 0) || val < idv) { idv = val; idk = (real)(2 * (j0 + jj) + 1); changed = true; }
         }
-        if (!first && changed && emit) { rb[op].w = idv; rc[op].w = idk; }
+        const int orc = rec_ofs(p, u, Wh);
+        if (!first && changed && emit) { rb[orc].w = idv; rc[orc].w = idk; }
       }
       if (emit) {
 #pragma unroll
         for (int jj = 0; jj < CT; ++jj) st4(cpk[jj] + p * Wp + u, xpA[jj].lo(), xpA[jj].hi(), xpB[jj], real(0));
         if (first) {
-          st4(ra + op, ypA.lo(), ypA.hi(), ypB, maskp ? ldmask<real>(maskp, op) : real(1));
-          st4(rb + op, myA.lo(), myA.hi(), myB, idv);
-          st4(rc + op, qyA.lo(), qyA.hi(), qyB, idk);
+          const int orc = rec_ofs(p, u, Wh);
+          st4(ra + orc, ypA.lo(), ypA.hi(), ypB, maskp ? ldmask<real>(maskp, op) : real(1));
+          st4(rb + orc, myA.lo(), myA.hi(), myB, idv);
+          st4(rc + orc, qyA.lo(), qyA.hi(), qyB, idk);
         }
         if (smooth) {
           const pr ex = ypA - ycpA, ey = ypA - yA;
@@ -389,9 +392,10 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
 
   const ScaleDesc& SD = P.sc[s];
   const vec4* ctxp = (const vec4*)S.ctxp[j] + (size_t)b * S.Hp * S.Wp;
-  const vec4* ra = (const vec4*)S.ra + (size_t)b * plane;
-  const vec4* rb = (const vec4*)S.rb + (size_t)b * plane;
-  const vec4* rcp = (const vec4*)S.rc + (size_t)b * plane;
+  const int Wh = S.Wh, rplane = H * 2 * Wh * 3;
+  const vec4* ra = (const vec4*)S.ra + (size_t)b * rplane;
+  const vec4* rb = (const vec4*)S.rb + (size_t)b * rplane;
+  const vec4* rcp = (const vec4*)S.rc + (size_t)b * rplane;
   asm volatile("" : "+l"(ctxp), "+l"(ra), "+l"(rb), "+l"(rcp));   // opaque: one IMAD.WIDE per load off a 32-bit offset
   const bool ups = VAR == 1 || (VAR == 2 && (SD.Hd != H || SD.Wd != W));   // inverse depths nearest-upsampled on load
   const real* invd = (const real*)SD.invd + (size_t)b * SD.Hd * SD.Wd;
@@ -563,8 +567,8 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
     load_pair(rayp + (reflect1(r0 - 1, H) * W + su) * 2, rxn, ryn);
   }
   {
-    ran = ld4(ra + reflect1(r0 - 2, H) * W + su);
-    const int orec = min(max(r0 - 3, 0), H - 1) * W + su;
+    ran = ld4(ra + rec_ofs(reflect1(r0 - 2, H), su, Wh));
+    const int orec = rec_ofs(min(max(r0 - 3, 0), H - 1), su, Wh);
     rbn = ld4(rb + orec);
     rcn = ld4(rcp + orec);
   }
@@ -604,8 +608,8 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
     // ---------------- prefetch of the next steps' operands, gather of row t + 1 ----------------------------
     {
       dpre = __ldg(invd + dofs(t + 2));
-      ran = ld4(ra + reflect1(t + 1, H) * W + su);
-      const int orec = min(max(p + 1, 0), H - 1) * W + su;
+      ran = ld4(ra + rec_ofs(reflect1(t + 1, H), su, Wh));
+      const int orec = rec_ofs(min(max(p + 1, 0), H - 1), su, Wh);
       rbn = ld4(rb + orec);
       rcn = ld4(rcp + orec);
       if (j == 0 && smooth) load_pair(wxy + (min(max(q + 1, 0), H - 1) * W + su) * 2, wxn, wyn);
@@ -1039,6 +1043,7 @@ static void make_plan(const psfm_loss_cfg* cfg, const psfm_loss_io* io, SweepPla
       used[k] = true;
     }
     S.Hp = S.H + kPadLo + kPadHi; S.Wp = S.W + kPadLo + kPadHi;
+    S.Wh = (S.W + 1) / 2;
     S.nstrips = cdiv(S.W, kInner);
     const int forced = env_int("PSFM_SWEEP_CHUNK", 0);
     S.chunk_h = forced > 0 ? (forced < S.H ? forced : S.H)
@@ -1066,7 +1071,7 @@ static void make_plan(const psfm_loss_cfg* cfg, const psfm_loss_io* io, SweepPla
     const int minc = Hs < kMinChunk ? Hs : kMinChunk;
     const size_t worst = (size_t)cdiv(Ws, kInner) * cdiv(Hs, minc);
     const size_t pworst = (size_t)cdiv(Ws, kPrepInner) * cdiv(Hs, minc);
-    pl.off_rec[s] = off;   off = al(off + px * 12 * rs);               // three real4 planes
+    pl.off_rec[s] = off;   off = al(off + (size_t)cfg->B * Hs * 2 * ((Ws + 1) / 2) * 12 * rs);   // three real4 planes
     pl.off_ctxp[s] = off;  off = al(off + (size_t)cfg->C * cfg->B * (Hs + kPadLo + kPadHi) * (Ws + kPadLo + kPadHi) * 4 * rs);
     pl.off_wxy[s] = off;   off = al(off + px * 2 * rs);
     pl.off_ray[s] = off;   if (cfg->camera_model == PSFM_CAM_FISHEYE) off = al(off + px * 2 * rs);
@@ -1148,10 +1153,10 @@ static cudaError_t run_sweep(const psfm_loss_cfg* cfg, const psfm_loss_io* io, v
     SP.set = pl.sets[i];
     const int s0 = SP.set.scale[0];
     {
-      const size_t px = (size_t)cfg->B * SP.set.H * SP.set.W * 4 * sizeof(real);
+      const size_t px = (size_t)cfg->B * SP.set.H * 2 * SP.set.Wh * 4 * sizeof(real);
       SP.set.ra = w + pl.off_rec[s0];
-      SP.set.rb = w + pl.off_rec[s0] + px;
-      SP.set.rc = w + pl.off_rec[s0] + 2 * px;
+      SP.set.rb = w + pl.off_rec[s0] + 4 * sizeof(real);
+      SP.set.rc = w + pl.off_rec[s0] + 8 * sizeof(real);
       const size_t cpx = (size_t)cfg->B * SP.set.Hp * SP.set.Wp * 4 * sizeof(real);
       for (int j = 0; j < PSFM_MAX_CTX; ++j) SP.set.ctxp[j] = j < cfg->C ? w + pl.off_ctxp[s0] + j * cpx : nullptr;
     }

@@ -37,6 +37,30 @@ __device__ __forceinline__ uint32_t decision_word(int x0, int y0) {
   return (uint32_t)min(max(x0 + 8, 0), 4095) | ((uint32_t)min(max(y0 + 8, 0), 4095) << 12);
 }
 
+// ---- staging of the pixel records: 1-D bulk copies (TMA) into shared memory, completion on an mbarrier ----------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t a, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(a), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t a, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(a), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t mbar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
+               "r"(bytes), "r"(mbar)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t a, uint32_t parity) {
+  uint32_t ok;
+  do {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok)
+                 : "r"(a), "r"(parity)
+                 : "memory");
+  } while (!ok);
+}
+constexpr int kRecStages = 4;        // record rows staged in shared memory: t - 1, t, and t + 1, t + 2 in flight
+
 template <typename real, int PAD, int VAR, int CT, bool DBG>
 __global__ void __launch_bounds__(32 * CT, sizeof(real) == 4 ? 8 / CT : 1) sweep2_kernel(const SweepParams SP) {
   typedef Real4<real> vec4;
@@ -63,20 +87,32 @@ __global__ void __launch_bounds__(32 * CT, sizeof(real) == 4 ? 8 / CT : 1) sweep
   vec4* ring = (vec4*)smem_raw + (size_t)j * 4 * kSlotVec * 32 + lane;      // [4 slots][kSlotVec][32]
   pr* photo_s = (pr*)((vec4*)smem_raw + (size_t)C * 4 * kSlotVec * 32);      // [2][C][32]
   pr* dpart_s = photo_s + 2 * C * 32;                                        // [2][C][32]
+  vec4* rec_s = (vec4*)(dpart_s + 2 * C * 32);                               // [kRecStages][2 halves][32][3 parts]
+  const uint32_t mbar0 = smem_u32(rec_s + kRecStages * 192);                 // kRecStages mbarriers
 
   const ScaleDesc& SD = P.sc[s];
   const vec4* ctxp = (const vec4*)S.ctxp[j] + (size_t)b * S.Hp * S.Wp;
-  const vec4* ra = (const vec4*)S.ra + (size_t)b * plane;
-  const vec4* rb = (const vec4*)S.rb + (size_t)b * plane;
-  const vec4* rcp = (const vec4*)S.rc + (size_t)b * plane;
-  asm volatile("" : "+l"(ctxp), "+l"(ra), "+l"(rb), "+l"(rcp));   // opaque: one IMAD.WIDE per load off a 32-bit offset
+  // pixel records (sweep_common.cuh), [B][H][2][Wh][3]: the strip's segment of a row -- 32 even and 32 odd columns,
+  // clipped to the image -- is staged in shared memory by two bulk copies
+  const int Wh = S.Wh;
+  const vec4* ra = (const vec4*)S.ra + ((size_t)b * H * 2 * Wh + max(strip * (kInner2 / 2) - 1, 0)) * 3;   // + the segment start
+  asm volatile("" : "+l"(ra));
+  const int h0 = max(strip * (kInner2 / 2) - 1, 0);                // first half-row index of the segment
+  const int ne = min(strip * (kInner2 / 2) + 31, (W + 1) / 2) - h0, no = min(strip * (kInner2 / 2) + 31, W / 2) - h0;
+  const int pos0 = ((su0 & 1) * 32 + min(max((su0 >> 1) - h0, 0), ((su0 & 1) ? no : ne) - 1)) * 3;
+  const int pos1 = ((su1 & 1) * 32 + min(max((su1 >> 1) - h0, 0), ((su1 & 1) ? no : ne) - 1)) * 3;
+  asm volatile("" : "+l"(ctxp));   // opaque: one IMAD.WIDE per load off a 32-bit offset
   constexpr bool ups = VAR == 1;                                   // inverse depths nearest-upsampled on load
   const real* invd = (const real*)SD.invd + (size_t)b * SD.Hd * SD.Wd;
   const int Wd = SD.Wd;
   const int sud0 = nearest_src(su0, SD.cs, SD.Wd, ups), sud1 = nearest_src(su1, SD.cs, SD.Wd, ups);
-  auto drow = [&](int row) { return nearest_src(reflect1(row, H), SD.rs, SD.Hd, ups) * Wd; };
-  auto load_d = [&](int row) { const int o = drow(row); return pr(__ldg(invd + o + sud0), __ldg(invd + o + sud1)); };
+  // `edge`: the row may lie outside the image (reflected / clamped); interior steps skip that arithmetic
+  auto load_d = [&](int row, bool edge, int dep) {
+    const int o = nearest_src(edge ? reflect1(row, H) : row, SD.rs, SD.Hd, ups) * Wd + dep;
+    return pr(__ldg(invd + (o + sud0)), __ldg(invd + (o + sud1)));
+  };
   const real* wxy = (const real*)S.wxy + (size_t)b * plane * 2;
+  asm volatile("" : "+l"(invd), "+l"(wxy));
   const int Wp = S.Wp;
   const bool smooth = P.smooth_w > 0.0;
 
@@ -142,25 +178,42 @@ __global__ void __launch_bounds__(32 * CT, sizeof(real) == 4 ? 8 / CT : 1) sweep
 #pragma unroll
     for (int k = 0; k < 4 * kSlotVec; ++k) ring[k * 32] = z;
   }
-  pr S0a[3], Sva[3], S1a[3];
+  pr S0a[3];                                                       // per pixel: the epilogue weighs them by the column
+  real Sva[3], S1a[3];
 #pragma unroll
-  for (int i = 0; i < 3; ++i) { S0a[i] = pr(real(0)); Sva[i] = pr(real(0)); S1a[i] = pr(real(0)); }
+  for (int i = 0; i < 3; ++i) { S0a[i] = pr(real(0)); Sva[i] = real(0); S1a[i] = real(0); }
   real loss_acc = real(0);
   pr w_cur(real(0)), w_old(real(0)), ls_p(real(0));
-  pr d0(real(0)), d1(real(0)), d2(real(0)), d3(real(0));        // raw inverse depths of rows t, t-1, t-2, t-3
   pr wy_prev(real(0)), dsum_prev(real(0));
   int prev_q = -1;
   real* d_out = (real*)SD.d_full + (size_t)b * plane;
+  asm volatile("" : "+l"(d_out));
 
   // ---- gather pipeline: geometry of `row`, 8 tap loads go in flight; consumed later in the same step -------
   vec4 tap[8];
   pr twx(real(0)), twy(real(0));
-  auto start_row = [&](int row, pr draw) {
-    const real fv = (real)reflect1(row, H);
+  auto start_row = [&](int row, bool edge, pr draw, int dep) {
+    const real fv = (real)((edge ? reflect1(row, H) : row) + dep);
     const Geo2<real> g = geometry(fv, draw);
-    real wx0, wy0, wx1, wy1, mx, my;
-    sample4_issue<real, vec4, PAD>(ctxp, H, W, Wp, kPadLo, g.ix.lo(), g.iy.lo(), wx0, wy0, mx, my, tap);
-    sample4_issue<real, vec4, PAD>(ctxp, H, W, Wp, kPadLo, g.ix.hi(), g.iy.hi(), wx1, wy1, mx, my, tap + 4);
+    // tap offset in the packed context image and the bilinear weights (sweep_device.cuh: sample4_issue)
+    auto tap_ofs = [&](real ix, real iy, real& wx, real& wy) {
+      if (PAD == PSFM_PAD_BORDER) {
+        ix = !(ix > real(0)) ? real(0) : rmin(ix, real(W - 1));
+        iy = !(iy > real(0)) ? real(0) : rmin(iy, real(H - 1));
+      } else {       // fully outside beyond [-1, size]: all four taps land in the zero border
+        ix = rmin(rmax(ix, real(-2)), real(W + 1));
+        iy = rmin(rmax(iy, real(-2)), real(H + 1));
+      }
+      const real fx = rfloor(ix), fy = rfloor(iy);
+      wx = ix - fx; wy = iy - fy;
+      return ((int)fy + kPadLo) * Wp + ((int)fx + kPadLo);
+    };
+    real wx0, wy0, wx1, wy1;
+    const int o0 = tap_ofs(g.ix.lo(), g.iy.lo(), wx0, wy0), o1 = tap_ofs(g.ix.hi(), g.iy.hi(), wx1, wy1);
+    tap[0] = ld4(ctxp + o0); tap[1] = ld4(ctxp + o0 + 1); tap[2] = ld4(ctxp + o0 + Wp); tap[3] = ld4(ctxp + o0 + Wp + 1);
+    tap[4] = ld4(ctxp + o1); tap[5] = ld4(ctxp + o1 + 1); tap[6] = ld4(ctxp + o1 + Wp); tap[7] = ld4(ctxp + o1 + Wp + 1);
+    // the next row's bottom taps are (mostly) one image row further down: pull that row into L1 now
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(ctxp + o0 + 2 * Wp));
     twx = pr(wx0, wx1);
     twy = pr(wy0, wy1);
     if (DBG) {
@@ -211,78 +264,118 @@ __global__ void __launch_bounds__(32 * CT, sizeof(real) == 4 ? 8 / CT : 1) sweep
     rs[5 * 32] = vec4{gya[0].lo(), gya[0].hi(), gya[1].lo(), gya[1].hi()};
   };
 
-  // prefetched operands of the next steps: target pixel (+ mask) records, statistics records
-  vec4 ran0, ran1, rbn0, rbn1, rcn0, rcn1;
-  pr mcur(real(1));                                                // mask values of row t - 1
   pr wxn(real(0)), wyn(real(0));                                   // edge weights of row q + 1 (context 0 only)
-  auto load_w = [&](int row) {
-    const real* p = wxy + (min(max(row, 0), H - 1) * W) * 2;
+  auto load_w = [&](int row, bool edge, int dep) {
+    const int o = (edge ? min(max(row, 0), H - 1) : row) * W + dep;
     real a0, b0, a1, b1;
-    load_pair(p + su0 * 2, a0, b0);
-    load_pair(p + su1 * 2, a1, b1);
+    load_pair(wxy + (o + su0) * 2, a0, b0);
+    load_pair(wxy + (o + su1) * 2, a1, b1);
     wxn = pr(a0, a1);
     wyn = pr(b0, b1);
   };
-  if (j == 0 && smooth) load_w(r0 - 4);
-  pr dnx = load_d(r0 - 2);
-  pr dpre = load_d(r0 - 1);
-  {
-    const int oy = reflect1(r0 - 2, H) * W;
-    ran0 = ld4(ra + oy + su0); ran1 = ld4(ra + oy + su1);
-    const int orec = min(max(r0 - 3, 0), H - 1) * W;
-    rbn0 = ld4(rb + orec + su0); rbn1 = ld4(rb + orec + su1);
-    rcn0 = ld4(rcp + orec + su0); rcn1 = ld4(rcp + orec + su1);
+  const int t0 = r0 - 2;
+  // record row `row` -> stage (row - (t0 - 1)) & 3; issued by one thread, two steps ahead of its use
+  const uint32_t rec_s32 = smem_u32(rec_s);
+  auto stage_row = [&](int row, bool mine) {
+    if (mine) {
+      const int k = row - (t0 - 1), st = k & (kRecStages - 1);
+      const uint32_t mb = mbar0 + st * 8;
+      const vec4* src = ra + (reflect1(row, H) * 2 * Wh) * 3;
+      const uint32_t dst = rec_s32 + st * (192 * (int)sizeof(vec4));
+      mbar_expect_tx(mb, (uint32_t)(3 * (ne + no) * sizeof(vec4)));
+      bulk_g2s(dst, src, (uint32_t)(3 * ne * sizeof(vec4)), mb);
+      bulk_g2s(dst + 96 * (int)sizeof(vec4), src + Wh * 3, (uint32_t)(3 * no * sizeof(vec4)), mb);
+    }
+  };
+  auto wait_row = [&](int row) {
+    const int k = row - (t0 - 1);
+    mbar_wait(mbar0 + (k & (kRecStages - 1)) * 8, (k / kRecStages) & 1);
+    return (const vec4*)(rec_s + (k & (kRecStages - 1)) * 192);
+  };
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int st = 0; st < kRecStages; ++st) mbar_init(mbar0 + st * 8, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  start_row(r0 - 2, dnx);
-  finish_row(r0 - 2);
+  __syncthreads();
+  stage_row(t0 - 1, threadIdx.x == 0);
+  stage_row(t0, threadIdx.x == 0);
+  stage_row(t0 + 1, threadIdx.x == 0);
+  if (j == 0 && smooth) load_w(t0 - 2, true, 0);
+  pr dnx = load_d(t0, true, 0);
+  pr dpre = load_d(t0 + 1, true, 0);
+  start_row(t0, true, dnx, 0);
+  finish_row(t0);
+  const vec4* rec_prev = wait_row(t0 - 1);                         // staged records of row t - 1
+  const int never = H >> 31;                                       // 0, unknown to the compiler
 
   auto finalize_row = [&](int par) {      // context 0 adds the other contexts' parts and stores the row
     if (j == 0 && prev_q >= 0) {
       pr tot = dsum_prev;
 #pragma unroll
       for (int jj = 1; jj < C; ++jj) tot = tot + dpart_s[(par * C + jj) * 32 + lane];
-      if (ok0) d_out[prev_q * W + u0] = tot.lo();
-      if (ok1) d_out[prev_q * W + u1] = tot.hi();
+      if (ok0) d_out[prev_q * W + su0] = tot.lo();
+      if (ok1) d_out[prev_q * W + su1] = tot.hi();
     }
     prev_q = -1;
   };
 
-  for (int t = r0 - 2; t <= r1 + 1; ++t) {
+  // RE: the step touches rows outside [0, H) (reflection, clamps, doubled border rows); steps 3 <= t <= H - 3 do not
+  auto step = [&](const int t, auto re) __attribute__((always_inline)) {
+    constexpr bool RE = decltype(re)::value;
     const int p = t - 1, q = t - 2;
     const int par = t & 1;
-    const bool p_row = (p >= 0) && (p < H);
+    const bool p_row = !RE || ((p >= 0) && (p < H));
     const bool p_real0 = p_row && real0, p_real1 = p_row && real1;
-    // ---------------- operands prefetched one step ago ---------------------------------------------------
-    const c3 y(pr(ran0.x, ran0.y), pr(ran1.x, ran1.y), pr(ran0.z, ran1.z));
-    const c3 my(pr(rbn0.x, rbn0.y), pr(rbn1.x, rbn1.y), pr(rbn0.z, rbn1.z));
-    const c3 qy(pr(rcn0.x, rcn0.y), pr(rcn1.x, rcn1.y), pr(rcn0.z, rcn1.z));
-    const pr idmin(rbn0.w, rbn1.w), idcand(rcn0.w, rcn1.w);
-    const pr m(p_real0 ? mcur.lo() : real(0), p_real1 ? mcur.hi() : real(0));   // 1 without a mask
-    mcur = pr(ran0.w, ran1.w);
-    d3 = d2; d2 = d1; d1 = d0;
-    d0 = dnx;
+    // ---------------- staged records: target pixel of row t, statistics / mask / identity candidate of row p ------
+    if (C == 1) __syncwarp();
+    // its stage held row t - 2, last read before the barrier of step t - 1; the warps take turns at issuing
+    if (t + 2 <= r1 + 1) stage_row(t + 2, lane == 0 && j == (C == 1 ? 0 : (t & (C - 1))));
+    const vec4* rec_cur = wait_row(t);
+    c3 y, my, qy;
+    pr idmin, idcand, m;
+    {
+      const vec4 ya = rec_cur[pos0], yb = rec_cur[pos1];
+      y = c3(pr(ya.x, ya.y), pr(yb.x, yb.y), pr(ya.z, yb.z));
+      const vec4 ma = rec_prev[pos0], mb = rec_prev[pos1];          // mask of row p in the 4th component
+      m = pr(p_real0 ? ma.w : real(0), p_real1 ? mb.w : real(0));   // 1 without a mask
+      const vec4 ba = rec_prev[pos0 + 1], bb = rec_prev[pos1 + 1];
+      my = c3(pr(ba.x, ba.y), pr(bb.x, bb.y), pr(ba.z, bb.z));
+      idmin = pr(ba.w, bb.w);
+      const vec4 ca = rec_prev[pos0 + 2], cb2 = rec_prev[pos1 + 2];
+      qy = c3(pr(ca.x, ca.y), pr(cb2.x, cb2.y), pr(ca.z, cb2.z));
+      idcand = pr(ca.w, cb2.w);
+    }
+    rec_prev = rec_cur;
     dnx = dpre;
     const pr wxq = wxn, wyq = wyn;
+    // All loads of a step share scoreboards, and a wait on one waits for everything in flight on it: every value of
+    // the previous batch is therefore consumed BEFORE the next batch is issued -- `dep` (always 0, unknown to the
+    // compiler) enters every new address (loss_sweep.cu, prep kernel: without it the one-row prefetch is void).
+    const int dep = (value_bits(dnx.lo()) | value_bits(dnx.hi()) | value_bits(wxq.lo()) | value_bits(wxq.hi())) & never;
     // ---------------- prefetch of the next steps' operands, gather of row t + 1 ---------------------------
-    dpre = load_d(t + 2);
-    {
-      const int oy = reflect1(t + 1, H) * W;
-      ran0 = ld4(ra + oy + su0); ran1 = ld4(ra + oy + su1);
-      const int orec = min(max(p + 1, 0), H - 1) * W;
-      rbn0 = ld4(rb + orec + su0); rbn1 = ld4(rb + orec + su1);
-      rcn0 = ld4(rcp + orec + su0); rcn1 = ld4(rcp + orec + su1);
-    }
-    if (j == 0 && smooth) load_w(q + 1);
-    start_row(t + 1, dnx);
+    dpre = load_d(t + 2, RE, dep);
+    if (j == 0 && smooth) load_w(q + 1, RE, dep);
+    // inverse depths of the adjoint's row (and, for the smoothness term of context 0, of the rows around it)
+    const pr d2 = load_d(q, RE, dep);
+    pr d1(real(0)), d3(real(0));
+    if (j == 0 && smooth) { d1 = load_d(q + 1, RE, dep); d3 = load_d(q - 1, RE, dep); }
+    start_row(t + 1, RE, dnx, dep);
     // ---------------- horizontal window sums of row t, L1 term of row t -----------------------------------
     const c3 x = xcar;
-    c3 hn[3];
+    c3 V[3];                                                       // 3 x 3 window sums at row p
     {
-      const c3 z = x * y;
-      const Nb3<real> nx = neighbours(x), nz = neighbours(z);
-      hn[0] = hsum(x, nx);
-      hn[1] = hsumsq(x, nx);
-      hn[2] = hsum(z, nz);
+      auto hsums = [&](c3* dst) {
+        const c3 z = x * y;
+        const Nb3<real> nx = neighbours(x), nz = neighbours(z);
+        dst[0] = hsum(x, nx);
+        dst[1] = hsumsq(x, nx);
+        dst[2] = hsum(z, nz);
+      };
+      c3 hn[3];
+      hsums(hn);
+#pragma unroll
+      for (int k = 0; k < 3; ++k) { V[k] = Aw[k] + hn[k]; Aw[k] = hp[k] + hn[k]; hp[k] = hn[k]; }
       vec4* rs = ring + (t & 3) * kSlotVec * 32;
       rs[2 * 32] = vec4{y.a0.lo(), y.a0.hi(), y.a1.lo(), y.a1.hi()};
       ((pr*)(rs + 1 * 32))[1] = y.b;
@@ -294,9 +387,18 @@ __global__ void __launch_bounds__(32 * CT, sizeof(real) == 4 ? 8 / CT : 1) sweep
     c3 F[3];
     {
       Ssim3<real> st;
-      const c3 dist = ssim_fwd3<real>(Aw[0] + hn[0], Aw[1] + hn[1], Aw[2] + hn[2], my, qy, K.C1, K.C2, st);
+      const c3 dist = ssim_fwd3<real>(V[0], V[1], V[2], my, qy, K.C1, K.C2, st);
+      // gradient coefficients for a unit selection weight, formed before the contexts meet: 3 values per channel
+      // cross the barrier instead of the 8 SSIM factors
+      {
+        const pr m9(real(-1) / real(9));
+        pr fa0[3], fa1[3], fb[3];
+        ssim_grad_w<real, pr>(st.a0, my.a0, m9, fa0);
+        ssim_grad_w<real, pr>(st.a1, my.a1, m9, fa1);
+        ssim_grad_w<real, pr>(st.b, my.b, m9, fb);
 #pragma unroll
-      for (int k = 0; k < 3; ++k) { Aw[k] = hp[k] + hn[k]; hp[k] = hn[k]; }
+        for (int k = 0; k < 3; ++k) F[k] = c3(fa0[k], fa1[k], fb[k]);
+      }
       const pr ds = chsum(c3(pclamp01(dist.a0), pclamp01(dist.a1), pclamp01(dist.b)));
       const pr photo = vfma(pr(K.ssim_w3), ds, pr(K.k1) * ls_p);
       ls_p = ls_t;
@@ -339,38 +441,39 @@ __global__ void __launch_bounds__(32 * CT, sizeof(real) == 4 ? 8 / CT : 1) sweep
           }
         }
       }
-      const pr wf9 = w_cur * pr(K.ssim_w3 * (real(-1) / real(9)));
-      pr fa0[3], fa1[3], fb[3];
-      ssim_grad_w<real, pr>(st.a0, my.a0, pr(wf9.lo()), fa0);
-      ssim_grad_w<real, pr>(st.a1, my.a1, pr(wf9.hi()), fa1);
-      ssim_grad_w<real, pr>(st.b, my.b, wf9, fb);
+      const c3 wf = bc(w_cur * pr(K.ssim_w3));
 #pragma unroll
-      for (int k = 0; k < 3; ++k) F[k] = c3(fa0[k], fa1[k], fb[k]);
+      for (int k = 0; k < 3; ++k) F[k] = F[k] * wf;
     }
     finalize_row(par ^ 1);
     // ---------------- adjoint at row q ----------------------------------------------------------------
     {
       c3 sq[3];
-      const real mv2 = (q == H - 2) ? real(2) : real(1), mv0n = (q == 0) ? real(2) : real(1);
+      const real mv2 = (RE && q == H - 2) ? real(2) : real(1), mv0n = (RE && q == 0) ? real(2) : real(1);
       const c3 mv2c(mv2), mv0c(mv0n);
+      // 3-tap horizontal sums of the coefficient planes (the reflected border columns count twice)
+      auto hfsums = [&](c3* dst) {
 #pragma unroll
-      for (int k = 0; k < 3; ++k) {
-        // 3-tap horizontal sum of the coefficient plane; the reflected border columns count twice
-        const Nb3<real> nf = neighbours(F[k]);
-        c3 hF = hsum(F[k], nf);
-        if (edge_strip) {
-          const real e0 = (u1 == 1) ? real(1) : real(0);            // column 0 once more into column 1
-          const real e1 = (u0 == W - 2) ? real(1) : real(0);        // column W-1 (own pixel 1) once more into pixel 0
-          const real e2 = (u1 == W - 2) ? real(1) : real(0);        // column W-1 (right neighbour) once more into pixel 1
-          hF.a1 = vfma(pr(e0), F[k].a0, hF.a1);
-          hF.a0 = vfma(pr(e1), F[k].a1, hF.a0);
-          hF.a1 = vfma(pr(e2), nf.ra, hF.a1);
-          hF.b = hF.b + pr(e1 * F[k].b.hi(), e0 * F[k].b.lo() + e2 * nf.lrb.hi());
+        for (int k = 0; k < 3; ++k) {
+          const Nb3<real> nf = neighbours(F[k]);
+          dst[k] = hsum(F[k], nf);
+          if (edge_strip) {
+            const real e0 = (u1 == 1) ? real(1) : real(0);            // column 0 once more into column 1
+            const real e1 = (u0 == W - 2) ? real(1) : real(0);        // column W-1 (own pixel 1) once more into pixel 0
+            const real e2 = (u1 == W - 2) ? real(1) : real(0);        // column W-1 (right neighbour) once more into pixel 1
+            dst[k].a1 = vfma(pr(e0), F[k].a0, dst[k].a1);
+            dst[k].a0 = vfma(pr(e1), F[k].a1, dst[k].a0);
+            dst[k].a1 = vfma(pr(e2), nf.ra, dst[k].a1);
+            dst[k].b = dst[k].b + pr(e1 * F[k].b.hi(), e0 * F[k].b.lo() + e2 * nf.lrb.hi());
+          }
         }
-        // vertical: s(q) = mv0 hF(q-1) + hF(q) + mv2 hF(q+1); the reflected border rows count twice
-        sq[k] = vfma(mv2c, hF, AF[k]);
-        AF[k] = vfma(mv0c, hFp[k], hF);
-        hFp[k] = hF;
+      };
+      // vertical: s(q) = mv0 hF(q-1) + hF(q) + mv2 hF(q+1); the reflected border rows count twice
+      {
+        c3 hF[3];
+        hfsums(hF);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { sq[k] = vfma(mv2c, hF[k], AF[k]); AF[k] = vfma(mv0c, hFp[k], hF[k]); hFp[k] = hF[k]; }
       }
       const bool q_row = (q >= r0) && (q < r1);
       const bool q_ok0 = q_row && ok0, q_ok1 = q_row && ok1;
@@ -405,10 +508,11 @@ __global__ void __launch_bounds__(32 * CT, sizeof(real) == 4 ? 8 / CT : 1) sweep
       const pr dph = mD2 * dD;
       const pr dphoto((q_ok0 && d2.lo() >= real(1e-6)) ? -dph.lo() : real(0), (q_ok1 && d2.hi() >= real(1e-6)) ? -dph.hi() : real(0));
       {
-        const pr e0 = dp0 * g.D, e1 = dp1 * g.D, e2 = dp2 * g.D, fqp(fq);
+        const pr e0 = dp0 * g.D, e1 = dp1 * g.D, e2 = dp2 * g.D;
         S0a[0] = S0a[0] + e0; S0a[1] = S0a[1] + e1; S0a[2] = S0a[2] + e2;
-        Sva[0] = vfma(e0, fqp, Sva[0]); Sva[1] = vfma(e1, fqp, Sva[1]); Sva[2] = vfma(e2, fqp, Sva[2]);
-        S1a[0] = S1a[0] + dp0; S1a[1] = S1a[1] + dp1; S1a[2] = S1a[2] + dp2;
+        Sva[0] = vfma(e0.lo() + e0.hi(), fq, Sva[0]); Sva[1] = vfma(e1.lo() + e1.hi(), fq, Sva[1]);
+        Sva[2] = vfma(e2.lo() + e2.hi(), fq, Sva[2]);
+        S1a[0] += dp0.lo() + dp0.hi(); S1a[1] += dp1.lo() + dp1.hi(); S1a[2] += dp2.lo() + dp2.hi();
       }
       if (j == 0) {
         pr gs(real(0));
@@ -421,11 +525,11 @@ __global__ void __launch_bounds__(32 * CT, sizeof(real) == 4 ? 8 / CT : 1) sweep
           if (u0 >= 1) qq0 -= signed_by(cx * wxl0, dl0 - d2.lo());
           if (u1 + 1 < W) qq1 += signed_by(cx * wxq.hi(), d2.hi() - dr1);
           if (u1 >= 1) qq1 -= signed_by(cx * wxq.lo(), d2.lo() - d2.hi());
-          if (q + 1 < H) {
+          if (!RE || q + 1 < H) {
             qq0 += signed_by(cy * wyq.lo(), d2.lo() - d1.lo());
             qq1 += signed_by(cy * wyq.hi(), d2.hi() - d1.hi());
           }
-          if (q >= 1) {
+          if (!RE || q >= 1) {
             qq0 -= signed_by(cy * wy_prev.lo(), d3.lo() - d2.lo());
             qq1 -= signed_by(cy * wy_prev.hi(), d3.hi() - d2.hi());
           }
@@ -436,14 +540,19 @@ __global__ void __launch_bounds__(32 * CT, sizeof(real) == 4 ? 8 / CT : 1) sweep
           if (C > 1) { dsum_prev = dphoto + gs; prev_q = q; }
           else {
             const pr tot = dphoto + gs;
-            if (ok0) d_out[q * W + u0] = tot.lo();
-            if (ok1) d_out[q * W + u1] = tot.hi();
+            if (ok0) d_out[q * W + su0] = tot.lo();
+            if (ok1) d_out[q * W + su1] = tot.hi();
           }
         }
       } else {
         dpart_s[(par * C + j) * 32 + lane] = dphoto;
       }
     }
+  };
+#pragma unroll 1
+  for (int t = t0; t <= r1 + 1; ++t) {
+    if (t >= 3 && t <= H - 3) step(t, IntC<0>());
+    else step(t, IntC<1>());
   }
   if (C > 1) {
     __syncthreads();
@@ -458,10 +567,10 @@ __global__ void __launch_bounds__(32 * CT, sizeof(real) == 4 ? 8 / CT : 1) sweep
     real G[12];
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
-      const real eu = fu0 * S0a[i].lo() + fu1 * S0a[i].hi(), ev = Sva[i].lo() + Sva[i].hi(), e1 = S0a[i].lo() + S0a[i].hi();
+      const real eu = fu0 * S0a[i].lo() + fu1 * S0a[i].hi(), ev = Sva[i], e1 = S0a[i].lo() + S0a[i].hi();
 #pragma unroll
       for (int k = 0; k < 3; ++k) G[i * 4 + k] = cam.ki[k * 3] * eu + cam.ki[k * 3 + 1] * ev + cam.ki[k * 3 + 2] * e1;
-      G[i * 4 + 3] = S1a[i].lo() + S1a[i].hi();
+      G[i * 4 + 3] = S1a[i];
     }
 #pragma unroll
     for (int e = 0; e < 12; ++e) G[e] = warp_allsum<real>(G[e]);
@@ -490,7 +599,8 @@ bool sweep2_eligible(const psfm_loss_cfg* cfg) {
 template <typename real, int PAD, int VAR, int CT, bool DBG>
 static cudaError_t launch2(const SweepParams& SP, dim3 grid, cudaStream_t st) {
   auto kern = sweep2_kernel<real, PAD, VAR, CT, DBG>;
-  const size_t smem = (size_t)CT * 4 * kSlotVec * 32 * sizeof(Real4<real>) + (size_t)4 * CT * 32 * sizeof(P2<real>);
+  const size_t smem = (size_t)CT * 4 * kSlotVec * 32 * sizeof(Real4<real>) + (size_t)4 * CT * 32 * sizeof(P2<real>) +
+                      (size_t)kRecStages * 192 * sizeof(Real4<real>) + kRecStages * 8;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
@@ -512,6 +622,9 @@ template <typename real>
 cudaError_t launch_sweep2(const SweepParams& SP, bool upsampled, bool debug, cudaStream_t st) {
   const SweepSet& S = SP.set;
   const dim3 grid(S.nstrips2 * S.nchunks2, S.ns, SP.P.B);
+#ifdef PSFM_SWEEP2_DEV      // development: the headline instantiation only (seconds to compile)
+  return launch2<float, PSFM_PAD_ZEROS, 0, 2, false>(SP, grid, st);
+#else
   const bool border = SP.P.padding == PSFM_PAD_BORDER;
   if (debug) {
     if (upsampled) return cudaErrorNotSupported;
@@ -520,6 +633,7 @@ cudaError_t launch_sweep2(const SweepParams& SP, bool upsampled, bool debug, cud
   if (upsampled)
     return border ? launch2_c<real, PSFM_PAD_BORDER, 1, false>(SP, grid, st) : launch2_c<real, PSFM_PAD_ZEROS, 1, false>(SP, grid, st);
   return border ? launch2_c<real, PSFM_PAD_BORDER, 0, false>(SP, grid, st) : launch2_c<real, PSFM_PAD_ZEROS, 0, false>(SP, grid, st);
+#endif
 }
 
 template cudaError_t launch_sweep2<float>(const SweepParams&, bool, bool, cudaStream_t);

@@ -25,13 +25,21 @@ struct SweepSet {                    // scales of equal resolution sharing the s
   int nstrips2, nchunks2, chunk_h2;  // two-pixels-per-lane sweep kernel decomposition
   int pstrips, pchunks, pchunk_h;    // prep kernel decomposition
   int Hp, Wp;                        // padded size of the packed context images
-  void* ra;                          // real4 [B][H][W]: target pixel y x3, mask value
-  void* rb;                          // real4 [B][H][W]: mean(y) x3, min identity photometric value (automask)
-  void* rc;                          // real4 [B][H][W]: E[y^2]-mean(y)^2+C2 x3, candidate index of that min
+  int Wh;                            // (W + 1) / 2: pitch of a half row of the pixel records
+  // pixel records, real4 [B][H][2][Wh][3]: a row holds its even columns, then its odd columns, three 4-vectors per
+  // pixel (rec_ofs) -- the pixels of the lanes of the two-pixels-per-lane sweep sit in two contiguous runs, which two
+  // bulk copies stage in shared memory, and the 48-byte pitch keeps 16-byte shared loads free of bank conflicts.
+  // ra, rb = ra + 1, rc = ra + 2 (in 4-vectors) address the three parts with the same offset
+  void* ra;                          // target pixel y x3, mask value
+  void* rb;                          // mean(y) x3, min identity photometric value (automask)
+  void* rc;                          // E[y^2]-mean(y)^2+C2 x3, candidate index of that min
   void* wxy;                         // real [B][H][W][2]: exp(-mean|dx I|), exp(-mean|dy I|)
   void* ray;                         // real [B][H][W][2]: fisheye only, x and y of the pixel's viewing ray (z = 1)
   void* ctxp[PSFM_MAX_CTX];          // real4 [B][Hp][Wp]: context image (r, g, b, 0), zero border
 };
+
+// element offset of pixel (row, u) in a record plane of one image
+__device__ __forceinline__ int rec_ofs(int row, int u, int Wh) { return ((row * 2 + (u & 1)) * Wh + (u >> 1)) * 3; }
 
 template <int V> struct IntC { static constexpr int value = V; };
 
