@@ -51,6 +51,25 @@ def workload_name(k, cfg):
         k - 1, cfg['B'], cfg['W'], cfg['H'], cfg['C'], cfg['n'], cfg['img'], cfg['padding'])
 
 
+def config_dict(args, cfg, world):
+    """The `config` object of the JSON line: names the workload; identical for both arms (ours / --impl reference)."""
+    B = cfg['B']
+    real_b = 4
+    e = 1 if args.host_images == 'u8' else (2 if cfg['img'] == 'bf16' else 4)
+    P = cfg['H'] * cfg['W']
+    in_bytes = B * P * (3 * e * (1 + cfg['C']) + real_b * cfg['n'])
+    foot = in_bytes + B * P * (real_b + 1) * cfg['n']
+    R = max(2, -(-3 * (126 * 2 ** 20) // foot)) if not args.no_rotate else 1
+    return {'workload': workload_name(args.config, cfg) + (
+                ' [inverse depths given as the decoder pyramid, upsampled in-kernel]' if args.pyramid else '') + (
+                ' [fisheye (VADAS) cameras instead of pinhole K]' if args.camera == 'fisheye' else '') + (
+                ' [frames as image bytes, to_tensor (byte / 255) applied in-kernel]' if args.host_images == 'u8' else ''),
+            'global_batch': world * B,
+            'l2': 'rotating %d resident input sets (%.0f MB total footprint > 3x 126 MB L2)' % (R, R * foot / 2 ** 20),
+            'loss': dict(LOSS_HP, padding_mode=cfg['padding']),
+            'parallelism': 'dp%d (batch-sharded, one NCCL all-reduce of the loss per step)' % world}, R, foot
+
+
 def bytes_per_frame(cfg, part='all'):
     """sum_s P_s * (12 + 6 e (1 + C)); fwd share = 4 + 3e(1+C), bwd share = that + 4."""
     e = 2 if cfg['img'] == 'bf16' else 4
@@ -176,19 +195,54 @@ def cpu_oracle_rate(cfg, frames_per_step, min_seconds=10.0, max_iters=10, warmup
     return frames_per_step / med, len(times), torch.get_num_threads()
 
 
+def gpu_eager_rate(cfg, dev, iters=10, max_frames=8):
+    """frames/s of the reference's PyTorch statements (the oracle port, plain torch ops, autograd backward) on the
+    GPU, fp32 with TF32 off: the GPU baseline SURVEY.md 8(d) / BASELINE.md 4 ask for.  Bounded sample of the batch."""
+    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+    import photometric_oracle as O
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    Bs = min(cfg['B'], max_frames)
+    h = synth_batch(dict(cfg, B=Bs, pyramid=False, camera=None, host_images='native'), dev)
+    hp = dict(LOSS_HP, padding_mode=cfg['padding'])
+
+    def one():
+        invd = [d.clone().requires_grad_() for d in h['inv_depths']]
+        vecs = [v.clone().requires_grad_() for v in h['vecs']]
+        out = O.multiview_photometric_loss(h['image'].float(), [x.float() for x in h['context']], invd, h['K'], h['K'],
+                                           [O.pose_vec_to_mat(v) for v in vecs], **hp)
+        out['loss'].backward()
+
+    for _ in range(3):
+        one()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        one()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    return {'value': Bs / (ms * 1e-3), 'unit': 'frames/s', 'ms_per_step': ms, 'frames_per_step': Bs, 'iters': iters,
+            'what': 'oracle port of the reference classes, PyTorch eager on cuda:0, fp32 (TF32 off), fwd + backward'}
+
+
 def run_reference(args):
-    """--impl reference: the reference's CPU implementation of the path (oracle port; the reference
-    is pure Python, no oracle/_ref binary) on the host cores; rank 0 only."""
+    """--impl reference: the reference's CPU implementation of the path (oracle port; the reference is pure Python,
+    no oracle/_ref binary) on the host cores, on the SAME configuration, steps and warm-up as the repo arm: every
+    step is one forward + backward over the full B-frame batch of the config.  Rank 0 only.
+    The port runs about 8 % slower than the reference's own classes on the same inputs (same loss; measured in the
+    build container with `python oracle/gen_golden.py --time`): immaterial against the GPU ratio, stated for the record."""
     if int(os.environ.get('RANK', 0)) != 0:
         return
-    cfg = CONFIGS[args.config]
-    sample = 1                     # frames per CPU step: a bounded sample of the B-frame batch
+    cfg = dict(CONFIGS[args.config], pyramid=args.pyramid, camera=args.camera, host_images=args.host_images)
+    world = int(os.environ.get('WORLD_SIZE', 1))
     cores = os.cpu_count()
     torch.set_num_threads(cores)
     sys.path.insert(0, os.path.join(ROOT, 'oracle'))
     import photometric_oracle as O
-    c = dict(cfg, B=sample)
-    h = synth_batch(c, None)
+    B = cfg['B']
+    h = synth_batch(dict(cfg, pyramid=False, camera=None, host_images='native'), None)
     hp = dict(LOSS_HP, padding_mode=cfg['padding'])
 
     def one():
@@ -198,21 +252,23 @@ def run_reference(args):
                                            h['K'], [O.pose_vec_to_mat(v) for v in vecs], **hp)
         out['loss'].backward()
 
-    steps = min(args.steps, 40)    # bounded: each CPU step costs ~0.1-0.5 s per frame
-    for _ in range(min(args.warmup, 3)):
+    steps, warm = args.steps, max(args.warmup, 3)
+    for _ in range(warm):
         one()
     t0 = time.perf_counter()
     for _ in range(steps):
         one()
     dt = time.perf_counter() - t0
-    val = sample * steps / dt
+    val = B * steps / dt
+    conf, _, _ = config_dict(args, cfg, world)
     line = {'impl': 'reference', 'metric': METRIC, 'value': val, 'unit': 'frames/s', 'n_gpus': args.gpus,
-            'steps': steps, 'warmup': min(args.warmup, 3), 'ms_per_step': 1e3 * dt / steps,
+            'steps': steps, 'warmup': warm, 'ms_per_step': 1e3 * dt / steps,
             'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-            'config': {'workload': workload_name(args.config, cfg)},
+            'config': conf,
             'cpu_baseline': {'value': val, 'unit': 'frames/s', 'cores': torch.get_num_threads(), 'kind': 'port',
-                             'sample': '%d frame(s) of the %d-frame batch per step, %d steps, fp32, PyTorch CPU' % (
-                                 sample, cfg['B'], steps)},
+                             'sample': 'the full %d-frame batch of the config per step, %d steps after %d warm-up, fp32, '
+                                       'PyTorch CPU (port of the reference classes; ~8 %% slower than the classes '
+                                       'themselves)' % (B, steps, warm)},
             'e2e': {'value': val, 'unit': 'frames/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
     emit(line)
 
@@ -229,6 +285,18 @@ def bind_to_gpu_numa_node(index):
         words = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
         cpus = {w * 64 + b for w, m in enumerate(words) for b in range(64) if (m >> b) & 1}
         cpus &= os.sched_getaffinity(0)
+        world = int(os.environ.get('LOCAL_WORLD_SIZE', os.environ.get('WORLD_SIZE', 1)))
+        if cpus and world > 1:
+            # boxes whose GPUs all report the same node (SCALE_r01: 8 GPUs -> cores 0-31): give each rank its own
+            # slice of that set instead of stacking every rank's copy threads on the same cores
+            same = True
+            for k in range(world):
+                wk = pynvml.nvmlDeviceGetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(k), (ncpu + 63) // 64)
+                same = same and list(wk) == list(words)
+            if same and len(cpus) >= world:
+                order = sorted(cpus)
+                per = len(order) // world
+                cpus = set(order[index * per:(index + 1) * per])
         if cpus:
             os.sched_setaffinity(0, cpus)
             return len(cpus)
@@ -255,27 +323,33 @@ def run_ours(args):
     B = cfg['B']
     loss_fn = MultiViewPhotometricLoss(padding_mode=cfg['padding'], kernel_mode=args.mode,
                                        upsample_depth_maps=args.pyramid, **LOSS_HP)
-    real_b = 4
-    e = 1 if args.host_images == 'u8' else (2 if cfg['img'] == 'bf16' else 4)
-    P = cfg['H'] * cfg['W']
-    in_bytes = B * P * (3 * e * (1 + cfg['C']) + real_b * cfg['n'])          # inputs of one step
-    foot = in_bytes + B * P * (real_b + 1) * cfg['n']                        # + grads + arg-min maps
-    L2 = 126 * 2 ** 20
-    R = max(2, -(-3 * L2 // foot)) if not args.no_rotate else 1              # rotating input sets > 3x L2
+    conf, R, foot = config_dict(args, cfg, world)                             # R rotating input sets > 3x L2
 
     class Slot:
         """One resident input set (device) with its pinned host copy and, optionally, a CUDA graph."""
         def __init__(self, seed):
-            self.host = synth_batch(cfg, None, seed)
-            self.pin = {k: ([t.pin_memory() for t in v] if isinstance(v, list) else v.pin_memory())
-                        for k, v in self.host.items()}
-            d = {k: ([t.to(dev) for t in v] if isinstance(v, list) else v.to(dev)) for k, v in self.host.items()}
-            self.image, self.context, self.K = d['image'], d['context'], d['K']
-            self.invd = [x.requires_grad_() for x in d['inv_depths']]
+            """All inputs of a step live in ONE device buffer with ONE pinned host image of it: the end-to-end path
+            moves them with a single cudaMemcpyAsync per step (round 1 issued nine copies from nine pinned tensors)."""
+            host = synth_batch(cfg, None, seed)
             with torch.no_grad():
-                self.mats = [Pose.from_vec(v, 'euler').mat for v in d['vecs']]
-            self.mats = [m.requires_grad_() for m in self.mats]
-            self.mats_pin = [m.detach().cpu().pin_memory() for m in self.mats]
+                mats = [Pose.from_vec(v.to(dev), 'euler').mat.cpu() for v in host['vecs']]
+            items = ([('image', host['image'])] + [('context', c) for c in host['context']] +
+                     [('invd', d) for d in host['inv_depths']] + [('mats', m) for m in mats] + [('K', host['K'])])
+            offs, off = [], 0
+            for _, t in items:
+                offs.append(off)
+                off = (off + t.numel() * t.element_size() + 255) // 256 * 256
+            self.flat_pin = torch.empty(off, dtype=torch.uint8).pin_memory()
+            self.flat = torch.empty(off, dtype=torch.uint8, device=dev)
+            view = lambda buf, o, t: buf[o:o + t.numel() * t.element_size()].view(t.dtype).view(t.shape)
+            got = {}
+            for (name, t), o in zip(items, offs):
+                view(self.flat_pin, o, t).copy_(t)
+                got.setdefault(name, []).append(view(self.flat, o, t))
+            self.flat.copy_(self.flat_pin)
+            self.image, self.context, self.K = got['image'][0], got['context'], got['K'][0]
+            self.invd = [x.requires_grad_() for x in got['invd']]
+            self.mats = [m.requires_grad_() for m in got['mats']]
             self.graph, self.loss = None, None
 
         def step(self):
@@ -299,6 +373,9 @@ def run_ours(args):
                 t.grad = None
             with torch.cuda.graph(self.graph):
                 self.step()
+                if graph_allreduce[0]:      # the step's collective inside the captured graph: no per-step Python launches
+                    red[0:1].copy_(self.loss.detach())
+                    dist.all_reduce(red)
 
         def run(self):
             if self.graph is not None:
@@ -308,19 +385,20 @@ def run_ours(args):
             return self.loss
 
         def upload(self):
-            """H2D of this step's inputs from pinned host memory."""
-            n = 0
-            self.image.copy_(self.pin['image'], non_blocking=True); n += self.image.numel() * self.image.element_size()
-            for a, b in zip(self.context, self.pin['context']):
-                a.copy_(b, non_blocking=True); n += a.numel() * a.element_size()
-            with torch.no_grad():
-                for a, b in zip(self.invd, self.pin['inv_depths']):
-                    a.copy_(b, non_blocking=True); n += a.numel() * a.element_size()
-                for a, b in zip(self.mats, self.mats_pin):
-                    a.copy_(b, non_blocking=True); n += a.numel() * a.element_size()
-            self.K.copy_(self.pin['K'], non_blocking=True); n += self.K.numel() * self.K.element_size()
-            return n
+            """H2D of this step's inputs from pinned host memory: one copy."""
+            self.flat.copy_(self.flat_pin, non_blocking=True)
+            return self.flat.numel()
 
+    # the per-step collective: the loss triple, or -- secondary measurement, --grad-bucket-mfloats -- the loss in front
+    # of a parameter-gradient bucket of that many floats (SURVEY.md 8(e): depth + pose network gradients, 14-27 M)
+    nred = 3 + int(args.grad_bucket_mfloats * 1e6)
+    red = torch.zeros(nred, device=dev)
+    if world > 1:      # communicator set-up is not timed work: warm it up whatever --warmup says
+        for _ in range(20):
+            dist.all_reduce(red)
+        torch.cuda.synchronize()
+
+    graph_allreduce = [world > 1 and args.allreduce == 'graph' and not args.no_graph]
     slots = [Slot(1234 + 100 * rank + r) for r in range(R)]
     # launches of one eager step (my kernels only; counted by the library)
     torch.cuda.synchronize()
@@ -337,10 +415,9 @@ def run_ours(args):
         except Exception as ex:      # keep measuring eagerly, but say so
             print('[bench] CUDA graph capture failed (%s); timing eager launches' % ex, file=sys.stderr)
             use_graph = False
+            graph_allreduce[0] = False
             for s in slots:
                 s.graph = None
-
-    red = torch.zeros(3, device=dev)
 
     def barrier():
         if world > 1:
@@ -385,7 +462,7 @@ def run_ours(args):
                 done[i % R].record(main)
                 if R == 1 and i + 1 < k:
                     prefetch(0)
-            if world > 1:
+            if world > 1 and not (graph_allreduce[0] and s.graph is not None):
                 if pending is not None:
                     pending.wait()
                 red[0:1].copy_(loss.detach())
@@ -457,6 +534,29 @@ def run_ours(args):
                 'kernel_ms_per_step': per_step[dom], 'all_kernels_ms_per_step': per_step,
                 'frac_of_nominal_8TBs': ach / 8000.0}
 
+    # ---- eager launches (no CUDA graph): what a trainer that calls the loss directly sees ------------------------
+    eager = None
+    if use_graph:
+        ne = min(args.steps, 50)
+        for i in range(3):
+            slots[i % R].step()
+        torch.cuda.synchronize()
+        ee0, ee1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ee0.record()
+        for i in range(ne):
+            slots[i % R].step()
+        ee1.record()
+        torch.cuda.synchronize()
+        eager = {'value': B * ne / (ee0.elapsed_time(ee1) * 1e-3), 'unit': 'frames/s (this rank)',
+                 'ms_per_step': ee0.elapsed_time(ee1) / ne, 'steps': ne}
+    # ---- the reference's own PyTorch ops on this GPU (the only GPU implementation that existed): SURVEY 8(d) -------
+    gpu_eager = None
+    if rank == 0 and world == 1 and not args.no_gpu_eager and args.camera == 'pinhole':
+        try:
+            gpu_eager = gpu_eager_rate(cfg, dev)
+        except Exception as ex:      # e.g. out of memory at the largest configs: say so, keep the line
+            gpu_eager = {'unavailable': str(ex)[:200]}
+            torch.cuda.empty_cache()
     if rank == 0:
         frames = world * B * args.steps
         cpu_val, cpu_iters, cpu_threads = (None, 0, 0)
@@ -465,16 +565,12 @@ def run_ours(args):
         line = {'metric': METRIC, 'value': frames / (t_ms * 1e-3), 'unit': 'frames/s', 'n_gpus': world,
                 'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': t_ms / args.steps,
                 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-                'config': {'workload': workload_name(args.config, cfg) + (
-                               ' [inverse depths given as the decoder pyramid, upsampled in-kernel]' if args.pyramid else '') + (
-                               ' [fisheye (VADAS) cameras instead of pinhole K]' if args.camera == 'fisheye' else '') + (
-                               ' [frames as image bytes, to_tensor (byte / 255) applied in-kernel]' if args.host_images == 'u8' else ''),
-                           'global_batch': world * B,
-                           'l2': 'rotating %d resident input sets (%.0f MB total footprint > 3x 126 MB L2)' % (
-                               R, R * foot / 2 ** 20),
-                           'numa_bound_cores': numa, 'cuda_graph': use_graph, 'kernel_mode': args.mode or 'fused',
-                           'loss': dict(LOSS_HP, padding_mode=cfg['padding']),
-                           'parallelism': 'dp%d (batch-sharded, one NCCL all-reduce of the loss per step)' % world},
+                'config': conf,
+                'run': {'numa_bound_cores': numa, 'cuda_graph': use_graph, 'kernel_mode': args.mode or 'fused',
+                        'sweep_kernel': 'two-pixels-per-lane' if os.environ.get('PSFM_SWEEP2', '0') not in ('', '0') else 'one-pixel-per-lane',
+                        'allreduce_floats_per_step': nred if world > 1 else 0,
+                        'allreduce': ('in the step graph' if graph_allreduce[0] else 'async, issued from Python') if world > 1 else None,
+                        'eager': eager, 'gpu_eager_baseline': gpu_eager},
                 'e2e': {'value': frames / (t_e2e_ms * 1e-3), 'unit': 'frames/s', 'h2d_bytes_per_step': h2d,
                         'd2h_bytes_per_step': d2h, 'ms_per_step': t_e2e_ms / args.steps},
                 'gpu_launches': launches_per_step * args.steps, 'gpu_launches_per_step': launches_per_step,
@@ -522,6 +618,13 @@ def main():
     ap.add_argument('--no-graph', action='store_true')
     ap.add_argument('--no-rotate', action='store_true')
     ap.add_argument('--no-cpu', action='store_true')
+    ap.add_argument('--allreduce', default='graph', choices=['graph', 'async'],
+                    help="multi-GPU: 'graph' captures the step's all-reduce in the step's CUDA graph; 'async' issues it "
+                         'from Python on the side and waits one step later (round-1 behaviour)')
+    ap.add_argument('--no-gpu-eager', action='store_true', help='skip the PyTorch-eager-on-GPU baseline leg')
+    ap.add_argument('--grad-bucket-mfloats', type=float, default=0.0,
+                    help='secondary multi-GPU measurement: all-reduce [loss | a parameter-gradient bucket of this many '
+                         'million floats] per step instead of the 12-byte loss triple (SURVEY.md 8(e): 14-27 M)')
     ap.add_argument('--no-numa', action='store_true', help='do not bind ranks to the cores next to their GPU')
     ap.add_argument('--host-images', default='native', choices=['native', 'u8'],
                     help='u8: frames stay image bytes on the host and in HBM; the kernels apply to_tensor (byte / 255)')

@@ -362,7 +362,8 @@ __global__ void __launch_bounds__(256) fisheye_ray_kernel(const SweepParams SP) 
 // upsampling decided per scale at run time)
 // CAM: 0 = pinhole cameras (K, ref_K 3x3), 1 = fisheye (VADAS) cameras (geometry/camera.py:194-394): K, ref_K are
 // rows of 11 values (k0..k6, s, div, ux, uy)
-template <typename real, int PAD, int VAR, int CT, int CAM = 0>
+// DBG: test instantiation that also records the discrete decisions (io->dbg decision words, io->sel arg-min maps)
+template <typename real, int PAD, int VAR, int CT, int CAM = 0, bool DBG = false>
 #ifdef PSFM_SWEEP_MAXREG
 __global__ void __maxnreg__(PSFM_SWEEP_MAXREG) sweep_kernel(const SweepParams SP) {
 #else
@@ -474,6 +475,20 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
   int prev_q = -1;
   real* d_out = (real*)SD.d_full + (size_t)b * plane;
 
+  // debug instantiation: floor of the sampling position after the padding mode's clipping (include/psfm.h, io->dbg)
+  auto record_decision = [&](int row, real ix, real iy) {
+    if (!SD.dbg || row < r0 || row >= r1 || !col_inner) return;
+    if (PAD == PSFM_PAD_BORDER) {
+      ix = !(ix > real(0)) ? real(0) : rmin(ix, real(W - 1));
+      iy = !(iy > real(0)) ? real(0) : rmin(iy, real(H - 1));
+    } else {
+      ix = rmin(rmax(ix, real(-2)), real(W + 1));
+      iy = rmin(rmax(iy, real(-2)), real(H + 1));
+    }
+    const int x0 = (int)rfloor(ix), y0 = (int)rfloor(iy);
+    SD.dbg[((size_t)j * P.B + b) * plane + (size_t)row * W + u] =
+        (uint32_t)min(max(x0 + 8, 0), 4095) | ((uint32_t)min(max(y0 + 8, 0), 4095) << 12);
+  };
   // gather pipeline: geometry of `row`, the 4 tap loads go in flight, consumed one step later
   vec4 tap[4];
   real twx = real(0), twy = real(0);
@@ -507,6 +522,7 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
       const real ix = fc[19] * (g * xn) + fc[21], iy = fc[20] * (g * yn) + fc[22];
       real mx, my;
       sample4_issue<real, vec4, PAD>(ctxp, H, W, Wp, kPadLo, ix, iy, twx, twy, mx, my, tap);
+      if (DBG) record_decision(row, ix, iy);
       // d (ix, iy) / d X, rows scaled by the border-clamp masks
       const real hxy = h * xn * yn;
       real a00 = fc[19] * (g + h * xn * xn), a01 = fc[19] * hxy, a10 = fc[20] * hxy, a11 = fc[20] * (g + h * yn * yn);
@@ -526,6 +542,7 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
     const real ix = p0 * iz, iy = p1 * iz;
     real mx, my;
     sample4_issue<real, vec4, PAD>(ctxp, H, W, Wp, kPadLo, ix, iy, twx, twy, mx, my, tap);
+    if (DBG) record_decision(row, ix, iy);
     rs[6 * 32] = (p2 >= real(1e-5)) ? D : -D;                     // sign flags the clamp of p2
     rs[7 * 32] = ix;
     rs[8 * 32] = iy;
@@ -644,6 +661,15 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
       const pr lA = xrA[P1] - yrA[P1];
       const real ls = (rabs(lA.lo()) + rabs(lA.hi())) + rabs(xrB[P1] - yrB[P1]);
       const real photo = K.ssim_w3 * ds + K.k1 * ls;
+      if (DBG) {       // L1 signs (bits 24-26) and SSIM clamp-range flags (bits 27-29) of this context at row p
+        if (SD.dbg && p >= r0 && p < r1 && p_real && col_inner) {
+          const real eB = xrB[P1] - yrB[P1];
+          auto in01 = [](real d) { return d >= real(0) && d <= real(1); };
+          const uint32_t bits = (lA.lo() >= real(0) ? 1u : 0u) | (lA.hi() >= real(0) ? 2u : 0u) | (eB >= real(0) ? 4u : 0u) |
+                                (in01(dA.lo()) ? 8u : 0u) | (in01(dA.hi()) ? 16u : 0u) | (in01(dB) ? 32u : 0u);
+          SD.dbg[((size_t)j * P.B + b) * plane + (size_t)p * W + u] |= bits << 24;
+        }
+      }
       real best = photo * m;
       int sel = mycand;
       if (C > 1) {
@@ -668,6 +694,9 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
       w_old = w_cur;
       w_cur = (p_real && sel == mycand) ? K.inv_count * m : real(0);
       if (j == 0 && p_real && col_inner && p >= r0 && p < r1) loss_acc += best;
+      if (DBG) {
+        if (j == 0 && p_real && col_inner && p >= r0 && p < r1 && SD.sel) SD.sel[(size_t)b * plane + (size_t)p * W + u] = (uint8_t)sel;
+      }
       const real wf = w_cur * K.ssim_w3;
       ssim_grad_v<real, pr>(stA, myA, wf, FA);
       ssim_grad_v<real, real>(stB, myB, wf, FB);
@@ -1023,7 +1052,7 @@ static int pick_prep_chunk(int H, long warps_per_chunk) {
   return best;
 }
 
-static bool use_sweep2(const psfm_loss_cfg* cfg) { return sweep2_eligible(cfg) && env_int("PSFM_SWEEP2", 1) != 0; }
+static bool use_sweep2(const psfm_loss_cfg* cfg) { return sweep2_eligible(cfg) && env_int("PSFM_SWEEP2", 0) != 0; }
 
 static void make_plan(const psfm_loss_cfg* cfg, const psfm_loss_io* io, SweepPlan& pl) {
   const size_t rs = cfg->real_dtype == PSFM_F64 ? 8 : 4;
@@ -1112,9 +1141,9 @@ static void fill_consts(SweepConsts<real>& c, const LossParams& P, int s0) {
   }
 }
 
-template <typename real, int PAD, int VAR, int CT, int CAM = 0>
+template <typename real, int PAD, int VAR, int CT, int CAM = 0, bool DBG = false>
 static cudaError_t launch_sweep_ct(const SweepParams& SP, dim3 grid, int threads, size_t smem, cudaStream_t st) {
-  auto kern = sweep_kernel<real, PAD, VAR, CT, CAM>;
+  auto kern = sweep_kernel<real, PAD, VAR, CT, CAM, DBG>;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
@@ -1194,7 +1223,6 @@ static cudaError_t run_sweep(const psfm_loss_cfg* cfg, const psfm_loss_io* io, v
       if (e2 != cudaSuccess) return e2;
       continue;
     }
-    if (debug) return cudaErrorNotSupported;        // decision words: two-pixels-per-lane sweep only
     const bool fisheye = cfg->camera_model == PSFM_CAM_FISHEYE;
     const int ring = fisheye ? 15 : (cfg->padding == PSFM_PAD_BORDER ? 11 : 10);
     const size_t smem = ((size_t)cfg->C * 4 * ring * 32 + (size_t)4 * cfg->C * 32 + (fisheye ? 24 * cfg->C : 0)) * sizeof(real);
@@ -1208,7 +1236,22 @@ static cudaError_t run_sweep(const psfm_loss_cfg* cfg, const psfm_loss_io* io, v
 #define PSFM_SWEEP(PADV) (var == 2 ? launch_sweep<real, PADV, 2>(SP, grid, threads, smem, st) \
                           : var == 1 ? launch_sweep<real, PADV, 1>(SP, grid, threads, smem, st) \
                                      : launch_sweep<real, PADV, 0>(SP, grid, threads, smem, st))
-    if (fisheye) {
+    if (debug) {
+      // decision words / arg-min maps (parity tests): fp32, plain inputs, 2 or 4 contexts (fisheye: 2)
+      e = cudaErrorNotSupported;
+      if constexpr (sizeof(real) == 4) {
+        const bool bd = cfg->padding == PSFM_PAD_BORDER;
+        if (var == 0 && fisheye && cfg->C == 2)
+          e = bd ? launch_sweep_ct<real, PSFM_PAD_BORDER, 0, 2, 1, true>(SP, grid, threads, smem, st)
+                 : launch_sweep_ct<real, PSFM_PAD_ZEROS, 0, 2, 1, true>(SP, grid, threads, smem, st);
+        else if (var == 0 && !fisheye && cfg->C == 2)
+          e = bd ? launch_sweep_ct<real, PSFM_PAD_BORDER, 0, 2, 0, true>(SP, grid, threads, smem, st)
+                 : launch_sweep_ct<real, PSFM_PAD_ZEROS, 0, 2, 0, true>(SP, grid, threads, smem, st);
+        else if (var == 0 && !fisheye && cfg->C == 4)
+          e = bd ? launch_sweep_ct<real, PSFM_PAD_BORDER, 0, 4, 0, true>(SP, grid, threads, smem, st)
+                 : launch_sweep_ct<real, PSFM_PAD_ZEROS, 0, 4, 0, true>(SP, grid, threads, smem, st);
+      }
+    } else if (fisheye) {
       // fp32, two contexts, plain inputs: own instantiation; everything else (any C, pre-map, upsampled inverse
       // depths, fp64) runs the run-time-generic one
       bool done = false;

@@ -381,6 +381,14 @@ __global__ void __launch_bounds__(32 * CT, sizeof(real) == 4 ? 8 / CT : 1) sweep
       ((pr*)(rs + 1 * 32))[1] = y.b;
     }
     const pr ls_t = chsum(cabs(x - y));
+    if (DBG) {         // L1 signs (bits 24-26) of this context at row t
+      if (SD.dbg && t >= r0 && t < r1) {
+        uint32_t* dw = SD.dbg + ((size_t)j * P.B + b) * plane + (size_t)t * W;
+        const c3 e = x - y;
+        if (ok0) dw[su0] |= ((e.a0.lo() >= real(0) ? 1u : 0u) | (e.a0.hi() >= real(0) ? 2u : 0u) | (e.b.lo() >= real(0) ? 4u : 0u)) << 24;
+        if (ok1) dw[su1] |= ((e.a1.lo() >= real(0) ? 1u : 0u) | (e.a1.hi() >= real(0) ? 2u : 0u) | (e.b.hi() >= real(0) ? 4u : 0u)) << 24;
+      }
+    }
     // ---------------- finish the gather of row t + 1 ---------------------------------------------------
     finish_row(t + 1);
     // ---------------- SSIM + L1 at row p, candidate min across the contexts --------------------------
@@ -398,6 +406,14 @@ __global__ void __launch_bounds__(32 * CT, sizeof(real) == 4 ? 8 / CT : 1) sweep
         ssim_grad_w<real, pr>(st.b, my.b, m9, fb);
 #pragma unroll
         for (int k = 0; k < 3; ++k) F[k] = c3(fa0[k], fa1[k], fb[k]);
+      }
+      if (DBG) {       // SSIM clamp-range flags (bits 27-29) of this context at row p
+        if (SD.dbg && p >= r0 && p < r1 && p_row) {
+          uint32_t* dw = SD.dbg + ((size_t)j * P.B + b) * plane + (size_t)p * W;
+          auto in01 = [](real d) { return d >= real(0) && d <= real(1); };
+          if (ok0) dw[su0] |= ((in01(dist.a0.lo()) ? 8u : 0u) | (in01(dist.a0.hi()) ? 16u : 0u) | (in01(dist.b.lo()) ? 32u : 0u)) << 24;
+          if (ok1) dw[su1] |= ((in01(dist.a1.lo()) ? 8u : 0u) | (in01(dist.a1.hi()) ? 16u : 0u) | (in01(dist.b.hi()) ? 32u : 0u)) << 24;
+        }
       }
       const pr ds = chsum(c3(pclamp01(dist.a0), pclamp01(dist.a1), pclamp01(dist.b)));
       const pr photo = vfma(pr(K.ssim_w3), ds, pr(K.k1) * ls_p);

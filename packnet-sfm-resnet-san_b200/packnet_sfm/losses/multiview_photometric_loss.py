@@ -57,6 +57,7 @@ class MultiViewPhotometricLoss(LossBase):
         # (models/SfmModel.py:86-88 -> models/model_utils.py:152-176).  With this flag the loss takes the
         # decoder's native pyramid and does that upsampling (and its adjoint) inside the kernels.
         self.upsample_depth_maps = bool(kwargs.get('upsample_depth_maps', False))
+        self.debug_decisions = bool(kwargs.get('debug_decisions', False))      # test hook: ops.LAST_DECISIONS
         if self.automask_loss:
             assert self.photometric_reduce_op == 'min', \
                 'For automasking only the min photometric_reduce_op is supported.'
@@ -70,7 +71,7 @@ class MultiViewPhotometricLoss(LossBase):
                     C1=self.C1, C2=self.C2, photometric_reduce_op=self.photometric_reduce_op,
                     clip_loss=self.clip_loss, padding_mode=self.padding_mode, automask_loss=self.automask_loss,
                     premap=int(self.sigmoid_premap), min_depth=self.min_depth, max_depth=self.max_depth,
-                    upsample_depth_maps=self.upsample_depth_maps)
+                    upsample_depth_maps=self.upsample_depth_maps, debug_decisions=self.debug_decisions)
 
     def warp_ref_image(self, inv_depths, ref_image, K, ref_K, pose, image_size=None):
         """Warp `ref_image` into the target view at every scale (reference :131-195).  Returns a list of

@@ -21,6 +21,9 @@ from .block_ops import (abs_mean_op, normalize_op, photometric_map_op, project_o
 DEFAULT_MODE = os.environ.get('PSFM_LOSS_MODE', 'fused')
 
 
+# set by a call with hp['debug_decisions']: {'taps': [C,B,Hs,Ws] int32 decision words per scale, 'sel': [B,Hs,Ws] uint8}
+LAST_DECISIONS = None
+
 FISHEYE_KEYS = ('k', 's', 'div', 'ux', 'uy')
 
 
@@ -170,6 +173,13 @@ class _LossPlan:
         self.sel = [torch.empty((B, cfg.Hs[s], cfg.Ws[s]), dtype=torch.uint8, device=dev) for s in range(n)]
         for s in range(n):
             io.sel[s] = self.sel[s].data_ptr()
+        # test hook (include/psfm.h, io->dbg): the discrete decisions of the fused kernels, for the parity protocol
+        self.dbg = None
+        if hp.get('debug_decisions'):
+            self.dbg = [torch.zeros((Cn, B, cfg.Hs[s], cfg.Ws[s]), dtype=torch.int32, device=dev) for s in range(n)]
+            for s in range(n):
+                self.sel[s].fill_(255)
+                io.dbg[s] = self.dbg[s].data_ptr()
         self.out = torch.empty(3, dtype=real, device=dev)
         self.grads = None
 
@@ -207,6 +217,9 @@ class _PhotometricLossFn(torch.autograd.Function):
                 _C.check(_C.lib.psfm_loss_forward_backward(*plan.args(), _C.ptr(plan.out), st))
             else:
                 _C.check(_C.lib.psfm_loss_forward(*plan.args(), _C.ptr(plan.out), st))
+        if plan.dbg is not None:
+            global LAST_DECISIONS
+            LAST_DECISIONS = dict(taps=plan.dbg, sel=plan.sel)
         ctx.plan, ctx.mode, ctx.consumed = plan, mode, False
         ctx.counts = (n, Cn)
         out, plan.out = plan.out, None      # the node must not reference its own output (reference cycle)

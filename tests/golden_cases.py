@@ -54,6 +54,15 @@ CASES.update({
     'fisheye_B1_192x640_C2_U_zeros': (dict(B=1, H=192, W=640, C=2, pyramid=False), {}, dict(fisheye=True)),
 })
 
+# Shapes of the benchmarked configurations (BASELINE.json configs[1..4]) for the live-oracle parity tests
+# (tests/test_loss_shapes_gpu.py); no fixture files: the CPU oracle runs in the test.
+CASES.update({
+    'cfg2_B2_192x640_C2': (dict(B=2, H=192, W=640, C=2, pyramid=False), {}, {}),
+    'cfg3_B1_384x640_C2_bf16': (dict(B=1, H=384, W=640, C=2, pyramid=False), {}, dict(bf16=True)),
+    'cfg4_B1_1216x1936_C2_border': (dict(B=1, H=1216, W=1936, C=2, pyramid=False), dict(padding_mode='border'), {}),
+    'cfg5_B1_384x640_C4': (dict(B=1, H=384, W=640, C=4, pyramid=False), {}, {}),
+})
+
 FORK_RANGE = (0.5, 80.0)
 
 

@@ -1,13 +1,27 @@
-# 1/2/4/8-GPU bench lines of the final build on one box, plus the byte-frame variants at 8 GPUs
+# 1/2/4/8-GPU bench lines on one box.   bash tools/scale_run.sh [--config K] [extra bench flags]
+# writes gpurun_out/scale/cfg<K>_n<N>.json (+ the reference arm at N=1, the bucket line at N=8 and the bare H2D ceiling)
+CFG=2
+if [ "$1" = "--config" ]; then CFG=$2; shift 2; fi
 mkdir -p gpurun_out/scale
+NG=$(nvidia-smi -L | wc -l)
 for n in 1 2 4 8; do
-  if [ $n = 1 ]; then python bench.py --gpus 1 --steps 100 --warmup 10 --no-cpu > gpurun_out/scale/n1.json 2> gpurun_out/scale/n1.err
-  else python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 2951$n bench.py --gpus $n --steps 100 --warmup 10 --no-cpu > gpurun_out/scale/n$n.json 2> gpurun_out/scale/n$n.err; fi
+  [ $n -gt $NG ] && continue
+  out=gpurun_out/scale/cfg${CFG}_n$n
+  if [ $n = 1 ]; then python bench.py --gpus 1 --config $CFG --steps 100 --warmup 10 --no-cpu "$@" > $out.json 2> $out.err
+  else python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 2951$n bench.py --gpus $n --config $CFG --steps 100 --warmup 10 --no-cpu "$@" > $out.json 2> $out.err; fi
+  python -c "
+import json; d=json.load(open('$out.json')); print('cfg$CFG n$n', d['n_gpus'], round(d['value']), round(d['ms_per_step'],4), 'e2e', round(d['e2e']['value']), d['run'].get('allreduce'))"
 done
-for n in 4 8; do
-python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 2952$n bench.py --gpus $n --steps 100 --warmup 10 --no-cpu --host-images u8 > gpurun_out/scale/n${n}_u8.json 2> gpurun_out/scale/n${n}_u8.err
-python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 2953$n bench.py --gpus $n --steps 100 --warmup 10 --no-cpu --host-images u8 --pyramid > gpurun_out/scale/n${n}_u8_pyramid.json 2> gpurun_out/scale/n${n}_u8_pyramid.err
-done
+if [ $CFG = 2 ]; then
+  for n in 1 2 4 8; do
+    [ $n -gt $NG ] && continue
+    if [ $n = 1 ]; then python tools/h2d_ceiling.py > gpurun_out/scale/h2d_n$n.json 2>/dev/null
+    else python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 2961$n tools/h2d_ceiling.py > gpurun_out/scale/h2d_n$n.json 2>/dev/null
+         python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 2962$n tools/h2d_ceiling.py --bind > gpurun_out/scale/h2d_bind_n$n.json 2>/dev/null; fi
+    cat gpurun_out/scale/h2d_n$n.json
+  done
+  n=$NG
+  [ $n -gt 1 ] && python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29540 bench.py --gpus $n --steps 100 --warmup 10 --no-cpu --grad-bucket-mfloats 28 --allreduce async > gpurun_out/scale/cfg2_n${n}_bucket28.json 2> gpurun_out/scale/cfg2_n${n}_bucket28.err
+  [ $n -gt 1 ] && python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29541 bench.py --gpus $n --steps 100 --warmup 10 --no-cpu --allreduce async > gpurun_out/scale/cfg2_n${n}_async.json 2> gpurun_out/scale/cfg2_n${n}_async.err
+fi
 nvidia-smi topo -m > gpurun_out/scale/topo.txt 2>&1
-for f in n1 n2 n4 n8 n4_u8 n4_u8_pyramid n8_u8 n8_u8_pyramid; do python -c "
-import json; d=json.load(open('gpurun_out/scale/$f.json')); print('$f', d['n_gpus'], round(d['value']), round(d['ms_per_step'],4), round(d['e2e']['value']), d['e2e']['h2d_bytes_per_step'], d['config'].get('numa_bound_cores'))"; done
