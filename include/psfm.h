@@ -100,10 +100,11 @@ typedef struct psfm_loss_io {
   void* d_pose[PSFM_MAX_CTX];                       /* [B,4,4] real (bwd out, overwritten; row 3 = 0) */
   uint32_t* dbg[PSFM_MAX_SCALES];                   /* NULL, or [C,B,Hs,Ws] u32 (test hook of psfm_loss_forward_backward,
                                                      * pinhole sweep kernels): the discrete decisions the loss took at
-                                                     * each pixel -- bits 0-11 floor(ix) + 8, bits 12-23 floor(iy) + 8 of
+                                                     * each pixel -- bits 0-11 floor(ix) + 8, bits 12-22 floor(iy) + 8 of
                                                      * the bilinear tap of context c (after the padding mode's clipping),
-                                                     * bits 24-26 sign (>= 0) of warped - target per channel (L1 term),
-                                                     * bits 27-29 SSIM distance of the channel inside its clamp range;
+                                                     * bits 23-28 sign of warped - target per channel (L1 term; two bits
+                                                     * each: 0 negative, 1 zero, 2 positive), bits 29-31 SSIM distance of
+                                                     * the channel inside its clamp range;
                                                      * io->sel[i] then receives the arg-min candidate as in
                                                      * psfm_loss_forward.  Lets the parity tests name the pixels whose
                                                      * tap or arg-min ACTUALLY differs from the fp64 oracle's

@@ -487,7 +487,7 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
     }
     const int x0 = (int)rfloor(ix), y0 = (int)rfloor(iy);
     SD.dbg[((size_t)j * P.B + b) * plane + (size_t)row * W + u] =
-        (uint32_t)min(max(x0 + 8, 0), 4095) | ((uint32_t)min(max(y0 + 8, 0), 4095) << 12);
+        (uint32_t)min(max(x0 + 8, 0), 4095) | ((uint32_t)min(max(y0 + 8, 0), 2047) << 12);
   };
   // gather pipeline: geometry of `row`, the 4 tap loads go in flight, consumed one step later
   vec4 tap[4];
@@ -661,13 +661,14 @@ __global__ void __launch_bounds__(CT ? 32 * CT : 256, (CT == 2 && sizeof(real) =
       const pr lA = xrA[P1] - yrA[P1];
       const real ls = (rabs(lA.lo()) + rabs(lA.hi())) + rabs(xrB[P1] - yrB[P1]);
       const real photo = K.ssim_w3 * ds + K.k1 * ls;
-      if (DBG) {       // L1 signs (bits 24-26) and SSIM clamp-range flags (bits 27-29) of this context at row p
+      if (DBG) {       // L1 signs (bits 23-28) and SSIM clamp-range flags (bits 29-31) of this context at row p
         if (SD.dbg && p >= r0 && p < r1 && p_real && col_inner) {
           const real eB = xrB[P1] - yrB[P1];
           auto in01 = [](real d) { return d >= real(0) && d <= real(1); };
-          const uint32_t bits = (lA.lo() >= real(0) ? 1u : 0u) | (lA.hi() >= real(0) ? 2u : 0u) | (eB >= real(0) ? 4u : 0u) |
-                                (in01(dA.lo()) ? 8u : 0u) | (in01(dA.hi()) ? 16u : 0u) | (in01(dB) ? 32u : 0u);
-          SD.dbg[((size_t)j * P.B + b) * plane + (size_t)p * W + u] |= bits << 24;
+          auto sg = [](real e) { return e > real(0) ? 2u : (e < real(0) ? 0u : 1u); };
+          const uint32_t bits = sg(lA.lo()) | (sg(lA.hi()) << 2) | (sg(eB) << 4) |
+                                (in01(dA.lo()) ? 64u : 0u) | (in01(dA.hi()) ? 128u : 0u) | (in01(dB) ? 256u : 0u);
+          SD.dbg[((size_t)j * P.B + b) * plane + (size_t)p * W + u] |= bits << 23;
         }
       }
       real best = photo * m;

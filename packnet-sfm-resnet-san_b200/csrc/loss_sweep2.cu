@@ -32,9 +32,10 @@ template <typename real> struct Geo2 {
   P2<real> D, T0, T1, T2, p2, iz, ix, iy;    // T = A0 + A1 v (d p / d D)
 };
 
-// decision word of the debug instantiation: bits 0-11 floor(ix) + 8, 12-23 floor(iy) + 8 (after the mode's clipping)
+// decision word of the debug instantiation (include/psfm.h): bits 0-11 floor(ix) + 8, 12-22 floor(iy) + 8 (after the
+// mode's clipping), 23-28 L1 signs, 29-31 SSIM clamp-range flags
 __device__ __forceinline__ uint32_t decision_word(int x0, int y0) {
-  return (uint32_t)min(max(x0 + 8, 0), 4095) | ((uint32_t)min(max(y0 + 8, 0), 4095) << 12);
+  return (uint32_t)min(max(x0 + 8, 0), 4095) | ((uint32_t)min(max(y0 + 8, 0), 2047) << 12);
 }
 
 // ---- staging of the pixel records: 1-D bulk copies (TMA) into shared memory, completion on an mbarrier ----------
@@ -381,12 +382,13 @@ __global__ void __launch_bounds__(32 * CT, sizeof(real) == 4 ? 8 / CT : 1) sweep
       ((pr*)(rs + 1 * 32))[1] = y.b;
     }
     const pr ls_t = chsum(cabs(x - y));
-    if (DBG) {         // L1 signs (bits 24-26) of this context at row t
+    if (DBG) {         // L1 signs (bits 23-28, two per channel: 0 negative, 1 zero, 2 positive) of this context at row t
       if (SD.dbg && t >= r0 && t < r1) {
         uint32_t* dw = SD.dbg + ((size_t)j * P.B + b) * plane + (size_t)t * W;
         const c3 e = x - y;
-        if (ok0) dw[su0] |= ((e.a0.lo() >= real(0) ? 1u : 0u) | (e.a0.hi() >= real(0) ? 2u : 0u) | (e.b.lo() >= real(0) ? 4u : 0u)) << 24;
-        if (ok1) dw[su1] |= ((e.a1.lo() >= real(0) ? 1u : 0u) | (e.a1.hi() >= real(0) ? 2u : 0u) | (e.b.hi() >= real(0) ? 4u : 0u)) << 24;
+        auto sg = [](real v) { return v > real(0) ? 2u : (v < real(0) ? 0u : 1u); };
+        if (ok0) dw[su0] |= (sg(e.a0.lo()) | (sg(e.a0.hi()) << 2) | (sg(e.b.lo()) << 4)) << 23;
+        if (ok1) dw[su1] |= (sg(e.a1.lo()) | (sg(e.a1.hi()) << 2) | (sg(e.b.hi()) << 4)) << 23;
       }
     }
     // ---------------- finish the gather of row t + 1 ---------------------------------------------------
@@ -407,12 +409,12 @@ __global__ void __launch_bounds__(32 * CT, sizeof(real) == 4 ? 8 / CT : 1) sweep
 #pragma unroll
         for (int k = 0; k < 3; ++k) F[k] = c3(fa0[k], fa1[k], fb[k]);
       }
-      if (DBG) {       // SSIM clamp-range flags (bits 27-29) of this context at row p
+      if (DBG) {       // SSIM clamp-range flags (bits 29-31) of this context at row p
         if (SD.dbg && p >= r0 && p < r1 && p_row) {
           uint32_t* dw = SD.dbg + ((size_t)j * P.B + b) * plane + (size_t)p * W;
           auto in01 = [](real d) { return d >= real(0) && d <= real(1); };
-          if (ok0) dw[su0] |= ((in01(dist.a0.lo()) ? 8u : 0u) | (in01(dist.a0.hi()) ? 16u : 0u) | (in01(dist.b.lo()) ? 32u : 0u)) << 24;
-          if (ok1) dw[su1] |= ((in01(dist.a1.lo()) ? 8u : 0u) | (in01(dist.a1.hi()) ? 16u : 0u) | (in01(dist.b.hi()) ? 32u : 0u)) << 24;
+          if (ok0) dw[su0] |= ((in01(dist.a0.lo()) ? 1u : 0u) | (in01(dist.a0.hi()) ? 2u : 0u) | (in01(dist.b.lo()) ? 4u : 0u)) << 29;
+          if (ok1) dw[su1] |= ((in01(dist.a1.lo()) ? 1u : 0u) | (in01(dist.a1.hi()) ? 2u : 0u) | (in01(dist.b.hi()) ? 4u : 0u)) << 29;
         }
       }
       const pr ds = chsum(c3(pclamp01(dist.a0), pclamp01(dist.a1), pclamp01(dist.b)));

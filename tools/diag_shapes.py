@@ -34,12 +34,15 @@ top = e.flatten().topk(3)
 w = res['taps'][s].long()
 for v, i in zip(top.values.tolist(), top.indices.tolist()):
     b, r = divmod(i, H * W); y, x = divmod(r, W)
-    print('pixel b=%d y=%d x=%d err %.3g g %.4g g64 %.4g' % (b, y, x, v, g[b, 0, y, x].item(), g64[b, 0, y, x].item()))
+    print('pixel b=%d y=%d x=%d err %.3g g %.6g g64 %.6g g32(ref arithmetic) %.6g' % (b, y, x, v, g[b, 0, y, x].item(), g64[b, 0, y, x].item(), ref32['d_invd'][s][b, 0, y, x].item()))
+    print('  3x3 g  ', g[b, 0, max(y-1,0):y+2, max(x-1,0):x+2].numpy().tolist())
+    print('  3x3 g64', g64[b, 0, max(y-1,0):y+2, max(x-1,0):x+2].numpy().tolist())
+    print('  3x3 g32', ref32['d_invd'][s][b, 0, max(y-1,0):y+2, max(x-1,0):x+2].numpy().tolist())
     ys, xs = slice(max(y - 2, 0), y + 3), slice(max(x - 2, 0), x + 3)
     print('  sel kernel\n', res['sel'][s][b, ys, xs].numpy(), '\n  arg oracle\n', dec[s]['arg'][b, ys, xs].numpy())
     for j in range(w.shape[0]):
         print('  ctx', j, 'kernel x0', ((w[j, b, ys, xs] & 0xfff) - 8).numpy().tolist(), 'oracle x0', dec[s]['x0'][j, b, ys, xs].numpy().tolist())
-        print('  ctx', j, 'kernel y0', (((w[j, b, ys, xs] >> 12) & 0xfff) - 8).numpy().tolist(), 'oracle y0', dec[s]['y0'][j, b, ys, xs].numpy().tolist())
-        print('  ctx', j, 'bits kernel', ((w[j, b, ys, xs] >> 24) & 0x3f).numpy().tolist(), 'oracle', dec[s]['bits'][j, b, ys, xs].numpy().tolist())
+        print('  ctx', j, 'kernel y0', (((w[j, b, ys, xs] >> 12) & 0x7ff) - 8).numpy().tolist(), 'oracle y0', dec[s]['y0'][j, b, ys, xs].numpy().tolist())
+        print('  ctx', j, 'bits kernel', ((w[j, b, ys, xs] >> 23) & 0x1ff).numpy().tolist(), 'oracle', dec[s]['bits'][j, b, ys, xs].numpy().tolist())
     d = inp['inv_depths'][s][b, 0, ys, xs]
     print('  inv depth', d.numpy().tolist())
