@@ -237,6 +237,8 @@ def run_reference(args):
         return
     cfg = dict(CONFIGS[args.config], pyramid=args.pyramid, camera=args.camera, host_images=args.host_images)
     world = int(os.environ.get('WORLD_SIZE', 1))
+    if args.global_batch:
+        cfg['B'] = max(1, args.global_batch // world)
     cores = os.cpu_count()
     torch.set_num_threads(cores)
     sys.path.insert(0, os.path.join(ROOT, 'oracle'))
@@ -320,6 +322,8 @@ def run_ours(args):
     sys.path.insert(0, os.path.join(ROOT, 'oracle'))
 
     cfg = dict(CONFIGS[args.config], pyramid=args.pyramid, camera=args.camera, host_images=args.host_images)
+    if args.global_batch:      # strong scaling (BASELINE.json configs[2]: global batch 16 sharded over 2 / 4 / 8 GPUs)
+        cfg['B'] = max(1, args.global_batch // world)
     B = cfg['B']
     loss_fn = MultiViewPhotometricLoss(padding_mode=cfg['padding'], kernel_mode=args.mode,
                                        upsample_depth_maps=args.pyramid, **LOSS_HP)
@@ -564,7 +568,8 @@ def run_ours(args):
             cpu_val, cpu_iters, cpu_threads = cpu_oracle_rate(CONFIGS[1], 1)
         line = {'metric': METRIC, 'value': frames / (t_ms * 1e-3), 'unit': 'frames/s', 'n_gpus': world,
                 'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': t_ms / args.steps,
-                'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+                'higher_is_better': True, 'scaling': 'strong' if args.global_batch else 'weak', 'vs_baseline': None,
+                'dtype': 'f32', 'data': 'synthetic',
                 'config': conf,
                 'run': {'numa_bound_cores': numa, 'cuda_graph': use_graph, 'kernel_mode': args.mode or 'fused',
                         'sweep_kernel': 'two-pixels-per-lane' if os.environ.get('PSFM_SWEEP2', '0') not in ('', '0') else 'one-pixel-per-lane',
@@ -618,6 +623,8 @@ def main():
     ap.add_argument('--no-graph', action='store_true')
     ap.add_argument('--no-rotate', action='store_true')
     ap.add_argument('--no-cpu', action='store_true')
+    ap.add_argument('--global-batch', type=int, default=0,
+                    help='strong scaling: this many frames in total, sharded over the ranks (default: B per GPU of the config)')
     ap.add_argument('--allreduce', default='graph', choices=['graph', 'async'],
                     help="multi-GPU: 'graph' captures the step's all-reduce in the step's CUDA graph; 'async' issues it "
                          'from Python on the side and waits one step later (round-1 behaviour)')

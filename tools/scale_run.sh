@@ -2,13 +2,16 @@
 # writes gpurun_out/scale/cfg<K>_n<N>.json (+ the reference arm at N=1, the bucket line at N=8 and the bare H2D ceiling)
 CFG=2
 if [ "$1" = "--config" ]; then CFG=$2; shift 2; fi
+STEPS=100
+[ $CFG = 4 ] && STEPS=40
+[ $CFG = 5 ] && STEPS=30
 mkdir -p gpurun_out/scale
 NG=$(nvidia-smi -L | wc -l)
 for n in 1 2 4 8; do
   [ $n -gt $NG ] && continue
   out=gpurun_out/scale/cfg${CFG}_n$n
-  if [ $n = 1 ]; then python bench.py --gpus 1 --config $CFG --steps 100 --warmup 10 --no-cpu "$@" > $out.json 2> $out.err
-  else python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 2951$n bench.py --gpus $n --config $CFG --steps 100 --warmup 10 --no-cpu "$@" > $out.json 2> $out.err; fi
+  if [ $n = 1 ]; then python bench.py --gpus 1 --config $CFG --steps $STEPS --warmup 10 --no-cpu --no-gpu-eager "$@" > $out.json 2> $out.err
+  else python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 2951$n bench.py --gpus $n --config $CFG --steps $STEPS --warmup 10 --no-cpu --no-gpu-eager "$@" > $out.json 2> $out.err; fi
   python -c "
 import json; d=json.load(open('$out.json')); print('cfg$CFG n$n', d['n_gpus'], round(d['value']), round(d['ms_per_step'],4), 'e2e', round(d['e2e']['value']), d['run'].get('allreduce'))"
 done
