@@ -586,8 +586,12 @@ def run_ours(args):
                               'PyTorch-CPU oracle' % cpu_iters}}
         emit(line)
     if world > 1:
+        # leave without tearing the communicator down: with collectives captured in CUDA graphs the tear-down was seen to
+        # block until the watchdog fired (round 2, 2 GPUs); the line is out, nothing is left to flush
         dist.barrier()
-        dist.destroy_process_group()
+        torch.cuda.synchronize()
+        sys.stdout.flush(); sys.stderr.flush()
+        os._exit(0)
 
 
 _RESULT_FD = None
@@ -625,9 +629,11 @@ def main():
     ap.add_argument('--no-cpu', action='store_true')
     ap.add_argument('--global-batch', type=int, default=0,
                     help='strong scaling: this many frames in total, sharded over the ranks (default: B per GPU of the config)')
-    ap.add_argument('--allreduce', default='graph', choices=['graph', 'async'],
-                    help="multi-GPU: 'graph' captures the step's all-reduce in the step's CUDA graph; 'async' issues it "
-                         'from Python on the side and waits one step later (round-1 behaviour)')
+    ap.add_argument('--allreduce', default='async', choices=['graph', 'async'],
+                    help="multi-GPU: 'async' (default) issues the step's all-reduce from Python on NCCL's stream and waits "
+                         "for it one step later, so it overlaps the next step; 'graph' captures it inside the step's CUDA "
+                         'graph (measured at 2 GPUs: 0.335 ms/step against 0.321 async -- the collective then sits on '
+                         'the critical path -- and the ranks do not shut down cleanly: kept for the record only)')
     ap.add_argument('--no-gpu-eager', action='store_true', help='skip the PyTorch-eager-on-GPU baseline leg')
     ap.add_argument('--grad-bucket-mfloats', type=float, default=0.0,
                     help='secondary multi-GPU measurement: all-reduce [loss | a parameter-gradient bucket of this many '

@@ -123,8 +123,13 @@ unsigned long long psfm_launch_count(void);
 int psfm_profile_enable(int on);
 int psfm_profile_read(float* ms, int* tags, int max_records);
 
-/* Scratch bytes psfm_loss_forward/backward need for this configuration. */
+/* Scratch bytes psfm_loss_forward/backward need for this configuration (upper bound: every scale is assumed to
+ * have its own images). */
 size_t psfm_loss_workspace_bytes(const psfm_loss_cfg* cfg);
+/* The same for these pointers: scales that share their image / context / mask pointers (all of them in the shipped
+ * upsample_depth_maps mode) share the image-sized scratch regions -- 0.11 GiB instead of 0.33 GiB at 8 x 192 x 640.
+ * A workspace of this size is accepted by the loss entry points when they are called with the same cfg / io. */
+size_t psfm_loss_workspace_bytes_io(const psfm_loss_cfg* cfg, const psfm_loss_io* io);
 
 /* MultiViewPhotometricLoss.forward (losses/multiview_photometric_loss.py:331-410) with the
  * pinhole warp_ref_image (:131-195 upstream form): view synthesis for every (scale, context)
@@ -168,10 +173,29 @@ int psfm_warp_backward(int B, int H, int W, int img_dtype, int real_dtype, int p
                        const void* pose, const void* grad_out, void* d_depth, void* d_pose,
                        void* d_ref_image, void* workspace, size_t workspace_bytes, void* stream);
 
-/* interpolate_image / match_scales (utils/image.py:117-214): bilinear, align_corners=True
- * (mode 0) or nearest (mode 1) resize of [N,Hi,Wi] planes to [N,Ho,Wo]. */
+/* interpolate_image / interpolate_scales / match_scales (utils/image.py:117-214) and the model's upsample_output
+ * (models/model_utils.py:152-193): resize of [N,Hi,Wi] planes to [N,Ho,Wo] with torch's F.interpolate arithmetic --
+ * mode 0 bilinear align_corners=True, mode 1 nearest, mode 2 bilinear align_corners=False.
+ * psfm_resize_backward is its adjoint (grad_out [N,Ho,Wo] -> grad_in [N,Hi,Wi], f32 / f64, gathered per source
+ * pixel in a fixed order: deterministic). */
 int psfm_resize(int N, int Hi, int Wi, int Ho, int Wo, int dtype, int mode, const void* in, void* out,
                 void* stream);
+int psfm_resize_backward(int N, int Hi, int Wi, int Ho, int Wo, int dtype, int mode, const void* grad_out,
+                         void* grad_in, void* stream);
+
+/* GenericCamera.project (geometry/camera_generic.py:86-208): the ray-surface camera "projects" a
+ * point by a soft arg-max over the 41 x 41 patch of viewing rays around the pixel -- softmax, with temperature
+ * `temperature` (max(1e-8, 1e-4 / exp(0.1 progress)), :107-110,:183-185), of the cosines between the point's direction
+ * and the rays; the result is the weighted mean of the patch's (row, col) indices.  dir [B,3,h,w]: point directions
+ * (un-normalised; the half-resolution, pose-transformed points of :172-180), rays [B,3,h,w]: the ray surface at the
+ * same resolution; h, w >= 41.  Outputs: coords [B,h,w,2] = (row, col); dhat [B,3,h,w] and stats [B,h,w,2] are state
+ * for the backward.  The reference is batch-1 (.squeeze()) and materialises the [h w, 1681, 3] patch tensor.
+ * Backward: grad_coords [B,h,w,2] -> d_dir, d_rays [B,3,h,w]; d_rays is gathered per ray in a fixed order (no atomics). */
+int psfm_raysurf_project(int B, int h, int w, int dt, double temperature, const void* dir, const void* rays, void* coords,
+                         void* dhat, void* stats, void* stream);
+int psfm_raysurf_project_backward(int B, int h, int w, int dt, double temperature, const void* dir, const void* rays,
+                                  const void* coords, const void* dhat, const void* stats, const void* grad_coords,
+                                  void* d_dir, void* d_rays, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Building-block operators: the reference functions of this path for callers that use them

@@ -457,7 +457,7 @@ static WorkspaceLayout carve(const psfm_loss_cfg* cfg, LossParams& P) {
   return L;
 }
 
-size_t stream_workspace_bytes(const psfm_loss_cfg* cfg);        // loss_stream.cu
+size_t stream_workspace_bytes(const psfm_loss_cfg* cfg, const psfm_loss_io* io);        // loss_sweep.cu
 bool stream_eligible(const psfm_loss_cfg* cfg);
 cudaError_t loss_stream_dispatch(const psfm_loss_cfg* cfg, const psfm_loss_io* io, void* ws_split, void* ws_stream,
                                  void* loss_out, cudaStream_t st);
@@ -468,8 +468,9 @@ static size_t split_workspace_bytes(const psfm_loss_cfg* cfg) {
 }
 
 // [ tile-kernel (split) region | streaming-kernel region ]
-size_t loss_workspace_bytes(const psfm_loss_cfg* cfg) {
-  return split_workspace_bytes(cfg) + (stream_eligible(cfg) ? stream_workspace_bytes(cfg) : 0);
+// io == nullptr: by configuration alone (every scale its own image set); with io: for the image sets that exist
+size_t loss_workspace_bytes(const psfm_loss_cfg* cfg, const psfm_loss_io* io) {
+  return split_workspace_bytes(cfg) + (stream_eligible(cfg) ? stream_workspace_bytes(cfg, io) : 0);
 }
 
 void build_params(const psfm_loss_cfg* cfg, const psfm_loss_io* io, void* ws, LossParams& P) {

@@ -1092,7 +1092,12 @@ static void make_plan(const psfm_loss_cfg* cfg, const psfm_loss_io* io, SweepPla
     if (S.pchunk_h < kMinChunk) S.pchunk_h = S.H < kMinChunk ? S.H : kMinChunk;
     S.pchunks = cdiv(S.H, S.pchunk_h);
   }
-  // workspace layout does not depend on the grouping: every scale owns worst-case sized regions
+  // workspace layout: the image-sized regions (records, packed contexts, edge weights, rays) exist once per SET --
+  // one set in the shipped upsample_depth_maps mode, where all scales share the images; without `io` (size query by
+  // configuration alone) every scale is assumed to be its own set
+  bool heavy[PSFM_MAX_SCALES];
+  for (int s = 0; s < cfg->n; ++s) heavy[s] = io == nullptr;
+  for (int i = 0; i < pl.nsets && io; ++i) heavy[pl.sets[i].scale[0]] = true;
   size_t off = 0;
   pl.off_one = off; off = al(off + rs);
   for (int s = 0; s < cfg->n; ++s) {
@@ -1101,10 +1106,10 @@ static void make_plan(const psfm_loss_cfg* cfg, const psfm_loss_io* io, SweepPla
     const int minc = Hs < kMinChunk ? Hs : kMinChunk;
     const size_t worst = (size_t)cdiv(Ws, kInner) * cdiv(Hs, minc);
     const size_t pworst = (size_t)cdiv(Ws, kPrepInner) * cdiv(Hs, minc);
-    pl.off_rec[s] = off;   off = al(off + (size_t)cfg->B * Hs * 2 * ((Ws + 1) / 2) * 12 * rs);   // three real4 planes
-    pl.off_ctxp[s] = off;  off = al(off + (size_t)cfg->C * cfg->B * (Hs + kPadLo + kPadHi) * (Ws + kPadLo + kPadHi) * 4 * rs);
-    pl.off_wxy[s] = off;   off = al(off + px * 2 * rs);
-    pl.off_ray[s] = off;   if (cfg->camera_model == PSFM_CAM_FISHEYE) off = al(off + px * 2 * rs);
+    pl.off_rec[s] = off;   if (heavy[s]) off = al(off + (size_t)cfg->B * Hs * 2 * ((Ws + 1) / 2) * 12 * rs);   // three real4 parts
+    pl.off_ctxp[s] = off;  if (heavy[s]) off = al(off + (size_t)cfg->C * cfg->B * (Hs + kPadLo + kPadHi) * (Ws + kPadLo + kPadHi) * 4 * rs);
+    pl.off_wxy[s] = off;   if (heavy[s]) off = al(off + px * 2 * rs);
+    pl.off_ray[s] = off;   if (heavy[s] && cfg->camera_model == PSFM_CAM_FISHEYE) off = al(off + px * 2 * rs);
     const bool ups = cfg->Hd[s] > 0 && (cfg->Hd[s] != Hs || cfg->Wd[s] != Ws);
     pl.off_dfull[s] = off; if (ups) off = al(off + px * rs);            // full-resolution d inv_depth before pooling
     pl.off_prep[s] = off;  off = al(off + (size_t)cfg->B * pworst * kPrepVals * sizeof(double));
@@ -1119,9 +1124,9 @@ static void make_plan(const psfm_loss_cfg* cfg, const psfm_loss_io* io, SweepPla
   pl.total = off;
 }
 
-size_t stream_workspace_bytes(const psfm_loss_cfg* cfg) {
+size_t stream_workspace_bytes(const psfm_loss_cfg* cfg, const psfm_loss_io* io) {
   SweepPlan pl;
-  make_plan(cfg, nullptr, pl);
+  make_plan(cfg, io, pl);
   return pl.total;
 }
 

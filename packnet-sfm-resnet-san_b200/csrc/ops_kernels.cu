@@ -119,6 +119,70 @@ template <> __device__ __forceinline__ void st_val<float>(float* p, double v) { 
 template <> __device__ __forceinline__ void st_val<double>(double* p, double v) { *p = v; }
 template <> __device__ __forceinline__ void st_val<__nv_bfloat16>(__nv_bfloat16* p, double v) { *p = __float2bfloat16((float)v); }
 
+// One axis of torch's upsample kernels: the two source indices and weights of destination index d.
+//   mode 0 bilinear align_corners=True : src = d (in - 1) / (out - 1)
+//   mode 1 nearest                      : src = min(floor(d * (float)in / out), in - 1), one tap
+//   mode 2 bilinear align_corners=False : src = max((d + 0.5) in / out - 0.5, 0)
+template <typename acc_t>
+__device__ __forceinline__ void axis_taps(int mode, int d, int in, int out, int& i0, int& i1, acc_t& w0, acc_t& w1) {
+  if (mode == 1) {
+    const float sc = (float)in / (float)out;
+    i0 = (int)floorf(d * sc);
+    i0 = i0 < in - 1 ? i0 : in - 1;
+    i1 = i0; w0 = acc_t(1); w1 = acc_t(0);
+    return;
+  }
+  acc_t f;
+  if (mode == 0) f = (out > 1 ? (acc_t)(in - 1) / (acc_t)(out - 1) : acc_t(0)) * d;
+  else { f = ((acc_t)d + acc_t(0.5)) * ((acc_t)in / (acc_t)out) - acc_t(0.5); f = f < acc_t(0) ? acc_t(0) : f; }
+  i0 = (int)f;
+  i0 = i0 < in - 1 ? i0 : in - 1;
+  i1 = i0 + (i0 < in - 1 ? 1 : 0);
+  w1 = f - i0; w0 = acc_t(1) - w1;
+}
+
+// Adjoint of the resize: one thread per SOURCE pixel gathers, in a fixed order, the gradients of the destination pixels
+// that read it (no atomics: deterministic).  grad_out [N,Ho,Wo] -> grad_in [N,Hi,Wi], arithmetic type = element type.
+template <typename acc_t>
+__global__ void __launch_bounds__(kOpThreads) resize_bwd_kernel(int Hi, int Wi, int Ho, int Wo, int mode, const acc_t* gout,
+                                                                acc_t* gin) {
+  const size_t n = blockIdx.y;
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (size_t)Hi * Wi) return;
+  const int y = (int)(i / Wi), x = (int)(i - (size_t)y * Wi);
+  // destination range whose taps can touch source index s (monotone maps; one extra index on both sides)
+  auto range = [&](int s, int in, int out, int& lo, int& hi) {
+    double a, b;
+    if (mode == 1) { const double sc = (double)in / out; a = s / sc; b = (s + 1) / sc; }
+    else if (mode == 0) {
+      if (out <= 1 || in <= 1) { lo = 0; hi = out - 1; return; }
+      const double r = (double)(in - 1) / (out - 1); a = (s - 1) / r; b = (s + 1) / r;
+    } else { const double sc = (double)in / out; a = (s - 0.5) / sc - 0.5; b = (s + 1.5) / sc - 0.5; }
+    lo = (int)floor(a) - 2; hi = (int)ceil(b) + 2;
+    lo = lo < 0 ? 0 : lo; hi = hi > out - 1 ? out - 1 : hi;
+  };
+  int ylo, yhi, xlo, xhi;
+  range(y, Hi, Ho, ylo, yhi);
+  range(x, Wi, Wo, xlo, xhi);
+  const acc_t* g = gout + n * (size_t)Ho * Wo;
+  acc_t acc = acc_t(0);
+  for (int dy = ylo; dy <= yhi; ++dy) {
+    int a0, a1; acc_t u0, u1;
+    axis_taps<acc_t>(mode, dy, Hi, Ho, a0, a1, u0, u1);
+    const acc_t wy = (a0 == y ? u0 : acc_t(0)) + (a1 == y && a1 != a0 ? u1 : acc_t(0));
+    if (wy == acc_t(0)) continue;
+    acc_t row = acc_t(0);
+    for (int dx = xlo; dx <= xhi; ++dx) {
+      int b0, b1; acc_t v0, v1;
+      axis_taps<acc_t>(mode, dx, Wi, Wo, b0, b1, v0, v1);
+      const acc_t wx = (b0 == x ? v0 : acc_t(0)) + (b1 == x && b1 != b0 ? v1 : acc_t(0));
+      if (wx != acc_t(0)) row += wx * g[(size_t)dy * Wo + dx];
+    }
+    acc += wy * row;
+  }
+  gin[n * (size_t)Hi * Wi + i] = acc;
+}
+
 template <typename T, typename acc_t>
 __global__ void __launch_bounds__(kOpThreads) resize_kernel(int Hi, int Wi, int Ho, int Wo, int mode, const T* in, T* out) {
   const size_t n = blockIdx.y;
@@ -126,6 +190,15 @@ __global__ void __launch_bounds__(kOpThreads) resize_kernel(int Hi, int Wi, int 
   if (i >= (size_t)Ho * Wo) return;
   const int y = (int)(i / Wo), x = (int)(i - (size_t)y * Wo);
   const T* src = in + n * (size_t)Hi * Wi;
+  if (mode == 2) {
+    int y0, y1, x0, x1; acc_t hy, ly, hx, lx;
+    axis_taps<acc_t>(2, y, Hi, Ho, y0, y1, hy, ly);
+    axis_taps<acc_t>(2, x, Wi, Wo, x0, x1, hx, lx);
+    const acc_t v = hy * (hx * ldimg<acc_t>(src, (size_t)y0 * Wi + x0) + lx * ldimg<acc_t>(src, (size_t)y0 * Wi + x1)) +
+                    ly * (hx * ldimg<acc_t>(src, (size_t)y1 * Wi + x0) + lx * ldimg<acc_t>(src, (size_t)y1 * Wi + x1));
+    st_val<T>(out + n * (size_t)Ho * Wo + i, (double)v);
+    return;
+  }
   if (mode == 1) {
     // upsample_nearest2d: scale = in / out computed in float, src = min(floor(dst * scale), in - 1)
     const float sy = (float)Hi / (float)Ho, sx = (float)Wi / (float)Wo;
@@ -222,6 +295,17 @@ cudaError_t resize_dispatch(int N, int Hi, int Wi, int Ho, int Wo, int dtype, in
                                                                      (__nv_bfloat16*)out);
   else
     resize_kernel<float, float><<<grid, kOpThreads, 0, st>>>(Hi, Wi, Ho, Wo, mode, (const float*)in, (float*)out);
+  return cudaGetLastError();
+}
+
+cudaError_t resize_backward_dispatch(int N, int Hi, int Wi, int Ho, int Wo, int dtype, int mode, const void* gout, void* gin,
+                                     cudaStream_t st) {
+  dim3 grid((unsigned)(((size_t)Hi * Wi + kOpThreads - 1) / kOpThreads), N);
+  count_launches(1);
+  if (dtype == PSFM_F64)
+    resize_bwd_kernel<double><<<grid, kOpThreads, 0, st>>>(Hi, Wi, Ho, Wo, mode, (const double*)gout, (double*)gin);
+  else
+    resize_bwd_kernel<float><<<grid, kOpThreads, 0, st>>>(Hi, Wi, Ho, Wo, mode, (const float*)gout, (float*)gin);
   return cudaGetLastError();
 }
 

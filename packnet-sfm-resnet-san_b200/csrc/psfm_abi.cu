@@ -13,7 +13,7 @@
 #include <vector>
 
 namespace psfm {
-size_t loss_workspace_bytes(const psfm_loss_cfg* cfg);
+size_t loss_workspace_bytes(const psfm_loss_cfg* cfg, const psfm_loss_io* io);
 cudaError_t loss_forward_dispatch(const psfm_loss_cfg*, const psfm_loss_io*, void*, void*, cudaStream_t);
 cudaError_t loss_backward_dispatch(const psfm_loss_cfg*, const psfm_loss_io*, void*, const void*, cudaStream_t);
 cudaError_t loss_fused_dispatch(const psfm_loss_cfg*, const psfm_loss_io*, void*, void*, cudaStream_t);
@@ -23,6 +23,7 @@ size_t warp_workspace_bytes(int, int, int, int);
 cudaError_t warp_backward_dispatch(int, int, int, int, int, int, const void*, const void*, const void*, const void*,
                                    const void*, const void*, void*, void*, void*, void*, cudaStream_t);
 cudaError_t resize_dispatch(int, int, int, int, int, int, int, const void*, void*, cudaStream_t);
+cudaError_t resize_backward_dispatch(int, int, int, int, int, int, int, const void*, void*, cudaStream_t);
 cudaError_t scale_dispatch(void*, const void*, size_t, int, cudaStream_t);
 }  // namespace psfm
 
@@ -169,7 +170,12 @@ const char* psfm_last_error(void) { return g_err; }
 
 size_t psfm_loss_workspace_bytes(const psfm_loss_cfg* cfg) {
   if (check_cfg(cfg) != PSFM_OK) return 0;
-  return psfm::loss_workspace_bytes(cfg);
+  return psfm::loss_workspace_bytes(cfg, nullptr);
+}
+
+size_t psfm_loss_workspace_bytes_io(const psfm_loss_cfg* cfg, const psfm_loss_io* io) {
+  if (check_cfg(cfg) != PSFM_OK || !io) return 0;
+  return psfm::loss_workspace_bytes(cfg, io);
 }
 
 int psfm_loss_forward(const psfm_loss_cfg* cfg, const psfm_loss_io* io, void* workspace, size_t workspace_bytes,
@@ -185,8 +191,8 @@ int psfm_loss_forward(const psfm_loss_cfg* cfg, const psfm_loss_io* io, void* wo
   if (cfg->camera_model == PSFM_CAM_FISHEYE) return psfm_fail(PSFM_ERR_INVALID, "fisheye cameras: use psfm_loss_forward_backward");
   if (cfg->img_dtype == PSFM_U8) return psfm_fail(PSFM_ERR_INVALID, "u8 images: use psfm_loss_forward_backward");
   if (!loss_out || !workspace) return psfm_fail(PSFM_ERR_INVALID, "loss_out / workspace is NULL");
-  if (workspace_bytes < psfm::loss_workspace_bytes(cfg))
-    return psfm_fail(PSFM_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes, psfm::loss_workspace_bytes(cfg));
+  if (workspace_bytes < psfm::loss_workspace_bytes(cfg, io))
+    return psfm_fail(PSFM_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes, psfm::loss_workspace_bytes(cfg, io));
   return cuda_result(psfm::loss_forward_dispatch(cfg, io, workspace, loss_out, (cudaStream_t)stream), "psfm_loss_forward");
 }
 
@@ -203,8 +209,8 @@ int psfm_loss_backward(const psfm_loss_cfg* cfg, const psfm_loss_io* io, void* w
   if (cfg->camera_model == PSFM_CAM_FISHEYE) return psfm_fail(PSFM_ERR_INVALID, "fisheye cameras: use psfm_loss_forward_backward");
   if (cfg->img_dtype == PSFM_U8) return psfm_fail(PSFM_ERR_INVALID, "u8 images: use psfm_loss_forward_backward");
   if (!grad_loss || !workspace) return psfm_fail(PSFM_ERR_INVALID, "grad_loss / workspace is NULL");
-  if (workspace_bytes < psfm::loss_workspace_bytes(cfg))
-    return psfm_fail(PSFM_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes, psfm::loss_workspace_bytes(cfg));
+  if (workspace_bytes < psfm::loss_workspace_bytes(cfg, io))
+    return psfm_fail(PSFM_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes, psfm::loss_workspace_bytes(cfg, io));
   return cuda_result(psfm::loss_backward_dispatch(cfg, io, workspace, grad_loss, (cudaStream_t)stream),
                      "psfm_loss_backward");
 }
@@ -215,8 +221,8 @@ int psfm_loss_forward_backward(const psfm_loss_cfg* cfg, const psfm_loss_io* io,
   if (rc) return rc;
   if ((rc = check_io(cfg, io, true))) return rc;
   if (!loss_out || !workspace) return psfm_fail(PSFM_ERR_INVALID, "loss_out / workspace is NULL");
-  if (workspace_bytes < psfm::loss_workspace_bytes(cfg))
-    return psfm_fail(PSFM_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes, psfm::loss_workspace_bytes(cfg));
+  if (workspace_bytes < psfm::loss_workspace_bytes(cfg, io))
+    return psfm_fail(PSFM_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes, psfm::loss_workspace_bytes(cfg, io));
   return cuda_result(psfm::loss_fused_dispatch(cfg, io, workspace, loss_out, (cudaStream_t)stream),
                      "psfm_loss_forward_backward");
 }
@@ -271,9 +277,20 @@ int psfm_warp_backward(int B, int H, int W, int img_dtype, int real_dtype, int p
 int psfm_resize(int N, int Hi, int Wi, int Ho, int Wo, int dtype, int mode, const void* in, void* out, void* stream) {
   if (N < 1 || Hi < 1 || Wi < 1 || Ho < 1 || Wo < 1) return psfm_fail(PSFM_ERR_INVALID, "bad resize shape");
   if (dtype != PSFM_F32 && dtype != PSFM_BF16 && dtype != PSFM_F64) return psfm_fail(PSFM_ERR_INVALID, "bad dtype");
-  if (mode != 0 && mode != 1) return psfm_fail(PSFM_ERR_INVALID, "mode must be 0 (bilinear) or 1 (nearest)");
+  if (mode < 0 || mode > 2)
+    return psfm_fail(PSFM_ERR_INVALID, "mode must be 0 (bilinear, align_corners=True), 1 (nearest) or 2 (bilinear, align_corners=False)");
   if (!in || !out) return psfm_fail(PSFM_ERR_INVALID, "NULL pointer argument");
   return cuda_result(psfm::resize_dispatch(N, Hi, Wi, Ho, Wo, dtype, mode, in, out, (cudaStream_t)stream), "psfm_resize");
+}
+
+int psfm_resize_backward(int N, int Hi, int Wi, int Ho, int Wo, int dtype, int mode, const void* grad_out, void* grad_in,
+                         void* stream) {
+  if (N < 1 || Hi < 1 || Wi < 1 || Ho < 1 || Wo < 1) return psfm_fail(PSFM_ERR_INVALID, "bad resize shape");
+  if (dtype != PSFM_F32 && dtype != PSFM_F64) return psfm_fail(PSFM_ERR_INVALID, "gradients are f32 or f64");
+  if (mode < 0 || mode > 2) return psfm_fail(PSFM_ERR_INVALID, "mode must be 0, 1 or 2");
+  if (!grad_out || !grad_in) return psfm_fail(PSFM_ERR_INVALID, "NULL pointer argument");
+  return cuda_result(psfm::resize_backward_dispatch(N, Hi, Wi, Ho, Wo, dtype, mode, grad_out, grad_in, (cudaStream_t)stream),
+                     "psfm_resize_backward");
 }
 
 }  // extern "C"

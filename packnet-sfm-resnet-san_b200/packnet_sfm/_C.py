@@ -19,14 +19,15 @@ REDUCE = {'min': 0, 'mean': 1}
 CAM_PINHOLE, CAM_FISHEYE = 0, 1
 
 EXPORTS = ('psfm_abi_version', 'psfm_last_error', 'psfm_launch_count', 'psfm_profile_enable', 'psfm_profile_read',
-           'psfm_loss_workspace_bytes', 'psfm_loss_forward',
+           'psfm_loss_workspace_bytes', 'psfm_loss_workspace_bytes_io', 'psfm_loss_forward',
            'psfm_loss_backward', 'psfm_loss_forward_backward', 'psfm_scale_inplace', 'psfm_warp_forward',
-           'psfm_warp_workspace_bytes', 'psfm_warp_backward', 'psfm_resize',
+           'psfm_warp_workspace_bytes', 'psfm_warp_backward', 'psfm_resize', 'psfm_resize_backward',
            'psfm_block_workspace_bytes', 'psfm_reconstruct', 'psfm_reconstruct_backward', 'psfm_project',
            'psfm_project_backward', 'psfm_transform_points', 'psfm_transform_points_backward',
            'psfm_pose_from_vec', 'psfm_pose_from_vec_backward',
            'psfm_fisheye_reconstruct', 'psfm_fisheye_reconstruct_backward', 'psfm_fisheye_project',
            'psfm_fisheye_project_backward', 'psfm_grid_sample', 'psfm_grid_sample_backward',
+           'psfm_raysurf_project', 'psfm_raysurf_project_backward',
            'psfm_supervised_loss', 'psfm_supervised_loss_backward', 'psfm_dual_head_loss', 'psfm_dual_head_loss_backward',
            'psfm_depth_metrics_workspace_bytes', 'psfm_depth_metrics',
            'psfm_sobel_gradient_code_bytes', 'psfm_sobel_gradient_workspace_bytes', 'psfm_sobel_gradient_loss',
@@ -75,6 +76,8 @@ def _load():
     lib.psfm_profile_read.argtypes = [C.POINTER(C.c_float), C.POINTER(C.c_int), i]
     lib.psfm_loss_workspace_bytes.restype = sz
     lib.psfm_loss_workspace_bytes.argtypes = [C.POINTER(LossCfg)]
+    lib.psfm_loss_workspace_bytes_io.restype = sz
+    lib.psfm_loss_workspace_bytes_io.argtypes = [C.POINTER(LossCfg), C.POINTER(LossIO)]
     lib.psfm_loss_forward.restype = i
     lib.psfm_loss_forward.argtypes = [C.POINTER(LossCfg), C.POINTER(LossIO), vp, sz, vp, vp]
     lib.psfm_loss_backward.restype = i
@@ -91,6 +94,8 @@ def _load():
     lib.psfm_warp_backward.argtypes = [i, i, i, i, i, i, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, sz, vp]
     lib.psfm_resize.restype = i
     lib.psfm_resize.argtypes = [i, i, i, i, i, i, i, vp, vp, vp]
+    lib.psfm_resize_backward.restype = i
+    lib.psfm_resize_backward.argtypes = [i, i, i, i, i, i, i, vp, vp, vp]
     d = C.c_double
     lib.psfm_block_workspace_bytes.restype = sz
     lib.psfm_block_workspace_bytes.argtypes = [i, sz]
@@ -110,6 +115,8 @@ def _load():
             ('psfm_fisheye_reconstruct_backward', [i, i, i, i, vp, vp, vp, vp]),
             ('psfm_fisheye_project', [i, sz, i, i, i, vp, vp, vp, vp]),
             ('psfm_fisheye_project_backward', [i, sz, i, i, i, vp, vp, vp, vp, vp]),
+            ('psfm_raysurf_project', [i, i, i, i, d, vp, vp, vp, vp, vp, vp]),
+            ('psfm_raysurf_project_backward', [i, i, i, i, d, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
             ('psfm_grid_sample', [i, i, i, i, i, i, i, vp, vp, vp, vp]),
             ('psfm_grid_sample_backward', [i, i, i, i, i, i, i, vp, vp, vp, vp, vp]),
             ('psfm_supervised_loss', [i, i, sz, i, vp, vp, vp, C.POINTER(d), vp, vp, vp, sz, vp]),

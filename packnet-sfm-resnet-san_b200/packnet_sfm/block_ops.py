@@ -227,6 +227,46 @@ def grid_sample_op(image, grid, padding_mode='zeros'):
     return _GridSample.apply(image, grid, _C.PAD[padding_mode])
 
 
+class _RaysurfProject(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, direction, rays, temperature):
+        _C.require_cuda(direction, rays)
+        dt = _real(direction)
+        if direction.dim() != 4 or direction.shape[1] != 3 or rays.shape != direction.shape:
+            raise ValueError('direction and rays must both be [B,3,h,w]')
+        direction, rays = direction.contiguous(), rays.to(direction.dtype).contiguous()
+        B, _, h, w = direction.shape
+        coords = torch.empty((B, h, w, 2), dtype=direction.dtype, device=direction.device)
+        dhat = torch.empty_like(direction)
+        stats = torch.empty_like(coords)
+        with torch.cuda.device(direction.device):
+            _C.check(_C.lib.psfm_raysurf_project(B, h, w, dt, float(temperature), _C.ptr(direction), _C.ptr(rays),
+                                                 _C.ptr(coords), _C.ptr(dhat), _C.ptr(stats),
+                                                 _C.stream_ptr(direction.device)))
+        ctx.save_for_backward(direction, rays, coords, dhat, stats)
+        ctx.temperature = float(temperature)
+        return coords
+
+    @staticmethod
+    def backward(ctx, g):
+        direction, rays, coords, dhat, stats = ctx.saved_tensors
+        B, _, h, w = direction.shape
+        g = g.to(direction.dtype).contiguous()
+        d_dir, d_rays = torch.empty_like(direction), torch.empty_like(rays)
+        with torch.cuda.device(direction.device):
+            _C.check(_C.lib.psfm_raysurf_project_backward(B, h, w, _real(direction), ctx.temperature, _C.ptr(direction),
+                                                          _C.ptr(rays), _C.ptr(coords), _C.ptr(dhat), _C.ptr(stats),
+                                                          _C.ptr(g), _C.ptr(d_dir), _C.ptr(d_rays),
+                                                          _C.stream_ptr(direction.device)))
+        return d_dir, d_rays, None
+
+
+def raysurf_project_op(direction, rays, temperature):
+    """Soft arg-max projection of the ray-surface camera (reference geometry/camera_generic.py:151-199): point
+    directions [B,3,h,w] and viewing rays [B,3,h,w] -> (row, col) coordinates [B,h,w,2]; differentiable w.r.t. both."""
+    return _RaysurfProject.apply(direction, rays, temperature)
+
+
 class _TransformPoints(torch.autograd.Function):
     @staticmethod
     def forward(ctx, mat, X):

@@ -39,3 +39,15 @@ def view_synthesis(ref_image, depth, ref_cam, cam, mode='bilinear', padding_mode
     if not cam._identity_pose:
         T = T.bmm(cam.Twc.mat.to(T.dtype))
     return view_synthesis_op(ref_image, depth, cam.K, ref_cam.K, T, padding_mode)
+
+
+def view_synthesis_generic(ref_image, depth, ref_cam, cam, mode='bilinear', padding_mode='zeros', progress=0.0):
+    """Warp `ref_image` with two ray-surface cameras (reference :64-96): reconstruct with `cam`, project with
+    `ref_cam` (soft arg-max kernels, geometry/camera_generic.py), bilinear gather."""
+    assert depth.size(1) == 1
+    if mode != 'bilinear':
+        raise NotImplementedError('only bilinear view synthesis is implemented')
+    from packnet_sfm.block_ops import grid_sample_op
+    world_points = cam.reconstruct(depth, frame='w')
+    ref_coords = ref_cam.project(world_points, progress=progress, frame='w')
+    return grid_sample_op(ref_image, ref_coords, padding_mode)

@@ -60,20 +60,61 @@ def _as_batched_K(K, B, dtype):
     return K.to(dtype).contiguous()
 
 
+RESIZE_MODES = {'bilinear': 0, 'nearest': 1, 'bilinear_ac_false': 2}
+
+
+class _ResizeFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, Ho, Wo, mode):
+        x = x.contiguous()
+        Hi, Wi = x.shape[-2:]
+        out = torch.empty(x.shape[:-2] + (Ho, Wo), dtype=x.dtype, device=x.device)
+        N = x.numel() // (Hi * Wi)
+        with torch.cuda.device(x.device):
+            _C.check(_C.lib.psfm_resize(N, Hi, Wi, Ho, Wo, _C.dtype_code(x), mode, _C.ptr(x), _C.ptr(out),
+                                        _C.stream_ptr(x.device)))
+        ctx.geom = (N, Hi, Wi, Ho, Wo, mode, x.shape, x.dtype)
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        N, Hi, Wi, Ho, Wo, mode, shape, dtype = ctx.geom
+        real = torch.float64 if dtype == torch.float64 else torch.float32
+        g = grad_out.to(real).contiguous()
+        gin = torch.empty(shape, dtype=real, device=g.device)
+        with torch.cuda.device(g.device):
+            _C.check(_C.lib.psfm_resize_backward(N, Hi, Wi, Ho, Wo, _C.dtype_code(g), mode, _C.ptr(g), _C.ptr(gin),
+                                                 _C.stream_ptr(g.device)))
+        return gin.to(dtype), None, None, None
+
+
 def resize_op(x, size, mode='bilinear'):
-    """[..,Hi,Wi] -> [..,Ho,Wo]; bilinear means align_corners=True.  No autograd."""
+    """[..,Hi,Wi] -> [..,Ho,Wo] with F.interpolate's arithmetic: 'bilinear' (align_corners=True), 'nearest',
+    'bilinear_ac_false' (align_corners=False).  Differentiable (reference utils/image.py:117-146 runs F.interpolate
+    under autograd; the model's upsample_output, models/model_utils.py:175-193, needs the gradient)."""
     _C.require_cuda(x)
-    if x.requires_grad:
-        raise NotImplementedError('resize of a tensor that requires grad is outside the accelerated path')
-    Ho, Wo = int(size[0]), int(size[1])
-    x = x.contiguous()
-    Hi, Wi = x.shape[-2:]
-    out = torch.empty(x.shape[:-2] + (Ho, Wo), dtype=x.dtype, device=x.device)
-    N = x.numel() // (Hi * Wi)
-    with torch.cuda.device(x.device):
-        _C.check(_C.lib.psfm_resize(N, Hi, Wi, Ho, Wo, _C.dtype_code(x), 0 if mode == 'bilinear' else 1,
-                                    _C.ptr(x), _C.ptr(out), _C.stream_ptr(x.device)))
-    return out
+    if mode not in RESIZE_MODES:
+        raise NotImplementedError('resize mode %s' % mode)
+    if x.dtype == torch.uint8:
+        raise ValueError('resize takes float images')
+    return _ResizeFn.apply(x, int(size[0]), int(size[1]), RESIZE_MODES[mode])
+
+
+_WS_CACHE = {}
+
+
+def _workspace(dev, nbytes, shared):
+    """Scratch buffer of a loss call.  `shared`: one persistent buffer per (device, stream), grown on demand -- valid
+    for the fused mode, whose workspace is dead once the forward kernels have run (stream order protects the next
+    call); the split mode keeps per-call scratch because its backward reads the forward's state."""
+    if not shared or torch.cuda.is_current_stream_capturing():
+        return torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
+    buf = _WS_CACHE.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        _WS_CACHE[key] = buf
+    return buf
 
 
 class _LossPlan:
@@ -166,10 +207,12 @@ class _LossPlan:
             io.pose[j] = m.data_ptr()
         self.keep = keep
         self.cfg, self.io = cfg, io
-        self.ws_bytes = int(_C.lib.psfm_loss_workspace_bytes(C.byref(cfg)))
+        # scratch for the image sets that exist (one set when every scale is at image resolution); the fused mode
+        # needs it only while the forward call's kernels run, so calls on the same stream share one buffer
+        self.ws_bytes = int(_C.lib.psfm_loss_workspace_bytes_io(C.byref(cfg), C.byref(io)))
         if self.ws_bytes == 0:
             _C.check(-1)
-        self.ws = torch.empty(self.ws_bytes, dtype=torch.uint8, device=dev)
+        self.ws = _workspace(dev, self.ws_bytes, shared=hp.get('_mode') == 'fused')
         self.sel = [torch.empty((B, cfg.Hs[s], cfg.Ws[s]), dtype=torch.uint8, device=dev) for s in range(n)]
         for s in range(n):
             io.sel[s] = self.sel[s].data_ptr()
@@ -206,7 +249,7 @@ class _PhotometricLossFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, hp, mode, image, K, ref_K, mask, n, Cn, *tensors):
         context, inv_depths, pose_mats = tensors[:Cn], tensors[Cn:Cn + n], tensors[Cn + n:]
-        plan = _LossPlan(hp, image, context, inv_depths, K, ref_K, pose_mats, mask)
+        plan = _LossPlan(dict(hp, _mode=mode), image, context, inv_depths, K, ref_K, pose_mats, mask)
         need_grad = any(t.requires_grad for t in tensors[Cn:])
         st = _C.stream_ptr(plan.dev)
         with torch.cuda.device(plan.dev):
@@ -235,13 +278,24 @@ class _PhotometricLossFn(torch.autograd.Function):
         g = grad_out.to(plan.real).contiguous()
         st = _C.stream_ptr(plan.dev)
         with torch.cuda.device(plan.dev):
-            if ctx.mode == 'fused':
-                if ctx.consumed:
-                    raise RuntimeError('the fused photometric loss keeps its gradients in place and can be '
-                                       'back-propagated once; use mode="split" to retain the graph')
+            if ctx.mode == 'fused' and not ctx.consumed:
                 ctx.consumed = True
                 _C.check(_C.lib.psfm_scale_inplace(_C.ptr(plan.grads), _C.ptr(g), plan.grads.numel(),
                                                    plan.cfg.real_dtype, st))
+            elif ctx.mode == 'fused':
+                # a second backward through the same graph (retain_graph=True): the fused pass handed its gradient
+                # buffers to autograd the first time, so this one recomputes them with the forward / backward kernel
+                # pair from the inputs the node still holds
+                if plan.upsampled or plan.fisheye or plan.u8:
+                    raise RuntimeError('a second backward through the fused photometric loss is recomputed by the '
+                                       'split kernels, which do not take upsample_depth_maps / fisheye cameras / '
+                                       'uint8 images; call the loss again instead')
+                plan.alloc_grads()
+                ws = torch.empty(plan.ws_bytes, dtype=torch.uint8, device=plan.dev)
+                out = torch.empty(3, dtype=plan.real, device=plan.dev)
+                args = (C.byref(plan.cfg), C.byref(plan.io), _C.ptr(ws), plan.ws_bytes)
+                _C.check(_C.lib.psfm_loss_forward(*args, _C.ptr(out), st))
+                _C.check(_C.lib.psfm_loss_backward(*args, _C.ptr(g), st))
             else:
                 plan.alloc_grads()
                 _C.check(_C.lib.psfm_loss_backward(*plan.args(), _C.ptr(g), st))

@@ -18,17 +18,18 @@ def gradient_y(image):
 
 def interpolate_image(image, shape, mode='bilinear', align_corners=True):
     """Resize to `shape`; returns `image` itself when the spatial size already matches
-    (reference :117-146).  bilinear/align_corners=True and nearest run as CUDA kernels."""
+    (reference :117-146).  bilinear (both align_corners settings) and nearest run as CUDA kernels, with their adjoint
+    under autograd."""
     if len(shape) > 2:
         shape = shape[-2:]
     if same_shape(image.shape[-2:], shape):
         return image
     from packnet_sfm.ops import resize_op
-    if mode == 'bilinear' and align_corners:
-        return resize_op(image, shape, 'bilinear')
+    if mode == 'bilinear':
+        return resize_op(image, shape, 'bilinear' if align_corners else 'bilinear_ac_false')
     if mode == 'nearest':
         return resize_op(image, shape, 'nearest')
-    raise NotImplementedError('interpolate_image supports bilinear/align_corners=True and nearest')
+    raise NotImplementedError('interpolate_image supports the bilinear and nearest modes')
 
 
 def interpolate_scales(images, shape=None, mode='bilinear', align_corners=False):

@@ -201,3 +201,27 @@ def test_ssi_gradient_term_oracle_matches_reference():
             np.testing.assert_allclose(preds[0].grad.numpy(), gold[name + '/d_pred'], rtol=1e-10, atol=1e-14, err_msg=name)
         else:
             assert not gold[name + '/d_pred'].any()
+
+
+def test_raysurf_oracle_matches_the_reference_fixtures():
+    """oracle/raysurf_oracle.py against GenericMultiViewPhotometricLoss / GenericCamera outputs."""
+    import numpy as np
+    import photometric_oracle as O
+    import raysurf_oracle as RO
+    for name, (skw, hp) in RO.RAYSURF_CASES.items():
+        g = load_golden(name)
+        cfg = dict(RO.RAYSURF_LOSS)
+        cfg.update(hp)
+        image, context, invd, res, vecs, tmpl = RO.synth_raysurf(skw['H'], skw['W'], skw['C'])
+        invd, res = invd.clone().requires_grad_(), res.clone().requires_grad_()
+        vecs = [v.clone().requires_grad_() for v in vecs]
+        out = RO.generic_photometric_loss(image, context, invd, res, tmpl, [O.pose_vec_to_mat(v) for v in vecs],
+                                          skw['progress'], **cfg)
+        out['loss'].backward()
+        rel = lambda a, b: float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300))
+        assert abs(out['loss'].item() - g['loss'].item()) <= 1e-12 * abs(g['loss'].item())
+        assert np.abs(out['warped'][0].detach().numpy() - g['warped0']).max() <= 1e-11
+        assert rel(invd.grad.numpy(), g['d_inv_depth']) <= 1e-10
+        assert rel(np.stack([v.grad.numpy() for v in vecs]), g['d_vec']) <= 1e-10
+        if np.linalg.norm(g['d_residual']) > 0:
+            assert rel(res.grad.numpy(), g['d_residual']) <= 1e-10
