@@ -169,13 +169,13 @@ __global__ void __launch_bounds__(kOpThreads) resize_bwd_kernel(int Hi, int Wi, 
   for (int dy = ylo; dy <= yhi; ++dy) {
     int a0, a1; acc_t u0, u1;
     axis_taps<acc_t>(mode, dy, Hi, Ho, a0, a1, u0, u1);
-    const acc_t wy = (a0 == y ? u0 : acc_t(0)) + (a1 == y && a1 != a0 ? u1 : acc_t(0));
+    const acc_t wy = (a0 == y ? u0 : acc_t(0)) + (a1 == y ? u1 : acc_t(0));      // a1 == a0 at the last row: both weights count
     if (wy == acc_t(0)) continue;
     acc_t row = acc_t(0);
     for (int dx = xlo; dx <= xhi; ++dx) {
       int b0, b1; acc_t v0, v1;
       axis_taps<acc_t>(mode, dx, Wi, Wo, b0, b1, v0, v1);
-      const acc_t wx = (b0 == x ? v0 : acc_t(0)) + (b1 == x && b1 != b0 ? v1 : acc_t(0));
+      const acc_t wx = (b0 == x ? v0 : acc_t(0)) + (b1 == x ? v1 : acc_t(0));
       if (wx != acc_t(0)) row += wx * g[(size_t)dy * Wo + dx];
     }
     acc += wy * row;
