@@ -50,8 +50,13 @@ class SSISilogLoss(LossBase):
             from packnet_sfm.block_ops import sobel_gradient_loss_op
             gradient_loss, self.gradient_state = sobel_gradient_loss_op(pred_inv_depth, gt_inv_depth, mask=mask,
                                                                         scales=self.gradient_scales)
-            # fewer than 100 valid pixels: the whole loss is the constant 0 (:398-400); decided on the device
-            loss = loss + (st[4] >= 100).to(loss.dtype) * (self.gradient_weight * gradient_loss)
+            # fewer than 100 valid pixels: the whole loss is the constant 0 (:398-400); a NaN ssi / silog part: the
+            # constant 1 (:403-407; state[15] flags both); a NaN gradient term is dropped (:410-411).  All decided on the
+            # device (torch.where, not a product: 0 * NaN is NaN)
+            import torch
+            term = self.gradient_weight * gradient_loss
+            keep = (st[4] >= 100) & (st[15] == 0) & torch.isfinite(term)
+            loss = loss + torch.where(keep, term, torch.zeros_like(term)).to(loss.dtype)
         self.add_metric('ssi_mean', st[10])
         self.add_metric('ssi_var', st[11])
         self.add_metric('silog1', st[12])

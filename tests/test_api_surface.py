@@ -191,3 +191,42 @@ def test_identity_resize_returns_same_object():
     assert interpolate_image(img, (8, 10)) is img
     assert match_scales(img, [torch.rand(2, 1, 8, 10)] * 2, 2)[1] is img
     assert gradient_x(img).shape == (2, 3, 8, 9) and gradient_y(img).shape == (2, 3, 7, 10)
+
+
+def test_workspace_size_follows_the_image_sets_without_gpu():
+    """psfm_loss_workspace_bytes_io (round 2): scales that share their image pointers share the image-sized scratch; the
+    configuration-only query stays the upper bound.  Pure host arithmetic: no CUDA call."""
+    from packnet_sfm import _C
+
+    def make(B, H, W, Cn, n, shared):
+        cfg = _C.LossCfg()
+        cfg.B, cfg.C, cfg.n, cfg.H, cfg.W = B, Cn, n, H, W
+        for s in range(n):
+            cfg.Hs[s], cfg.Ws[s] = H, W
+        cfg.automask, cfg.ssim_w, cfg.smooth_w, cfg.C1, cfg.C2 = 1, 0.85, 0.001, 1e-4, 9e-4
+        io = _C.LossIO()
+        for s in range(n):
+            base = 0x10000 * (1 if shared else s + 1)
+            io.image[s], io.inv_depth[s] = base, 0x900000 + s
+            for j in range(Cn):
+                io.ctx[s][j] = base + 0x100 * (j + 1)
+        return cfg, io
+
+    cfg, io = make(8, 192, 640, 2, 4, shared=True)
+    upper = _C.lib.psfm_loss_workspace_bytes(ctypes.byref(cfg))
+    one_set = _C.lib.psfm_loss_workspace_bytes_io(ctypes.byref(cfg), ctypes.byref(io))
+    cfg2, io2 = make(8, 192, 640, 2, 4, shared=False)
+    four_sets = _C.lib.psfm_loss_workspace_bytes_io(ctypes.byref(cfg2), ctypes.byref(io2))
+    assert 0 < one_set < 0.3 * upper and one_set < 100 * 2 ** 20        # 86 MiB at config 2 (round 1: 337 MiB)
+    assert four_sets == upper
+    assert _C.lib.psfm_loss_workspace_bytes_io(ctypes.byref(cfg), None) == 0
+
+
+def test_class_default_is_the_upstream_inverse_depth_semantics():
+    """ADVICE (round 1): the fork's forward pre-maps sigmoids to inverse depths (:362-369); this build takes true inverse
+    depths unless `sigmoid_premap=True` is passed -- on purpose (north star), and the flag reaches the kernels."""
+    from packnet_sfm.losses.multiview_photometric_loss import MultiViewPhotometricLoss
+    assert MultiViewPhotometricLoss().sigmoid_premap is False
+    assert MultiViewPhotometricLoss()._hyper()['premap'] == 0
+    L = MultiViewPhotometricLoss(sigmoid_premap=True, min_depth=0.5, max_depth=80.0)
+    assert L._hyper()['premap'] == 1 and L._hyper()['min_depth'] == 0.5 and L._hyper()['max_depth'] == 80.0
