@@ -250,5 +250,42 @@ def main():
     save('B2_64x160_C2_U_zeros_clip', run_case(2, 64, 160, 2, False, clip_loss=0.5))
 
 
+def time_port_vs_reference(B=2, H=192, W=640, C=2, iters=5, threads=8):
+    """`--time`: frames/s of the reference's own classes and of the oracle port on the same fp32 inputs (build container
+    only; bench.py's reference arm runs the port because /root/reference does not exist on the GPU box)."""
+    import time
+    import photometric_oracle as O
+    torch.set_num_threads(threads)
+    image, context, inv_depths, vecs, K = synth_S3(B, H, W, C, torch.float32)
+    hp = dict(YAML_LOSS)
+
+    def ref_step():
+        d = [x.clone().requires_grad_() for x in inv_depths]
+        v = [x.clone().requires_grad_() for x in vecs]
+        out = PinholeReference(**hp)(image, context, d, K, K, [Pose.from_vec(x, 'euler') for x in v])
+        out['loss'].backward()
+        return float(out['loss'])
+
+    def port_step():
+        d = [x.clone().requires_grad_() for x in inv_depths]
+        v = [x.clone().requires_grad_() for x in vecs]
+        out = O.multiview_photometric_loss(image, context, d, K, K, [O.pose_vec_to_mat(x) for x in v], **hp)
+        out['loss'].backward()
+        return float(out['loss'])
+
+    res = {}
+    for name, fn in (('reference classes', ref_step), ('oracle port', port_step)):
+        loss = fn()
+        t0 = time.perf_counter()
+        for _ in range(iters):
+            fn()
+        res[name] = (B * iters / (time.perf_counter() - t0), loss)
+        print('%-18s %.2f frames/s  (loss %.9f, %d threads, B=%d %dx%d C=%d fp32)' % (name, res[name][0], loss, threads, B, H, W, C))
+    print('port / reference = %.3f' % (res['oracle port'][0] / res['reference classes'][0]))
+
+
 if __name__ == '__main__':
-    main()
+    if '--time' in sys.argv:
+        time_port_vs_reference()
+    else:
+        main()
